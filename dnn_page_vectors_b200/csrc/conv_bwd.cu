@@ -1,0 +1,226 @@
+// Backward of Convolution1D + global max-pool, arg-max sparse form.
+//   (gradient of dssm_cnn_v2/cnn_dssm_tf.py:84-100)
+// Only the arg-max window of each (sequence, filter) receives gradient, so instead of the two
+// dense-equivalent GEMMs (2x the forward FLOPs) this does S*F*k*D multiply-adds for each of dW
+// and dX -- ~T (= L-k+1) times fewer.  Both kernels are bound by L1/L2 row reads, not FLOPs.
+//   dW[j,c,f] = sum_s G[s,f] X[s, a(s,f)+j, c]      (dw kernel: lanes over c, registers over f,j)
+//   dX[s,t,c] = sum_{f,j: a(s,f)+j = t} G[s,f] W[j,c,f]   (dx kernel: one warp per output row)
+// Every sum is taken in a fixed order (s ascending / f ascending), no atomics: deterministic.
+#include "common.cuh"
+
+int clsm_colsum(const float* A, int64_t rows, int ld, int col0, int n, float* out, float* part,
+                int n_chunks, cudaStream_t st);   // dense.cu
+
+namespace {
+
+constexpr int FPW = 4;            // filters per warp
+constexpr int DW_WARPS = 32;      // warps per CTA -> 128 filters per CTA
+constexpr int FT = FPW * DW_WARPS;
+
+template <typename T> struct Pair;
+template <> struct Pair<float> {
+  static __device__ __forceinline__ float2 ld(const float* p) { return *reinterpret_cast<const float2*>(p); }
+};
+template <> struct Pair<__nv_bfloat16> {
+  static __device__ __forceinline__ float2 ld(const __nv_bfloat16* p) {
+    return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+  }
+};
+
+// grid (n_groups, Dpad/64, ceil(F/FT)); part[g][f][j][c]
+template <typename T, int KW>
+__global__ void __launch_bounds__(DW_WARPS * 32, 1)
+conv_bwd_dw_kernel(const T* __restrict__ X, int L, int Dpad, int64_t S, int64_t seq_per_group,
+                   const float* __restrict__ G, const int32_t* __restrict__ A, int ldp, int col0, int F,
+                   float* __restrict__ part) {
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int cbase = blockIdx.y * 64 + lane * 2;
+  const int f0 = blockIdx.z * FT + warp * FPW;
+  const int64_t s0 = static_cast<int64_t>(blockIdx.x) * seq_per_group;
+  const int64_t s1 = (s0 + seq_per_group < S) ? s0 + seq_per_group : S;
+  float2 acc[FPW][KW];
+#pragma unroll
+  for (int i = 0; i < FPW; ++i)
+#pragma unroll
+    for (int j = 0; j < KW; ++j) acc[i][j] = make_float2(0.f, 0.f);
+
+  for (int64_t s = s0; s < s1; ++s) {
+    float g = 0.0f; int a = 0;
+    if (lane < FPW && f0 + lane < F) {
+      g = __ldg(G + s * ldp + col0 + f0 + lane);
+      a = __ldg(A + s * ldp + col0 + f0 + lane);
+    }
+    const T* xs = X + s * L * static_cast<int64_t>(Dpad) + cbase;
+#pragma unroll
+    for (int i = 0; i < FPW; ++i) {
+      const float gi = __shfl_sync(0xffffffffu, g, i);
+      const int ai = __shfl_sync(0xffffffffu, a, i);
+      if (gi != 0.0f) {
+#pragma unroll
+        for (int j = 0; j < KW; ++j) {
+          const float2 x = Pair<T>::ld(xs + static_cast<int64_t>(ai + j) * Dpad);
+          acc[i][j].x = fmaf(gi, x.x, acc[i][j].x);
+          acc[i][j].y = fmaf(gi, x.y, acc[i][j].y);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < FPW; ++i) {
+    const int f = f0 + i;
+    if (f >= F) continue;
+#pragma unroll
+    for (int j = 0; j < KW; ++j) {
+      float* dst = part + ((static_cast<int64_t>(blockIdx.x) * F + f) * KW + j) * Dpad + cbase;
+      *reinterpret_cast<float2*>(dst) = acc[i][j];
+    }
+  }
+}
+
+// dW_ref[j][c][f] = sum_g part[g][f][j][c]
+__global__ void conv_bwd_dw_reduce_kernel(const float* __restrict__ part, int n_groups, int k, int D, int Dpad, int F,
+                                          float* __restrict__ dW) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int64_t n = static_cast<int64_t>(k) * D * F;
+  if (i >= n) return;
+  // consecutive threads walk c (contiguous in part); dW writes are strided by F but tiny.
+  const int c = static_cast<int>(i % D);
+  const int64_t r = i / D;
+  const int j = static_cast<int>(r % k);
+  const int f = static_cast<int>(r / k);
+  const int64_t stride = static_cast<int64_t>(F) * k * Dpad;
+  const float* src = part + (static_cast<int64_t>(f) * k + j) * Dpad + c;
+  float s = 0.0f;
+  for (int g = 0; g < n_groups; ++g) s += src[g * stride];
+  dW[(static_cast<int64_t>(j) * D + c) * F + f] = s;
+}
+
+// one warp per output row (s, t); lane owns columns {2*lane + 64*p, +1}, p < Dpad/64
+template <typename T>
+__global__ void __launch_bounds__(256)
+conv_bwd_dx_kernel(const T* __restrict__ Wt, int k, int Dpad, int64_t n_rows, int L,
+                   const float* __restrict__ G, const int32_t* __restrict__ A, int ldp, int col0, int F,
+                   float* __restrict__ dX, int accumulate) {
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int64_t r = static_cast<int64_t>(blockIdx.x) * 8 + warp;
+  if (r >= n_rows) return;
+  const int64_t s = r / L;
+  const int t = static_cast<int>(r - s * L);
+  const int np = Dpad / 64;
+  const int64_t K = static_cast<int64_t>(k) * Dpad;
+  float2 acc[8];
+#pragma unroll
+  for (int p = 0; p < 8; ++p) acc[p] = make_float2(0.f, 0.f);
+  for (int fb = 0; fb < F; fb += 32) {
+    const int f = fb + lane;
+    float g = 0.0f; int a = -0x40000000;
+    if (f < F) { g = __ldg(G + s * ldp + col0 + f); a = __ldg(A + s * ldp + col0 + f); }
+    const int j = t - a;                       // window offset that lands on this row
+    const bool hit = (g != 0.0f) && j >= 0 && j < k;
+    unsigned m = __ballot_sync(0xffffffffu, hit);
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      const float gs = __shfl_sync(0xffffffffu, g, src);
+      const int js = __shfl_sync(0xffffffffu, j, src);
+      const T* w = Wt + static_cast<int64_t>(fb + src) * K + static_cast<int64_t>(js) * Dpad + lane * 2;
+#pragma unroll
+      for (int p = 0; p < 8; ++p) {
+        if (p < np) {
+          const float2 x = Pair<T>::ld(w + p * 64);
+          acc[p].x = fmaf(gs, x.x, acc[p].x);
+          acc[p].y = fmaf(gs, x.y, acc[p].y);
+        }
+      }
+    }
+  }
+  float* dst = dX + r * Dpad + lane * 2;
+#pragma unroll
+  for (int p = 0; p < 8; ++p) {
+    if (p < np) {
+      float2 v = acc[p];
+      if (accumulate) { const float2 o = *reinterpret_cast<const float2*>(dst + p * 64); v.x += o.x; v.y += o.y; }
+      *reinterpret_cast<float2*>(dst + p * 64) = v;
+    }
+  }
+}
+
+int dw_groups(int64_t S, int Dpad, int F) {
+  const int per = (Dpad / 64) * ((F + FT - 1) / FT);
+  int64_t g = (4 * static_cast<int64_t>(clsm_sm_count()) + per - 1) / per;
+  if (g > S) g = S;
+  if (g < 1) g = 1;
+  return static_cast<int>(g);
+}
+const int kColsumChunks = 64;
+
+template <typename T>
+int launch_dw(const T* X, int L, int Dpad, int64_t S, int64_t spg, const float* G, const int32_t* A, int ldp,
+              int col0, int F, int k, float* part, dim3 grid, cudaStream_t st) {
+  switch (k) {
+    case 1: conv_bwd_dw_kernel<T, 1><<<grid, DW_WARPS * 32, 0, st>>>(X, L, Dpad, S, spg, G, A, ldp, col0, F, part); break;
+    case 2: conv_bwd_dw_kernel<T, 2><<<grid, DW_WARPS * 32, 0, st>>>(X, L, Dpad, S, spg, G, A, ldp, col0, F, part); break;
+    case 3: conv_bwd_dw_kernel<T, 3><<<grid, DW_WARPS * 32, 0, st>>>(X, L, Dpad, S, spg, G, A, ldp, col0, F, part); break;
+    case 4: conv_bwd_dw_kernel<T, 4><<<grid, DW_WARPS * 32, 0, st>>>(X, L, Dpad, S, spg, G, A, ldp, col0, F, part); break;
+    case 5: conv_bwd_dw_kernel<T, 5><<<grid, DW_WARPS * 32, 0, st>>>(X, L, Dpad, S, spg, G, A, ldp, col0, F, part); break;
+    case 6: conv_bwd_dw_kernel<T, 6><<<grid, DW_WARPS * 32, 0, st>>>(X, L, Dpad, S, spg, G, A, ldp, col0, F, part); break;
+    case 7: conv_bwd_dw_kernel<T, 7><<<grid, DW_WARPS * 32, 0, st>>>(X, L, Dpad, S, spg, G, A, ldp, col0, F, part); break;
+    default: return CLSM_EUNSUPPORTED;
+  }
+  return CLSM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t clsm_conv_bwd_workspace_bytes(int64_t S, int k, int D, int F) {
+  const int Dpad = (D + 63) / 64 * 64;
+  const size_t part = align_up(static_cast<size_t>(dw_groups(S, Dpad, F)) * F * k * Dpad * 4, 256);
+  const size_t cs = align_up(static_cast<size_t>(kColsumChunks) * F * 4, 256);
+  return part + cs;
+}
+
+int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
+                       const void* Wt, int k, int F, int Fpad,
+                       const float* G, const int32_t* argmax, int ldp, int col0,
+                       float* dW_ref, float* db, float* dX, int first_window,
+                       void* ws, size_t ws_bytes, void* stream) {
+  CLSM_REQUIRE(dtype == CLSM_BF16 || dtype == CLSM_F32, "conv_pool_bwd: bad dtype");
+  CLSM_REQUIRE(S > 0 && L >= k && k >= 1 && k <= 7 && F >= 1 && Fpad >= F, "conv_pool_bwd: bad sizes (k must be 1..7)");
+  CLSM_REQUIRE(Dpad == (D + 63) / 64 * 64 && Dpad <= 512, "conv_pool_bwd: Dpad must be D rounded up to 64 and <= 512");
+  CLSM_REQUIRE(ldp >= col0 + F, "conv_pool_bwd: G row too short");
+  if (ws_bytes < clsm_conv_bwd_workspace_bytes(S, k, D, F)) {
+    clsm_set_error("conv_pool_bwd: workspace too small (%zu < %zu)", ws_bytes, clsm_conv_bwd_workspace_bytes(S, k, D, F));
+    return CLSM_EWORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  const int n_groups = dw_groups(S, Dpad, F);
+  const int64_t spg = ceil_div64(S, n_groups);
+  char* w = static_cast<char*>(ws);
+  float* part = reinterpret_cast<float*>(w);
+  w += align_up(static_cast<size_t>(n_groups) * F * k * Dpad * 4, 256);
+  float* cs = reinterpret_cast<float*>(w);
+
+  dim3 grid(n_groups, Dpad / 64, (F + FT - 1) / FT);
+  int rc = dtype == CLSM_BF16
+      ? launch_dw<__nv_bfloat16>(static_cast<const __nv_bfloat16*>(X), L, Dpad, S, spg, G, argmax, ldp, col0, F, k, part, grid, st)
+      : launch_dw<float>(static_cast<const float*>(X), L, Dpad, S, spg, G, argmax, ldp, col0, F, k, part, grid, st);
+  if (rc != CLSM_OK) { clsm_set_error("conv_pool_bwd: unsupported window %d", k); return rc; }
+  CLSM_LAUNCH_CHECK();
+  const int64_t ne = static_cast<int64_t>(k) * D * F;
+  conv_bwd_dw_reduce_kernel<<<static_cast<unsigned>(ceil_div64(ne, 256)), 256, 0, st>>>(part, n_groups, k, D, Dpad, F, dW_ref);
+  CLSM_LAUNCH_CHECK();
+  if (clsm_colsum(G, S, ldp, col0, F, db, cs, kColsumChunks, st) != CLSM_OK) { clsm_set_error("conv_pool_bwd: colsum launch failed"); return CLSM_ECUDA; }
+
+  const int64_t n_rows = S * L;
+  const unsigned gx = static_cast<unsigned>(ceil_div64(n_rows, 8));
+  if (dtype == CLSM_BF16)
+    conv_bwd_dx_kernel<__nv_bfloat16><<<gx, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(Wt), k, Dpad, n_rows, L, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1);
+  else
+    conv_bwd_dx_kernel<float><<<gx, 256, 0, st>>>(static_cast<const float*>(Wt), k, Dpad, n_rows, L, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+}  // extern "C"

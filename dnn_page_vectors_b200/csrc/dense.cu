@@ -1,0 +1,215 @@
+// Dense semantic projection, forward and backward (CUDA-core fp32 GEMM, 64x64x16 tiles).
+//   replaces Dense(hidden_dims) + Activation('relu'), dssm_cnn_v2/cnn_dssm_tf.py:124-126,
+//   and its gradient.  These GEMMs are <0.2 % of the step's FLOPs.
+#include "common.cuh"
+
+namespace {
+
+constexpr int TM = 64, TN = 64, TK = 16;
+enum { EPI_NONE = 0, EPI_BIAS_ACT = 1, EPI_MUL_ACTGRAD = 2 };
+
+struct GemmP {
+  const float* A; int64_t sam, sak;     // A(m,k) = A[m*sam + k*sak]
+  const float* B; int64_t sbk, sbn;     // B(k,n) = B[k*sbk + n*sbn]
+  float* C; int64_t ldc;                // C(m,n) = C[m*ldc + n]  (split z writes at C + z*M*ldc)
+  int64_t M; int N; int64_t K;
+  int64_t k_per_split;
+  int epi; int act;
+  const float* bias;                    // EPI_BIAS_ACT
+  const float* aux; int64_t ldaux;      // EPI_MUL_ACTGRAD: multiply by act'(aux[m,n])
+};
+
+__global__ void __launch_bounds__(256) gemm_f32_kernel(GemmP p) {
+  __shared__ float As[TK][TM + 4];
+  __shared__ float Bs[TK][TN + 4];
+  const int tid = threadIdx.x;
+  const int64_t m0 = static_cast<int64_t>(blockIdx.x) * TM;
+  const int n0 = blockIdx.y * TN;
+  const int64_t kbeg = static_cast<int64_t>(blockIdx.z) * p.k_per_split;
+  const int64_t kend = (kbeg + p.k_per_split < p.K) ? kbeg + p.k_per_split : p.K;
+  const int ty = tid / 16, tx = tid % 16;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+
+  // loader mappings: pick the one whose fastest thread index walks the contiguous stride
+  const bool a_kfast = (p.sak == 1);
+  const bool b_nfast = (p.sbn == 1);
+  for (int64_t kk = kbeg; kk < kend; kk += TK) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      int m, q;
+      if (a_kfast) { q = tid % 16; m = tid / 16 + e * 16; }
+      else         { m = tid % 64; q = tid / 64 + e * 4; }
+      const int64_t gm = m0 + m, gk = kk + q;
+      As[q][m] = (gm < p.M && gk < kend) ? p.A[gm * p.sam + gk * p.sak] : 0.0f;
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      int n, q;
+      if (b_nfast) { n = tid % 64; q = tid / 64 + e * 4; }
+      else         { q = tid % 16; n = tid / 16 + e * 16; }
+      const int gn = n0 + n; const int64_t gk = kk + q;
+      Bs[q][n] = (gn < p.N && gk < kend) ? p.B[gk * p.sbk + gn * p.sbn] : 0.0f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < TK; ++q) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = As[q][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = Bs[q][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  float* C = p.C + static_cast<int64_t>(blockIdx.z) * p.M * p.ldc;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t m = m0 + ty * 4 + i;
+    if (m >= p.M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n >= p.N) continue;
+      float v = acc[i][j];
+      if (p.epi == EPI_BIAS_ACT) v = act_apply(v + p.bias[n], p.act);
+      else if (p.epi == EPI_MUL_ACTGRAD) v *= act_grad_out(p.aux[m * p.ldaux + n], p.act);
+      C[m * p.ldc + n] = v;
+    }
+  }
+}
+
+// out[i] = sum_z part[z*stride + i], z ascending (deterministic)
+__global__ void reduce_splits_kernel(const float* __restrict__ part, int n_splits, int64_t stride,
+                                     int64_t n, float* __restrict__ out) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float s = 0.0f;
+  for (int z = 0; z < n_splits; ++z) s += part[z * stride + i];
+  out[i] = s;
+}
+
+// dpre = dsem * act'(sem)
+__global__ void dpre_kernel(const float* __restrict__ dsem, const float* __restrict__ sem, int64_t n, int act,
+                            float* __restrict__ dpre) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < n) dpre[i] = dsem[i] * act_grad_out(sem[i], act);
+}
+
+}  // namespace
+
+// column sums of a (rows, ld) matrix over columns [col0, col0+n): two fixed-shape stages.
+// part must hold n_chunks*n floats.  Shared with conv_bwd.cu.
+__global__ void colsum_stage1_kernel(const float* __restrict__ A, int64_t rows, int ld, int col0, int n,
+                                     int64_t rows_per_chunk, float* __restrict__ part) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  const int64_t rb = static_cast<int64_t>(blockIdx.y) * rows_per_chunk;
+  const int64_t re = (rb + rows_per_chunk < rows) ? rb + rows_per_chunk : rows;
+  float s = 0.0f;
+  for (int64_t r = rb; r < re; ++r) s += A[r * ld + col0 + c];
+  part[static_cast<int64_t>(blockIdx.y) * n + c] = s;
+}
+
+int clsm_colsum(const float* A, int64_t rows, int ld, int col0, int n, float* out, float* part,
+                int n_chunks, cudaStream_t st) {
+  const int64_t rpc = ceil_div64(rows, n_chunks);
+  dim3 g1((n + 127) / 128, n_chunks);
+  colsum_stage1_kernel<<<g1, 128, 0, st>>>(A, rows, ld, col0, n, rpc, part);
+  reduce_splits_kernel<<<(n + 255) / 256, 256, 0, st>>>(part, n_chunks, n, n, out);
+  return cudaGetLastError() == cudaSuccess ? CLSM_OK : CLSM_ECUDA;
+}
+
+static int dense_bwd_splits(int64_t S) {
+  int64_t s = S / 512;
+  if (s < 1) s = 1;
+  if (s > 64) s = 64;
+  return static_cast<int>(s);
+}
+static const int kColsumChunks = 64;
+
+extern "C" {
+
+int clsm_dense_fwd(const float* pooled, int64_t S, int P, int ldp, const float* Wd, const float* bd,
+                   int H, int act, float* sem, void* stream) {
+  CLSM_REQUIRE(S >= 0 && P > 0 && H > 0 && ldp >= P, "dense_fwd: bad sizes");
+  if (S == 0) return CLSM_OK;
+  GemmP p{};
+  p.A = pooled; p.sam = ldp; p.sak = 1;
+  p.B = Wd; p.sbk = H; p.sbn = 1;
+  p.C = sem; p.ldc = H; p.M = S; p.N = H; p.K = P; p.k_per_split = P;
+  p.epi = EPI_BIAS_ACT; p.act = act; p.bias = bd;
+  dim3 grid(static_cast<unsigned>(ceil_div64(S, TM)), (H + TN - 1) / TN, 1);
+  gemm_f32_kernel<<<grid, 256, 0, as_stream(stream)>>>(p);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+size_t clsm_dense_bwd_workspace_bytes(int64_t S, int P, int H) {
+  const size_t dpre = align_up(static_cast<size_t>(S) * H * 4, 256);
+  const size_t parts = align_up(static_cast<size_t>(dense_bwd_splits(S)) * P * H * 4, 256);
+  const size_t cs = align_up(static_cast<size_t>(kColsumChunks) * H * 4, 256);
+  return dpre + parts + cs;
+}
+
+int clsm_dense_bwd(const float* pooled, const float* sem, const float* dsem, int64_t S, int P, int ldp,
+                   const float* Wd, int H, int act, float* dWd, float* dbd, float* G,
+                   void* ws, size_t ws_bytes, void* stream) {
+  CLSM_REQUIRE(S > 0 && P > 0 && H > 0 && ldp >= P, "dense_bwd: bad sizes");
+  if (ws_bytes < clsm_dense_bwd_workspace_bytes(S, P, H)) {
+    clsm_set_error("dense_bwd: workspace too small (%zu < %zu)", ws_bytes, clsm_dense_bwd_workspace_bytes(S, P, H));
+    return CLSM_EWORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  char* w = static_cast<char*>(ws);
+  float* dpre = reinterpret_cast<float*>(w);
+  w += align_up(static_cast<size_t>(S) * H * 4, 256);
+  float* parts = reinterpret_cast<float*>(w);
+  const int splits = dense_bwd_splits(S);
+  w += align_up(static_cast<size_t>(splits) * P * H * 4, 256);
+  float* cs = reinterpret_cast<float*>(w);
+
+  const int64_t n = S * H;
+  dpre_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(dsem, sem, n, act, dpre);
+  CLSM_LAUNCH_CHECK();
+  // dbd = colsum(dpre)
+  if (clsm_colsum(dpre, S, H, 0, H, dbd, cs, kColsumChunks, st) != CLSM_OK) { clsm_set_error("dense_bwd: colsum launch failed"); return CLSM_ECUDA; }
+  // dWd (P,H) = pooled^T (P,S) . dpre (S,H), split over S
+  {
+    GemmP p{};
+    p.A = pooled; p.sam = 1; p.sak = ldp;
+    p.B = dpre; p.sbk = H; p.sbn = 1;
+    p.C = (splits > 1) ? parts : dWd; p.ldc = H; p.M = P; p.N = H; p.K = S;
+    p.k_per_split = ceil_div64(ceil_div64(S, splits), TK) * TK;
+    p.epi = EPI_NONE;
+    dim3 grid((P + TM - 1) / TM, (H + TN - 1) / TN, splits);
+    gemm_f32_kernel<<<grid, 256, 0, st>>>(p);
+    CLSM_LAUNCH_CHECK();
+    if (splits > 1) {
+      const int64_t ne = static_cast<int64_t>(P) * H;
+      reduce_splits_kernel<<<static_cast<unsigned>(ceil_div64(ne, 256)), 256, 0, st>>>(parts, splits, ne, ne, dWd);
+      CLSM_LAUNCH_CHECK();
+    }
+  }
+  // G (S, ldp) = (dpre (S,H) . Wd^T (H,P)) * act'(pooled)
+  {
+    GemmP p{};
+    p.A = dpre; p.sam = H; p.sak = 1;
+    p.B = Wd; p.sbk = 1; p.sbn = H;
+    p.C = G; p.ldc = ldp; p.M = S; p.N = P; p.K = H; p.k_per_split = H;
+    p.epi = EPI_MUL_ACTGRAD; p.act = act; p.aux = pooled; p.ldaux = ldp;
+    dim3 grid(static_cast<unsigned>(ceil_div64(S, TM)), (P + TN - 1) / TN, 1);
+    gemm_f32_kernel<<<grid, 256, 0, st>>>(p);
+    CLSM_LAUNCH_CHECK();
+  }
+  return CLSM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,170 @@
+// Embedding gather (+ inverted dropout) and the table format conversions.
+//   replaces Embedding + Dropout of dssm_cnn_v2/cnn_dssm_tf.py:111-122.
+// HBM-bound: one thread moves one 16-column block of one token row with 128-bit loads/stores;
+// consecutive threads take consecutive blocks of the same row, so a warp reads and writes
+// contiguous 512 B (bf16) / 1 KB (fp32) runs.
+#include "common.cuh"
+
+namespace {
+
+// bf16: 16 columns = 2 x uint4.  fp32: 16 columns = 4 x uint4.
+template <bool BF16, bool DROPOUT>
+__global__ void __launch_bounds__(256)
+emb_gather_kernel(const int32_t* __restrict__ tok, int64_t n_tok, const uint4* __restrict__ table,
+                  int in_blocks,          // readable 16-col blocks per table row (ceil(ld_table/16))
+                  int ld_table_v,         // table row pitch in uint4
+                  int in_vec_valid,       // valid uint4 per table row (ld_table*esize/16)
+                  uint4* __restrict__ X, int out_blocks, int ldx_v,
+                  float inv_keep, uint32_t thr, uint64_t seed) {
+  constexpr int VPB = BF16 ? 2 : 4;       // uint4 per 16-column block
+  const int64_t item = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int64_t total = n_tok * out_blocks;
+  if (item >= total) return;
+  const int64_t r = item / out_blocks;
+  const int blk = static_cast<int>(item - r * out_blocks);
+  const int64_t id = __ldg(tok + r);
+  uint4 v[VPB];
+#pragma unroll
+  for (int i = 0; i < VPB; ++i) {
+    const int vi = blk * VPB + i;
+    v[i] = (blk < in_blocks && vi < in_vec_valid) ? __ldg(table + id * ld_table_v + vi)
+                                                  : make_uint4(0u, 0u, 0u, 0u);
+  }
+  if (DROPOUT) {
+    uint32_t bytes[4];
+    dropout_bytes16(seed, static_cast<uint64_t>(r), static_cast<uint32_t>(blk), bytes);
+    if (BF16) {
+      __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(v);
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        float f = __bfloat162float(e[c]);
+        f = dropout_keep(bytes, c, thr) ? f * inv_keep : 0.0f;
+        e[c] = __float2bfloat16_rn(f);
+      }
+    } else {
+      float* e = reinterpret_cast<float*>(v);
+#pragma unroll
+      for (int c = 0; c < 16; ++c) e[c] = dropout_keep(bytes, c, thr) ? e[c] * inv_keep : 0.0f;
+    }
+  }
+  uint4* dst = X + r * ldx_v + blk * VPB;
+#pragma unroll
+  for (int i = 0; i < VPB; ++i) dst[i] = v[i];
+}
+
+__global__ void dropout_mask_kernel(int64_t n_tok, int D, uint32_t thr, uint64_t seed, uint8_t* mask) {
+  const int nblk = (D + 15) / 16;
+  const int64_t item = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (item >= n_tok * nblk) return;
+  const int64_t r = item / nblk;
+  const int blk = static_cast<int>(item - r * nblk);
+  uint32_t bytes[4];
+  dropout_bytes16(seed, static_cast<uint64_t>(r), static_cast<uint32_t>(blk), bytes);
+  for (int c = 0; c < 16; ++c) {
+    const int col = blk * 16 + c;
+    if (col < D) mask[r * D + col] = dropout_keep(bytes, c, thr) ? 1 : 0;
+  }
+}
+
+__global__ void table_to_bf16_kernel(const float* __restrict__ p, int64_t n_rows, int D,
+                                     __nv_bfloat16* __restrict__ out, int ld) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n_rows * ld) return;
+  const int64_t r = i / ld;
+  const int c = static_cast<int>(i - r * ld);
+  out[i] = __float2bfloat16_rn(c < D ? p[r * D + c] : 0.0f);
+}
+
+// Wt[f, j*Dpad + c] = W_ref[j, c, f]
+template <typename T>
+__global__ void pack_conv_w_kernel(const float* __restrict__ W, int k, int D, int F, int Dpad, int Fpad,
+                                   T* __restrict__ Wt) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int64_t K = static_cast<int64_t>(k) * Dpad;
+  if (i >= K * Fpad) return;
+  const int f = static_cast<int>(i / K);
+  const int kk = static_cast<int>(i - f * K);
+  const int j = kk / Dpad, c = kk - j * Dpad;
+  float v = (f < F && c < D) ? W[(static_cast<int64_t>(j) * D + c) * F + f] : 0.0f;
+  if constexpr (sizeof(T) == 2) Wt[i] = __float2bfloat16_rn(v); else Wt[i] = v;
+}
+
+}  // namespace
+
+extern "C" {
+
+int clsm_emb_gather(const int32_t* tok, int64_t n_tok, const void* table, int64_t n_rows,
+                    int D, int ld_table, int dtype, void* X, int ldx,
+                    float keep, uint64_t seed, void* stream) {
+  CLSM_REQUIRE(dtype == CLSM_BF16 || dtype == CLSM_F32, "emb_gather: bad dtype %d", dtype);
+  CLSM_REQUIRE(n_tok >= 0 && n_rows > 0 && D > 0 && ld_table >= D && ldx >= D, "emb_gather: bad sizes");
+  const int es = dtype == CLSM_BF16 ? 2 : 4;
+  CLSM_REQUIRE((ld_table * es) % 16 == 0 && ldx % 16 == 0,
+               "emb_gather: rows must be 16-byte aligned and ldx a multiple of 16 (ld_table=%d ldx=%d)", ld_table, ldx);
+  CLSM_REQUIRE(keep > 0.0f, "emb_gather: keep must be > 0");
+  if (n_tok == 0) return CLSM_OK;
+  const int vec_per_row_in = ld_table * es / 16;
+  const int in_blocks = (ld_table + 15) / 16;
+  const int out_blocks = ldx / 16;
+  const int64_t total = n_tok * out_blocks;
+  const unsigned grid = static_cast<unsigned>(ceil_div64(total, 256));
+  const bool drop = keep < 1.0f;
+  const float inv_keep = 1.0f / keep;
+  const uint32_t thr = keep_threshold(keep);
+  const uint4* t = static_cast<const uint4*>(table);
+  uint4* x = static_cast<uint4*>(X);
+  cudaStream_t st = as_stream(stream);
+  if (dtype == CLSM_BF16) {
+    if (drop) emb_gather_kernel<true, true><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed);
+    else      emb_gather_kernel<true, false><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed);
+  } else {
+    if (drop) emb_gather_kernel<false, true><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed);
+    else      emb_gather_kernel<false, false><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed);
+  }
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+int clsm_emb_gather_h(const int32_t* tok_h, int32_t* tok_d, int64_t n_tok, const void* table,
+                      int64_t n_rows, int D, int ld_table, int dtype, void* X, int ldx,
+                      float keep, uint64_t seed, void* stream) {
+  CLSM_REQUIRE(tok_h != nullptr && tok_d != nullptr, "emb_gather_h: null token buffer");
+  CLSM_CUDA(cudaMemcpyAsync(tok_d, tok_h, static_cast<size_t>(n_tok) * sizeof(int32_t),
+                            cudaMemcpyHostToDevice, as_stream(stream)));
+  return clsm_emb_gather(tok_d, n_tok, table, n_rows, D, ld_table, dtype, X, ldx, keep, seed, stream);
+}
+
+int clsm_dropout_mask(int64_t n_tok, int D, float keep, uint64_t seed, uint8_t* mask, void* stream) {
+  CLSM_REQUIRE(n_tok >= 0 && D > 0 && keep > 0.0f, "dropout_mask: bad arguments");
+  if (n_tok == 0) return CLSM_OK;
+  const int64_t total = n_tok * ((D + 15) / 16);
+  dropout_mask_kernel<<<static_cast<unsigned>(ceil_div64(total, 256)), 256, 0, as_stream(stream)>>>(
+      n_tok, D, keep_threshold(keep), seed, mask);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+int clsm_table_to_bf16(const float* p, int64_t n_rows, int D, void* bf16_copy, int ld_copy, void* stream) {
+  CLSM_REQUIRE(n_rows > 0 && D > 0 && ld_copy >= D, "table_to_bf16: bad sizes");
+  const int64_t total = n_rows * ld_copy;
+  table_to_bf16_kernel<<<static_cast<unsigned>(ceil_div64(total, 256)), 256, 0, as_stream(stream)>>>(
+      p, n_rows, D, static_cast<__nv_bfloat16*>(bf16_copy), ld_copy);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+int clsm_pack_conv_w(const float* W_ref, int k, int D, int F, int Dpad, int Fpad,
+                     int dtype, void* Wt, void* stream) {
+  CLSM_REQUIRE(k > 0 && D > 0 && F > 0 && Dpad >= D && Fpad >= F, "pack_conv_w: bad sizes");
+  const int64_t total = static_cast<int64_t>(k) * Dpad * Fpad;
+  const unsigned grid = static_cast<unsigned>(ceil_div64(total, 256));
+  if (dtype == CLSM_BF16)
+    pack_conv_w_kernel<__nv_bfloat16><<<grid, 256, 0, as_stream(stream)>>>(W_ref, k, D, F, Dpad, Fpad, static_cast<__nv_bfloat16*>(Wt));
+  else if (dtype == CLSM_F32)
+    pack_conv_w_kernel<float><<<grid, 256, 0, as_stream(stream)>>>(W_ref, k, D, F, Dpad, Fpad, static_cast<float*>(Wt));
+  else CLSM_REQUIRE(false, "pack_conv_w: bad dtype %d", dtype);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,269 @@
+// Cosine top-k retrieval over a page-vector corpus.  No script in the reference does this; the
+// score is RTF's cosine (dssm_cnn_v2/cnn_dssm_tf.py:63-77) on already-normalised vectors.
+// Order is total: (score desc, id asc) -- every candidate is a 64-bit key
+//   (ordered(score) << 32) | (0xFFFFFFFF - id32), all keys distinct, larger key = better,
+// so the result does not depend on chunking, on the number of shards or on thread timing.
+// Selection = exact radix select (8 passes of 8 bits) of the k-th largest key among the 2048
+// candidates a CTA holds in registers, then a bitonic sort of the k survivors; levels repeat on
+// the survivors until one list per query is left.
+#include "common.cuh"
+
+namespace {
+
+constexpr int TPB = 256;
+constexpr int KPT = 8;                 // keys per thread
+constexpr int R = TPB * KPT;           // candidates per CTA
+constexpr int QG = 8;                  // queries per CTA at level 0
+constexpr int KMAX = 128;
+
+typedef unsigned long long u64;
+
+__device__ __forceinline__ u64 make_key(float score, uint32_t id) {
+  return (static_cast<u64>(f32_to_ordered(score)) << 32) | static_cast<u64>(0xFFFFFFFFu - id);
+}
+
+// Select the k largest of the CTA's keys (KPT per thread, 0 = empty) and write them sorted
+// descending into s_out[0:k] (zero padded).  Uses s_hist[256], s_ctl[4]; all threads call.
+__device__ void select_topk(const u64 (&keys)[KPT], int k, unsigned* s_hist, unsigned* s_ctl, u64* s_out) {
+  const int tid = threadIdx.x;
+  u64 prefix = 0, mask = 0;
+  unsigned need = static_cast<unsigned>(k);
+  for (int pass = 7; pass >= 0; --pass) {
+    const int shift = pass * 8;
+    s_hist[tid] = 0;                     // TPB == 256 bins
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < KPT; ++i)
+      if ((keys[i] & mask) == prefix) atomicAdd(&s_hist[static_cast<unsigned>(keys[i] >> shift) & 255u], 1u);
+    __syncthreads();
+    if (tid < 32) {
+      // lane l owns bins 255-8l .. 248-8l (descending digit order)
+      unsigned c[8], tot = 0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { c[i] = s_hist[255 - 8 * tid - i]; tot += c[i]; }
+      unsigned incl = tot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const unsigned n = __shfl_up_sync(0xffffffffu, incl, o); if (tid >= o) incl += n; }
+      const unsigned excl = incl - tot;   // count of keys in strictly higher bins
+      const bool mine = excl < need && need <= incl;
+      const unsigned any = __ballot_sync(0xffffffffu, mine);
+      if (any == 0) { if (tid == 0) { s_ctl[0] = 0; s_ctl[1] = need; } }   // fewer than `need` candidates
+      else if (mine) {
+        unsigned run = excl;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (run < need && need <= run + c[i]) { s_ctl[0] = 255 - 8 * tid - i; s_ctl[1] = need - run; }
+          run += c[i];
+        }
+      }
+    }
+    __syncthreads();
+    prefix |= static_cast<u64>(s_ctl[0]) << shift;
+    mask |= static_cast<u64>(0xFF) << shift;
+    need = s_ctl[1];
+  }
+  // prefix is now the k-th largest key (or 0 when there are fewer than k candidates)
+  if (tid < KMAX) s_out[tid] = 0;
+  if (tid == 0) s_ctl[2] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < KPT; ++i) {
+    if (keys[i] != 0 && keys[i] >= prefix) {
+      const unsigned slot = atomicAdd(&s_ctl[2], 1u);
+      if (slot < KMAX) s_out[slot] = keys[i];
+    }
+  }
+  __syncthreads();
+  // bitonic sort of KMAX keys, descending
+  for (int size = 2; size <= KMAX; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      if (tid < KMAX / 2) {
+        const int lo = (tid / stride) * stride * 2 + (tid % stride);
+        const int hi = lo + stride;
+        const bool desc = ((lo & size) == 0);
+        const u64 a = s_out[lo], b = s_out[hi];
+        if ((a < b) == desc) { s_out[lo] = b; s_out[hi] = a; }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// level 0: grid (ceil(nQ/QG), n_chunks).  Each thread scores KPT corpus rows against QG queries.
+__global__ void __launch_bounds__(TPB)
+topk_score_kernel(const float* __restrict__ Qn, int64_t nQ, const float* __restrict__ Cn, int64_t N, int H, int k,
+                  u64* __restrict__ out, int64_t out_stride_q /* = n_chunks*k */) {
+  extern __shared__ __align__(16) float s_q[];              // QG * H
+  __shared__ unsigned s_hist[256];
+  __shared__ unsigned s_ctl[4];
+  __shared__ u64 s_out[KMAX];
+  const int tid = threadIdx.x;
+  const int64_t q0 = static_cast<int64_t>(blockIdx.x) * QG;
+  const int64_t chunk = blockIdx.y;
+  for (int i = tid; i < QG * H; i += TPB) {
+    const int64_t q = q0 + i / H;
+    s_q[i] = q < nQ ? Qn[q * H + (i % H)] : 0.0f;
+  }
+  __syncthreads();
+  float sc[KPT][QG];
+#pragma unroll
+  for (int i = 0; i < KPT; ++i)
+#pragma unroll
+    for (int q = 0; q < QG; ++q) sc[i][q] = 0.0f;
+  const int64_t row0 = chunk * R;
+#pragma unroll
+  for (int i = 0; i < KPT; ++i) {
+    const int64_t row = row0 + tid + i * TPB;
+    if (row < N) {
+      const float4* c4 = reinterpret_cast<const float4*>(Cn + row * H);
+      for (int h = 0; h < H / 4; ++h) {
+        const float4 c = __ldg(c4 + h);
+#pragma unroll
+        for (int q = 0; q < QG; ++q) {
+          const float4 w = *reinterpret_cast<const float4*>(s_q + q * H + h * 4);
+          sc[i][q] = fmaf(c.x, w.x, fmaf(c.y, w.y, fmaf(c.z, w.z, fmaf(c.w, w.w, sc[i][q]))));
+        }
+      }
+    }
+  }
+  for (int q = 0; q < QG; ++q) {
+    if (q0 + q >= nQ) break;
+    u64 keys[KPT];
+#pragma unroll
+    for (int i = 0; i < KPT; ++i) {
+      const int64_t row = row0 + tid + i * TPB;
+      float s = 0.0f;
+#pragma unroll
+      for (int qq = 0; qq < QG; ++qq) if (qq == q) s = sc[i][qq];
+      keys[i] = row < N ? make_key(s, static_cast<uint32_t>(row)) : 0ull;
+    }
+    select_topk(keys, k, s_hist, s_ctl, s_out);
+    if (tid < k) out[(q0 + q) * out_stride_q + chunk * k + tid] = s_out[tid];
+    __syncthreads();
+  }
+}
+
+// level >= 1: grid (nQ, n_chunks); candidates in[q*in_stride + i], i < n_in
+__global__ void __launch_bounds__(TPB)
+topk_merge_kernel(const u64* __restrict__ in, int64_t in_stride, int64_t n_in, int k,
+                  u64* __restrict__ out, int64_t out_stride) {
+  __shared__ unsigned s_hist[256];
+  __shared__ unsigned s_ctl[4];
+  __shared__ u64 s_out[KMAX];
+  const int tid = threadIdx.x;
+  const int64_t q = blockIdx.x, chunk = blockIdx.y;
+  u64 keys[KPT];
+#pragma unroll
+  for (int i = 0; i < KPT; ++i) {
+    const int64_t idx = chunk * R + tid + i * TPB;
+    keys[i] = idx < n_in ? in[q * in_stride + idx] : 0ull;
+  }
+  select_topk(keys, k, s_hist, s_ctl, s_out);
+  if (tid < k) out[q * out_stride + chunk * k + tid] = s_out[tid];
+}
+
+__global__ void topk_decode_kernel(const u64* __restrict__ keys, int64_t n, int64_t id_base,
+                                   float* __restrict__ score, int64_t* __restrict__ id) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const u64 key = keys[i];
+  if (key == 0) { score[i] = -INFINITY; id[i] = -1; return; }
+  score[i] = ordered_to_f32(static_cast<uint32_t>(key >> 32));
+  id[i] = id_base + static_cast<int64_t>(0xFFFFFFFFu - static_cast<uint32_t>(key & 0xFFFFFFFFull));
+}
+
+__global__ void topk_encode_kernel(const float* __restrict__ score, const int64_t* __restrict__ id,
+                                   int n_parts, int64_t nQ, int k, u64* __restrict__ keys) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int64_t n = static_cast<int64_t>(n_parts) * nQ * k;
+  if (i >= n) return;
+  const int64_t part = i / (nQ * k);
+  const int64_t rem = i - part * nQ * k;
+  const int64_t q = rem / k;
+  const int j = static_cast<int>(rem - q * k);
+  const int64_t idv = id[i];
+  keys[q * (static_cast<int64_t>(n_parts) * k) + part * k + j] =
+      idv < 0 ? 0ull : make_key(score[i], static_cast<uint32_t>(idv));
+}
+
+// runs merge levels on keys (nQ, n_in) in buf[src] until one list of k per query is left;
+// returns the buffer index that holds (nQ, k).
+int run_merge_levels(u64* buf[2], int src, int64_t nQ, int64_t n_in, int k, cudaStream_t st) {
+  while (true) {
+    const int64_t n_chunks = ceil_div64(n_in, R);
+    const int dst = src ^ 1;
+    dim3 grid(static_cast<unsigned>(nQ), static_cast<unsigned>(n_chunks));
+    topk_merge_kernel<<<grid, TPB, 0, st>>>(buf[src], n_in, n_in, k, buf[dst], n_chunks * k);
+    src = dst;
+    n_in = n_chunks * k;
+    if (n_chunks == 1) break;
+  }
+  return src;
+}
+
+size_t level_bytes(int64_t nQ, int64_t n_lists, int k) { return align_up(static_cast<size_t>(nQ) * n_lists * k * 8, 256); }
+
+}  // namespace
+
+extern "C" {
+
+size_t clsm_cos_topk_workspace_bytes(int64_t nQ, int64_t N, int k) {
+  const int64_t c0 = ceil_div64(N, R);
+  const int64_t c1 = ceil_div64(c0 * k, R);
+  return level_bytes(nQ, c0, k) + level_bytes(nQ, c1 > 1 ? c1 : 1, k);
+}
+
+int clsm_cos_topk(const float* Qn, int64_t nQ, const float* Cn, int64_t N, int H, int k,
+                  int64_t id_base, float* out_score, int64_t* out_id,
+                  void* ws, size_t ws_bytes, void* stream) {
+  CLSM_REQUIRE(nQ > 0 && N > 0 && N < (1ll << 32) && H > 0 && H % 4 == 0, "cos_topk: bad sizes (H must be a multiple of 4)");
+  CLSM_REQUIRE(k >= 1 && k <= KMAX, "cos_topk: k must be in [1, %d]", KMAX);
+  CLSM_REQUIRE(static_cast<size_t>(QG) * H * 4 <= 40 * 1024, "cos_topk: H too large");
+  if (ws_bytes < clsm_cos_topk_workspace_bytes(nQ, N, k)) {
+    clsm_set_error("cos_topk: workspace too small (%zu < %zu)", ws_bytes, clsm_cos_topk_workspace_bytes(nQ, N, k));
+    return CLSM_EWORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  const int64_t c0 = ceil_div64(N, R);
+  u64* buf[2];
+  buf[0] = static_cast<u64*>(ws);
+  buf[1] = reinterpret_cast<u64*>(static_cast<char*>(ws) + level_bytes(nQ, c0, k));
+  dim3 grid(static_cast<unsigned>(ceil_div64(nQ, QG)), static_cast<unsigned>(c0));
+  topk_score_kernel<<<grid, TPB, static_cast<size_t>(QG) * H * 4, st>>>(Qn, nQ, Cn, N, H, k, buf[0], c0 * k);
+  CLSM_LAUNCH_CHECK();
+  int src = 0;
+  if (c0 > 1) { src = run_merge_levels(buf, 0, nQ, c0 * k, k, st); CLSM_LAUNCH_CHECK(); }
+  const int64_t n = nQ * k;
+  topk_decode_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(buf[src], n, id_base, out_score, out_id);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+size_t clsm_topk_merge_workspace_bytes(int n_parts, int64_t nQ, int k) {
+  const int64_t c1 = ceil_div64(static_cast<int64_t>(n_parts) * k, R);
+  return level_bytes(nQ, n_parts, k) + level_bytes(nQ, c1 > 1 ? c1 : 1, k);
+}
+
+int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_t nQ, int k,
+                    float* out_score, int64_t* out_id, void* ws, size_t ws_bytes, void* stream) {
+  CLSM_REQUIRE(n_parts >= 1 && nQ > 0 && k >= 1 && k <= KMAX, "topk_merge: bad sizes");
+  if (ws_bytes < clsm_topk_merge_workspace_bytes(n_parts, nQ, k)) {
+    clsm_set_error("topk_merge: workspace too small");
+    return CLSM_EWORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  u64* buf[2];
+  buf[0] = static_cast<u64*>(ws);
+  buf[1] = reinterpret_cast<u64*>(static_cast<char*>(ws) + level_bytes(nQ, n_parts, k));
+  const int64_t n_in = static_cast<int64_t>(n_parts) * nQ * k;
+  topk_encode_kernel<<<static_cast<unsigned>(ceil_div64(n_in, 256)), 256, 0, st>>>(scores, ids, n_parts, nQ, k, buf[0]);
+  CLSM_LAUNCH_CHECK();
+  const int src = run_merge_levels(buf, 0, nQ, static_cast<int64_t>(n_parts) * k, k, st);
+  CLSM_LAUNCH_CHECK();
+  const int64_t n = nQ * k;
+  topk_decode_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(buf[src], n, 0, out_score, out_id);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+}  // extern "C"

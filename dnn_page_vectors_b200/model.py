@@ -1,0 +1,549 @@
+"""CLSM two-tower model: build / train / predict entry points over libclsm_b200.
+
+Mirrors the model-level surface of the reference scripts (dssm_cnn_v2/cnn_dssm_tf.py):
+
+  model(sequence_length)            -> a tower (Embedding -> Dropout -> {Conv1D -> max-pool}_k ->
+                                       concat -> Dense -> act), :81-127            -> ``CLSM.model``
+  RTF(vects)                        -> clipped cosine, :63-77                       -> ``RTF``
+  Model(inputs, prob).compile(...)  -> :178-182                                     -> ``CLSM.compile``
+  fit_generator / save / save_weights / to_json -> :189-206                         -> same names
+  (added, absent in the reference)  predict, encode_pages, topk
+
+PyTorch is used for device memory, streams and (in parallel.py) NCCL only.  Every arithmetic
+step is a call into the C ABI (include/clsm_b200.h) on raw device pointers; there is no torch
+fallback for any of them.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import math
+import time
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import ACT, BF16, F32, IMPL, call, lib
+from .config import ModelParams
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _round_up(x, m):
+    return (x + m - 1) // m * m
+
+
+class Tower(object):
+    """Device-resident parameters and optimizer state of one tower (query or document).
+
+    Reference weight shapes are kept for the master copies (so they can be exchanged with a
+    Keras checkpoint): table (V+1, D); conv kernel (k, D, F) [Keras (k,1,D,F)]; conv bias (F,);
+    dense (|K|F, H); dense bias (H,).  All small tensors live in ONE flat fp32 buffer (p/m/v/g) so
+    the optimizer and the data-parallel allreduce are one call each.
+    """
+
+    def __init__(self, net, sequence_length, table):
+        p = net.params
+        dev = net.device
+        self.net = net
+        self.L = int(sequence_length)
+        self.V1, self.D = int(table.shape[0]), int(table.shape[1])
+        assert self.D == p.embedding_dim
+        self.Dpad = _round_up(self.D, 64)
+        self.windows = tuple(int(k) for k in p.filter_sizes)
+        self.F = int(p.num_filters)
+        self.Fpad = _round_up(self.F, 16)
+        self.P = len(self.windows) * self.F
+        self.H = int(p.hidden_dims)
+        if self.L < max(self.windows):
+            raise ValueError("sequence_length %d shorter than the widest window %d" % (self.L, max(self.windows)))
+        self.bf16 = p.precision == "bf16"
+        self.dtype_code = BF16 if self.bf16 else F32
+        self.cdtype = torch.bfloat16 if self.bf16 else torch.float32
+
+        # --- embedding table: master fp32 (V1, D) + Adam state, bf16 compute copy (V1, Dpad)
+        self.E = torch.as_tensor(np.ascontiguousarray(table, dtype=np.float32)).to(dev)
+        self.E_m = torch.zeros_like(self.E)
+        self.E_v = torch.zeros_like(self.E)
+        self.E_c = torch.zeros((self.V1, self.Dpad), dtype=torch.bfloat16, device=dev) if self.bf16 else None
+
+        # --- flat buffer of the small tensors
+        sizes = [k * self.D * self.F for k in self.windows] + [self.P, self.P * self.H, self.H]
+        offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+        self.n_small = int(offs[-1])
+        self.flat = torch.zeros(self.n_small, dtype=torch.float32, device=dev)
+        self.flat_m = torch.zeros_like(self.flat)
+        self.flat_v = torch.zeros_like(self.flat)
+        self.flat_g = torch.zeros_like(self.flat)
+        nw = len(self.windows)
+
+        def views(buf):
+            cw = [buf[offs[i]:offs[i + 1]].view(k, self.D, self.F) for i, k in enumerate(self.windows)]
+            cb = buf[offs[nw]:offs[nw + 1]]
+            wd = buf[offs[nw + 1]:offs[nw + 2]].view(self.P, self.H)
+            bd = buf[offs[nw + 2]:offs[nw + 3]]
+            return cw, cb, wd, bd
+
+        self.convW, self.convb, self.Wd, self.bd = views(self.flat)
+        self.g_convW, self.g_convb, self.g_Wd, self.g_bd = views(self.flat_g)
+        # compute-layout conv weights Wt (Fpad, k*Dpad)
+        self.Wt = [torch.zeros((self.Fpad, k * self.Dpad), dtype=self.cdtype, device=dev) for k in self.windows]
+        self._bufs = {}
+        self._init_small(net.rng)
+        self.refresh_compute_copies(table_too=True)
+
+    # ---- initialisation: Keras-1 defaults (Convolution1D 'uniform' +-0.05, Dense glorot_uniform)
+    def _init_small(self, rng):
+        for w in self.convW:
+            w.copy_(torch.as_tensor(rng.uniform(-0.05, 0.05, size=tuple(w.shape)).astype(np.float32)))
+        lim = math.sqrt(6.0 / (self.P + self.H))
+        self.Wd.copy_(torch.as_tensor(rng.uniform(-lim, lim, size=(self.P, self.H)).astype(np.float32)))
+
+    def refresh_compute_copies(self, table_too=False):
+        st = _stream()
+        for w, wt, k in zip(self.convW, self.Wt, self.windows):
+            call("clsm_pack_conv_w", _ptr(w), k, self.D, self.F, self.Dpad, self.Fpad, self.dtype_code, _ptr(wt), st)
+        if table_too and self.bf16:
+            call("clsm_table_to_bf16", _ptr(self.E), self.V1, self.D, _ptr(self.E_c), self.Dpad, st)
+
+    # ---- numpy import/export in reference layouts
+    def get_weights(self):
+        out = {"E": self.E.cpu().numpy()}
+        for i, w in enumerate(self.convW):
+            out["convW%d" % i] = w.cpu().numpy().copy()
+            out["convb%d" % i] = self.convb[i * self.F:(i + 1) * self.F].cpu().numpy().copy()
+        out["Wd"] = self.Wd.cpu().numpy().copy()
+        out["bd"] = self.bd.cpu().numpy().copy()
+        return out
+
+    def set_weights(self, w, theano_kernels=False):
+        """theano_kernels: conv kernels trained under Keras-Theano are applied flipped along the
+        window axis (filter_flip=True); flip them once on import."""
+        self.E.copy_(torch.as_tensor(np.asarray(w["E"], dtype=np.float32)))
+        for i, cw in enumerate(self.convW):
+            a = np.asarray(w["convW%d" % i], dtype=np.float32)
+            if a.ndim == 4:                       # Keras (k, 1, D, F)
+                a = a[:, 0]
+            if theano_kernels:
+                a = a[::-1].copy()
+            cw.copy_(torch.as_tensor(np.ascontiguousarray(a)))
+            self.convb[i * self.F:(i + 1) * self.F].copy_(torch.as_tensor(np.asarray(w["convb%d" % i], dtype=np.float32)))
+        self.Wd.copy_(torch.as_tensor(np.asarray(w["Wd"], dtype=np.float32)))
+        self.bd.copy_(torch.as_tensor(np.asarray(w["bd"], dtype=np.float32)))
+        self.refresh_compute_copies(table_too=True)
+
+    def state(self):
+        return {"E": self.E, "E_m": self.E_m, "E_v": self.E_v,
+                "flat": self.flat, "flat_m": self.flat_m, "flat_v": self.flat_v}
+
+    # ---- per-shape scratch (allocated once per (S, train) and reused)
+    def buffers(self, S, train):
+        key = (int(S), bool(train))
+        b = self._bufs.get(key)
+        if b is not None:
+            return b
+        dev = self.net.device
+        n_tok = S * self.L
+        b = {"S": S, "n_tok": n_tok}
+        b["tok"] = torch.empty((S, self.L), dtype=torch.int32, device=dev)
+        b["X"] = torch.zeros((n_tok + 8, self.Dpad), dtype=self.cdtype, device=dev)
+        b["keys"] = torch.empty((S, self.P), dtype=torch.int64, device=dev)
+        b["pooled"] = torch.empty((S, self.P), dtype=torch.float32, device=dev)
+        b["argmax"] = torch.empty((S, self.P), dtype=torch.int32, device=dev)
+        b["sem"] = torch.empty((S, self.H), dtype=torch.float32, device=dev)
+        if train:
+            b["dsem"] = torch.empty((S, self.H), dtype=torch.float32, device=dev)
+            b["G"] = torch.empty((S, self.P), dtype=torch.float32, device=dev)
+            b["dX"] = torch.empty((n_tok, self.Dpad), dtype=torch.float32, device=dev)
+            max_u = min(n_tok, self.V1)
+            b["uniq"] = torch.empty(n_tok, dtype=torch.int32, device=dev)
+            b["n_uniq"] = torch.zeros(1, dtype=torch.int32, device=dev)
+            b["dE_rows"] = torch.empty((max_u, self.Dpad), dtype=torch.float32, device=dev)
+            b["row_of_id"] = torch.empty(self.V1, dtype=torch.int32, device=dev)
+            ws = max(
+                lib.clsm_dense_bwd_workspace_bytes(S, self.P, self.H),
+                max(lib.clsm_conv_bwd_workspace_bytes(S, k, self.D, self.F) for k in self.windows),
+                lib.clsm_emb_scatter_workspace_bytes(n_tok, self.D))
+            b["ws"] = torch.empty(ws, dtype=torch.uint8, device=dev)
+            b["ws_bytes"] = ws
+        self._bufs[key] = b
+        return b
+
+    # ---- forward: tok already in b['tok']
+    def forward(self, b, train, seed=0):
+        net = self.net
+        st = _stream()
+        S, n_tok = b["S"], b["n_tok"]
+        keep = 1.0 - net.params.dropout_prob[0] if train else 1.0
+        table = self.E_c if self.bf16 else self.E
+        ld_table = self.Dpad if self.bf16 else self.D
+        call("clsm_emb_gather", _ptr(b["tok"]), n_tok, _ptr(table), self.V1, self.D, ld_table,
+             self.dtype_code, _ptr(b["X"]), self.Dpad, keep, seed, st)
+        for i, k in enumerate(self.windows):
+            call("clsm_conv_pool_fwd", _ptr(b["X"]), self.dtype_code, S, self.L, self.Dpad, _ptr(self.Wt[i]),
+                 k, self.F, self.Fpad, _ptr(b["keys"]), self.P, i * self.F, IMPL[net.conv_impl], st)
+        call("clsm_pool_finalize", _ptr(b["keys"]), S, self.P, self.P, _ptr(self.convb), ACT[net.params.activation],
+             _ptr(b["pooled"]), _ptr(b["argmax"]), self.P, st)
+        call("clsm_dense_fwd", _ptr(b["pooled"]), S, self.P, self.P, _ptr(self.Wd), _ptr(self.bd), self.H,
+             ACT[net.params.activation], _ptr(b["sem"]), st)
+        b["keep"], b["seed"] = keep, seed
+        return b["sem"]
+
+    # ---- backward: gradient of the loss wrt sem in b['dsem']; fills flat_g and the sparse table grad
+    def backward(self, b):
+        net = self.net
+        st = _stream()
+        S, n_tok = b["S"], b["n_tok"]
+        act = ACT[net.params.activation]
+        call("clsm_dense_bwd", _ptr(b["pooled"]), _ptr(b["sem"]), _ptr(b["dsem"]), S, self.P, self.P, _ptr(self.Wd),
+             self.H, act, _ptr(self.g_Wd), _ptr(self.g_bd), _ptr(b["G"]), _ptr(b["ws"]), b["ws_bytes"], st)
+        for i, k in enumerate(self.windows):
+            gb = self.g_convb[i * self.F:(i + 1) * self.F]
+            call("clsm_conv_pool_bwd", _ptr(b["X"]), self.dtype_code, S, self.L, self.D, self.Dpad, _ptr(self.Wt[i]),
+                 k, self.F, self.Fpad, _ptr(b["G"]), _ptr(b["argmax"]), self.P, i * self.F,
+                 _ptr(self.g_convW[i]), _ptr(gb), _ptr(b["dX"]), 1 if i == 0 else 0,
+                 _ptr(b["ws"]), b["ws_bytes"], st)
+        call("clsm_emb_scatter", _ptr(b["tok"]), n_tok, _ptr(b["dX"]), self.Dpad, self.D, b["keep"], b["seed"],
+             self.V1, _ptr(b["uniq"]), _ptr(b["n_uniq"]), _ptr(b["dE_rows"]), _ptr(b["row_of_id"]),
+             _ptr(b["ws"]), b["ws_bytes"], st)
+
+    def adam(self, b, step, sparse_grad=None):
+        """sparse_grad: optional (row_of_id, dE_rows, uniq, n_uniq) replacing this rank's own
+        (the data-parallel path passes the globally reduced gradient)."""
+        p = self.net.params
+        st = _stream()
+        call("clsm_adam_dense", _ptr(self.flat), _ptr(self.flat_m), _ptr(self.flat_v), _ptr(self.flat_g),
+             self.n_small, step, p.lr, p.beta_1, p.beta_2, p.epsilon, st)
+        row_of_id, dE_rows, uniq, n_uniq = sparse_grad if sparse_grad is not None else (
+            b["row_of_id"], b["dE_rows"], b["uniq"], b["n_uniq"])
+        if self.net.lazy_table_adam:
+            call("clsm_adam_rows", _ptr(self.E), _ptr(self.E_m), _ptr(self.E_v), self.D, _ptr(uniq), _ptr(n_uniq),
+                 dE_rows.shape[0], _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
+                 _ptr(self.E_c), self.Dpad, st)
+        else:
+            call("clsm_adam_table", _ptr(self.E), _ptr(self.E_m), _ptr(self.E_v), self.V1, self.D, _ptr(row_of_id),
+                 _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon, _ptr(self.E_c), self.Dpad, st)
+        self.refresh_compute_copies(table_too=False)
+
+    # ---- Keras-like predict on a tower: tokens (N, L) -> semantic vectors (N, H) numpy
+    def predict(self, tokens, batch_size=4096):
+        tokens = np.ascontiguousarray(tokens, dtype=np.int32)
+        out = np.empty((tokens.shape[0], self.H), dtype=np.float32)
+        for s in range(0, tokens.shape[0], batch_size):
+            chunk = tokens[s:s + batch_size]
+            b = self.buffers(chunk.shape[0], False)
+            b["tok"].copy_(torch.as_tensor(chunk))
+            out[s:s + chunk.shape[0]] = self.forward(b, False).cpu().numpy()
+        return out
+
+
+def RTF(vects):
+    """Clipped cosine of two (B, H) arrays, dssm_cnn_v2/cnn_dssm_tf.py:63-77, on the GPU.
+    Returns (B, 1) float32 like the reference's Lambda layer."""
+    x, y = (np.ascontiguousarray(v, dtype=np.float32) for v in vects)
+    B, H = x.shape
+    dev = torch.device("cuda", torch.cuda.current_device())
+    xq, yd = torch.as_tensor(x).to(dev), torch.as_tensor(y).to(dev)
+    cosv = torch.empty((B, 1), dtype=torch.float32, device=dev)
+    prob = torch.empty((B, 1), dtype=torch.float32, device=dev)
+    la = torch.empty(2, dtype=torch.float32, device=dev)
+    call("clsm_sim_loss", _ptr(xq), _ptr(yd), B, 0, H, 1.0, B, _ptr(cosv), _ptr(prob), _ptr(la),
+         C.c_void_p(0), C.c_void_p(0), _stream())
+    return cosv.cpu().numpy()
+
+
+class History(object):
+    def __init__(self):
+        self.history = {"loss": [], "acc": [], "val_loss": [], "val_acc": []}
+
+
+class CLSM(object):
+    """The compiled two-tower model of cnn_dssm_tf.py:130-182.
+
+    query_length / document_length / num_negative_examples come from a Configuration
+    (config.py:76-91); embedding weights from DataHelpers.get_vocab_index_embedding_weights
+    (one table per tower, each initialised from the same matrix, cnn_dssm_tf.py:111-116,135-137)
+    or, for char/ngram levels, random uniform +-0.05 (cnn_dssm_th.py:121-126).
+    """
+
+    def __init__(self, params=None, query_length=20, document_length=975, embedding_weights=None,
+                 vocab_size=None, device=None, conv_impl="auto", lazy_table_adam=False):
+        if not torch.cuda.is_available():
+            raise RuntimeError("dnn_page_vectors_b200 needs a CUDA device (sm_100a); there is no CPU path")
+        self.params = params if params is not None else ModelParams()
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        torch.cuda.set_device(self.device)
+        self.conv_impl = conv_impl
+        self.lazy_table_adam = lazy_table_adam
+        self.rng = np.random.RandomState(self.params.seed)
+        self.query_length, self.document_length = int(query_length), int(document_length)
+        self.J = int(self.params.J)
+        if embedding_weights is None or len(embedding_weights) == 0:
+            if vocab_size is None:
+                raise ValueError("pass embedding_weights (word level) or vocab_size (char/ngram level)")
+            embedding_weights = self.rng.uniform(-0.05, 0.05, size=(vocab_size, self.params.embedding_dim))
+        self.embedding_weights = np.asarray(embedding_weights)
+        self.query_model = self.model(self.query_length)
+        self.doc_model = self.model(self.document_length)
+        self.iterations = 0
+        self.compiled = False
+        self.dp = None                 # set by parallel.DataParallel
+        self._head = {}
+        self._pinned = {}
+
+    # cnn_dssm_tf.py:81-127
+    def model(self, sequence_length=None):
+        return Tower(self, sequence_length, self.embedding_weights)
+
+    # cnn_dssm_tf.py:182
+    def compile(self, optimizer="adam", loss="binary_crossentropy", metrics=("accuracy",)):
+        if optimizer != "adam" or loss != "binary_crossentropy":
+            raise ValueError("only optimizer='adam', loss='binary_crossentropy' (the reference's choice) exist")
+        self.compiled = True
+        return self
+
+    # ---- batch staging: [q, pos, neg_0..neg_{J-1}] (host, any int dtype) -> device int32
+    def _stage(self, x, train):
+        if len(x) != 2 + self.J:
+            raise ValueError("expected %d input arrays [query, pos_doc, %d neg_docs], got %d" % (2 + self.J, self.J, len(x)))
+        B = int(np.asarray(x[0]).shape[0])
+        key = (B, train)
+        pin = self._pinned.get(key)
+        if pin is None:
+            pin = (torch.empty((B, self.query_length), dtype=torch.int32).pin_memory(),
+                   torch.empty((B, 1 + self.J, self.document_length), dtype=torch.int32).pin_memory())
+            self._pinned[key] = pin
+        pq, pdoc = pin
+        pq.numpy()[...] = x[0]
+        dn = pdoc.numpy()
+        for j in range(1 + self.J):
+            dn[:, j, :] = x[1 + j]
+        bq = self.query_model.buffers(B, train)
+        bd = self.doc_model.buffers(B * (1 + self.J), train)
+        bq["tok"].copy_(pq, non_blocking=True)
+        bd["tok"].view(B, 1 + self.J, self.document_length).copy_(pdoc, non_blocking=True)
+        return B, bq, bd
+
+    def _head_bufs(self, B):
+        h = self._head.get(B)
+        if h is None:
+            dev = self.device
+            h = {"cos": torch.empty((B, 1 + self.J), dtype=torch.float32, device=dev),
+                 "prob": torch.empty((B, 1 + self.J), dtype=torch.float32, device=dev),
+                 "loss_acc": torch.empty(2, dtype=torch.float32, device=dev)}
+            self._head[B] = h
+        return h
+
+    def _forward_head(self, B, bq, bd, train, batch_total=None):
+        h = self._head_bufs(B)
+        call("clsm_sim_loss", _ptr(bq["sem"]), _ptr(bd["sem"]), B, self.J, self.query_model.H,
+             float(self.params.GAMMA), int(batch_total or B), _ptr(h["cos"]), _ptr(h["prob"]), _ptr(h["loss_acc"]),
+             _ptr(bq["dsem"]) if train else C.c_void_p(0), _ptr(bd["dsem"]) if train else C.c_void_p(0), _stream())
+        return h
+
+    def _seeds(self):
+        base = (self.params.seed << 20) + self.iterations * 2
+        rank = self.dp.rank if self.dp is not None else 0
+        return base + (rank << 44), base + 1 + (rank << 44)
+
+    # ---- device-resident step (bench `value`): tokens already staged in the tower buffers
+    def step_resident(self, B, bq, bd):
+        sq, sd = self._seeds()
+        self.query_model.forward(bq, True, sq)
+        self.doc_model.forward(bd, True, sd)
+        bt = B * (self.dp.world if self.dp is not None else 1)
+        h = self._forward_head(B, bq, bd, True, bt)
+        self.query_model.backward(bq)
+        self.doc_model.backward(bd)
+        self.iterations += 1
+        if self.dp is not None:
+            gq, gd = self.dp.exchange(self, bq, bd)
+            self.query_model.adam(bq, self.iterations, gq)
+            self.doc_model.adam(bd, self.iterations, gd)
+        else:
+            self.query_model.adam(bq, self.iterations)
+            self.doc_model.adam(bd, self.iterations)
+        return h
+
+    # ---- Keras-like batch API (host numpy in, python floats out)
+    def train_on_batch(self, x, y=None):
+        B, bq, bd = self._stage(x, True)
+        if B == 0:
+            return [0.0, 0.0]
+        h = self.step_resident(B, bq, bd)
+        la = h["loss_acc"].cpu().numpy()
+        return [float(la[0]), float(la[1])]
+
+    def test_on_batch(self, x, y=None):
+        B, bq, bd = self._stage(x, False)
+        self.query_model.forward(bq, False)
+        self.doc_model.forward(bd, False)
+        la = self._forward_head(B, bq, bd, False)["loss_acc"].cpu().numpy()
+        return [float(la[0]), float(la[1])]
+
+    def predict_on_batch(self, x):
+        B, bq, bd = self._stage(x, False)
+        self.query_model.forward(bq, False)
+        self.doc_model.forward(bd, False)
+        return self._forward_head(B, bq, bd, False)["prob"][:, :1].cpu().numpy()
+
+    predict = predict_on_batch
+
+    # cnn_dssm_tf.py:194
+    def fit_generator(self, generator, samples_per_epoch, nb_epoch, validation_data=None,
+                      nb_val_samples=None, callbacks=None, verbose=1):
+        if not self.compiled:
+            raise RuntimeError("compile() the model first")
+        hist = History()
+        callbacks = list(callbacks or [])
+        for epoch in range(nb_epoch):
+            seen, lsum, asum, t0 = 0, 0.0, 0.0, time.time()
+            while seen < samples_per_epoch:
+                x, y = next(generator)
+                n = len(y)
+                if n == 0:
+                    continue
+                l, a = self.train_on_batch(x, y)
+                lsum += l * n
+                asum += a * n
+                seen += n
+            logs = {"loss": lsum / max(seen, 1), "acc": asum / max(seen, 1)}
+            if validation_data is not None:
+                vseen, vl, va = 0, 0.0, 0.0
+                while vseen < (nb_val_samples or 0):
+                    x, y = next(validation_data)
+                    n = len(y)
+                    if n == 0:
+                        continue
+                    l, a = self.test_on_batch(x, y)
+                    vl += l * n
+                    va += a * n
+                    vseen += n
+                logs["val_loss"] = vl / max(vseen, 1)
+                logs["val_acc"] = va / max(vseen, 1)
+            for k, v in logs.items():
+                hist.history[k].append(v)
+            if verbose:
+                print("Epoch %d/%d - %.1fs - %s" % (epoch + 1, nb_epoch, time.time() - t0,
+                      " - ".join("%s: %.4f" % kv for kv in sorted(logs.items()))))
+            for cb in callbacks:
+                cb(self, epoch, logs)
+        return hist
+
+    # ---- page vectors and retrieval (absent in the reference; composition of model() and RTF)
+    def encode_pages(self, tokens, batch_size=8192, out=None, normalise=True):
+        """tokens (N, Ld) host ints -> device tensor (N, H) fp32 of L2-normalised page vectors."""
+        tokens = np.ascontiguousarray(tokens, dtype=np.int32)
+        return self._encode(self.doc_model, tokens, batch_size, out, normalise)
+
+    def encode_queries(self, tokens, batch_size=8192, normalise=True):
+        tokens = np.ascontiguousarray(tokens, dtype=np.int32)
+        return self._encode(self.query_model, tokens, batch_size, None, normalise)
+
+    def _encode(self, tower, tokens, batch_size, out, normalise):
+        N = tokens.shape[0]
+        if out is None:
+            out = torch.empty((N, tower.H), dtype=torch.float32, device=self.device)
+        for s in range(0, N, batch_size):
+            chunk = tokens[s:s + batch_size]
+            b = tower.buffers(chunk.shape[0], False)
+            b["tok"].copy_(torch.as_tensor(chunk), non_blocking=False)
+            self.encode_resident(tower, b, out[s:s + chunk.shape[0]], normalise)
+        return out
+
+    def encode_resident(self, tower, b, out, normalise=True):
+        sem = tower.forward(b, False)
+        if normalise:
+            call("clsm_normalize_rows", _ptr(sem), b["S"], tower.H, _ptr(out), _stream())
+        else:
+            out.copy_(sem)
+        return out
+
+    def topk(self, query_vecs, corpus_vecs, k=100, id_base=0):
+        """query_vecs (Q, H), corpus_vecs (N, H): normalised fp32 DEVICE tensors.
+        Returns (scores (Q, k) fp32, ids (Q, k) int64) device tensors, order (score desc, id asc)."""
+        Q, H = query_vecs.shape
+        N = corpus_vecs.shape[0]
+        k = int(k)
+        ws_bytes = lib.clsm_cos_topk_workspace_bytes(Q, N, k)
+        ws = self._scratch("topk", ws_bytes)
+        sc = torch.empty((Q, k), dtype=torch.float32, device=self.device)
+        ids = torch.empty((Q, k), dtype=torch.int64, device=self.device)
+        call("clsm_cos_topk", _ptr(query_vecs), Q, _ptr(corpus_vecs), N, H, k, int(id_base), _ptr(sc), _ptr(ids),
+             _ptr(ws), ws_bytes, _stream())
+        return sc, ids
+
+    def topk_merge(self, scores, ids):
+        """scores/ids (n_parts, Q, k) device tensors -> merged (Q, k)."""
+        n_parts, Q, k = scores.shape
+        ws_bytes = lib.clsm_topk_merge_workspace_bytes(n_parts, Q, k)
+        ws = self._scratch("merge", ws_bytes)
+        sc = torch.empty((Q, k), dtype=torch.float32, device=self.device)
+        out = torch.empty((Q, k), dtype=torch.int64, device=self.device)
+        call("clsm_topk_merge", _ptr(scores.contiguous()), _ptr(ids.contiguous()), n_parts, Q, k, _ptr(sc), _ptr(out),
+             _ptr(ws), ws_bytes, _stream())
+        return sc, out
+
+    def _scratch(self, name, nbytes):
+        t = self._head.get(("ws", name))
+        if t is None or t.numel() < nbytes:
+            t = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=self.device)
+            self._head[("ws", name)] = t
+        return t
+
+    # ---- persistence (cnn_dssm_tf.py:193,199-206).  h5py is not available here, so the on-disk
+    # format is a torch file holding the same tensors in the reference's layouts.
+    def to_json(self):
+        return json.dumps({"class_name": "CLSM", "config": dict(self.params.to_dict(),
+                           query_length=self.query_length, document_length=self.document_length,
+                           vocab_rows=int(self.embedding_weights.shape[0]))})
+
+    def get_weights(self):
+        return {"query": self.query_model.get_weights(), "doc": self.doc_model.get_weights()}
+
+    def set_weights(self, w, theano_kernels=False):
+        self.query_model.set_weights(w["query"], theano_kernels)
+        self.doc_model.set_weights(w["doc"], theano_kernels)
+
+    def save_weights(self, path):
+        torch.save({"weights": self.get_weights()}, path)
+
+    def load_weights(self, path, theano_kernels=False):
+        self.set_weights(torch.load(path, weights_only=False)["weights"], theano_kernels)
+
+    def save(self, path):
+        """Whole model: architecture JSON, weights, optimizer state and step (resume-able,
+        which the reference's save is not)."""
+        st = {"json": self.to_json(), "iterations": self.iterations,
+              "query": {k: v.cpu() for k, v in self.query_model.state().items()},
+              "doc": {k: v.cpu() for k, v in self.doc_model.state().items()}}
+        torch.save(st, path)
+
+    def load(self, path):
+        st = torch.load(path, weights_only=False)
+        self.iterations = int(st["iterations"])
+        for tower, key in ((self.query_model, "query"), (self.doc_model, "doc")):
+            for name, t in tower.state().items():
+                t.copy_(st[key][name])
+            tower.refresh_compute_copies(table_too=True)
+        return self
+
+
+class ModelCheckpoint(object):
+    """callbacks.ModelCheckpoint(filepath) of cnn_dssm_tf.py:193: saves weights each epoch."""
+
+    def __init__(self, filepath, verbose=0):
+        self.filepath, self.verbose = filepath, verbose
+
+    def __call__(self, model, epoch, logs):
+        path = self.filepath.format(epoch=epoch, **logs)
+        model.save_weights(path)
+        if self.verbose:
+            print("Epoch %05d: saving model to %s" % (epoch, path))

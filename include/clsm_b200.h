@@ -1,0 +1,176 @@
+/* clsm_b200.h -- C ABI of libclsm_b200.so: the CLSM (convolutional DSSM) hot path of
+ * collawolley/dnn_page_vectors `dssm_cnn_v2`, as hand-written sm_100a CUDA kernels.
+ *
+ * The reference has no FFI of its own: the path is Python that calls Keras-1 layers
+ * (dssm_cnn_v2/cnn_dssm_tf.py).  Each entry point below therefore cites the reference
+ * LAYER CALL it replaces (file:line under /root/reference).  The Python host package
+ * `dnn_page_vectors_b200` binds exactly these symbols through ctypes; INTEGRATION.md
+ * shows the stub.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless the name ends in `_h`;
+ *  - every call is asynchronous on `stream` (a cudaStream_t passed as void*), takes no
+ *    lock and keeps no global state except the last-error string (thread local);
+ *  - the library allocates nothing: scratch is a caller-provided workspace whose size
+ *    comes from the matching *_workspace_bytes() query;
+ *  - return value: 0 = CLSM_OK, negative = error (see clsm_last_error()).
+ *  - row-major everywhere; `ld*` are leading dimensions in ELEMENTS.
+ */
+#ifndef CLSM_B200_H_
+#define CLSM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { CLSM_OK = 0, CLSM_EINVAL = -1, CLSM_ECUDA = -2, CLSM_EWORKSPACE = -3, CLSM_EUNSUPPORTED = -4 };
+enum { CLSM_F32 = 0, CLSM_BF16 = 1 };
+enum { CLSM_ACT_LINEAR = 0, CLSM_ACT_RELU = 1, CLSM_ACT_TANH = 2 };
+/* conv_pool_fwd implementation selector */
+enum { CLSM_IMPL_AUTO = 0, CLSM_IMPL_SIMT = 1, CLSM_IMPL_TCGEN05 = 2 };
+
+int clsm_version(void);
+const char* clsm_last_error(void);
+/* number of SMs of the current device (grid sizing is done inside the library) */
+int clsm_num_sms(void);
+
+/* ---- embedding gather (+ optional inverted dropout) ------------------------------------
+ * replaces Embedding(...)            dssm_cnn_v2/cnn_dssm_tf.py:111-116
+ *      and Dropout(dropout_prob[0])  dssm_cnn_v2/cnn_dssm_tf.py:117-122
+ * X[r, 0:D] = table[tok[r], 0:D] * mask(r, c) / keep ; X[r, D:ldx] = 0.
+ * keep >= 1 disables dropout.  mask(r, c) is a counter-based Bernoulli(keep) bit that is a
+ * pure function of (seed, r, c) -- clsm_dropout_mask exports it for the oracle.
+ * dtype: CLSM_BF16 (table and X bf16) or CLSM_F32 (both fp32).  Rows must be 16-byte aligned
+ * (ld_table*esize and ldx*esize multiples of 16).  Returns CLSM_EINVAL for a token id outside
+ * [0, n_rows) only in debug builds; ids are trusted otherwise, as Keras trusts them. */
+int clsm_emb_gather(const int32_t* tok, int64_t n_tok, const void* table, int64_t n_rows,
+                    int D, int ld_table, int dtype, void* X, int ldx,
+                    float keep, uint64_t seed, void* stream);
+int clsm_dropout_mask(int64_t n_tok, int D, float keep, uint64_t seed, uint8_t* mask, void* stream);
+
+/* ---- conv weights: reference layout -> compute layout ------------------------------------
+ * W_ref fp32 (k, D, F)  [Keras-1 Convolution1D kernel (k,1,D,F), cnn_dssm_tf.py:85-91]
+ * Wt   dtype (Fpad, k*Dpad): Wt[f, j*Dpad + c] = W_ref[j, c, f], zero elsewhere. */
+int clsm_pack_conv_w(const float* W_ref, int k, int D, int F, int Dpad, int Fpad,
+                     int dtype, void* Wt, void* stream);
+
+/* ---- n-gram window convolution + max over time ---------------------------------------
+ * replaces Convolution1D(valid) + MaxPooling1D(L-k+1) + Flatten
+ *          dssm_cnn_v2/cnn_dssm_tf.py:84-100
+ * X (S*L, ldx) as written by clsm_emb_gather (it must own at least 8 readable rows past the
+ * end for the tensor-core path; the gather's callers allocate S*L+8).  Wt as packed above.
+ * keys (S, ldk) uint64, column f of this window at keys[s, col0 + f]: on return
+ *   keys = (orderable(max_t acc[s,t,f]) << 32) | (0xFFFFFFFF - argmax_t), ties -> lowest t,
+ * where acc is the fp32 accumulator before bias/activation (max commutes with both).
+ * The call clears its key columns itself.  impl: CLSM_IMPL_*; TCGEN05 needs dtype BF16,
+ * Dpad % 64 == 0 and Fpad % 16 == 0, Fpad <= 512. */
+int clsm_conv_pool_fwd(const void* X, int dtype, int64_t S, int L, int Dpad,
+                       const void* Wt, int k, int F, int Fpad,
+                       uint64_t* keys, int ldk, int col0, int impl, void* stream);
+
+/* keys -> pooled = act(max + bias) fp32 (S, ldp), argmax int32 (S, ldp) (may be NULL).
+ * For relu a column with pooled == 0 reports argmax 0 (all positions tie at 0 after the
+ * activation).  replaces the activation of Convolution1D + concat, cnn_dssm_tf.py:88,102-107 */
+int clsm_pool_finalize(const uint64_t* keys, int64_t S, int P, int ldk, const float* bias,
+                       int act, float* pooled, int32_t* argmax, int ldp, void* stream);
+
+/* ---- dense semantic projection ----------------------------------------------------------
+ * replaces Dense(hidden_dims) + Activation('relu')   cnn_dssm_tf.py:124-126
+ * sem (S, H) = act(pooled (S, P) . Wd (P, H) + bd). */
+int clsm_dense_fwd(const float* pooled, int64_t S, int P, int ldp, const float* Wd, const float* bd,
+                   int H, int act, float* sem, void* stream);
+
+/* dense backward.  dpre = dsem * act'(sem);  dWd = pooled^T dpre;  dbd = colsum(dpre);
+ * G (S, ldp) = (dpre . Wd^T) * act'(pooled)   (gradient arriving at the pooled maxima).
+ * accumulate != 0 adds into dWd/dbd (the doc tower is applied 1+J times with shared weights,
+ * cnn_dssm_tf.py:137-152; here that is one batched call, so accumulate is normally 0). */
+size_t clsm_dense_bwd_workspace_bytes(int64_t S, int P, int H);
+int clsm_dense_bwd(const float* pooled, const float* sem, const float* dsem, int64_t S, int P, int ldp,
+                   const float* Wd, int H, int act, float* dWd, float* dbd, float* G,
+                   void* ws, size_t ws_bytes, void* stream);
+
+/* ---- cosine / gamma-softmax / loss, forward + gradient in one pass --------------------------
+ * replaces RTF (cnn_dssm_tf.py:63-77), x*GAMMA, exp, p0 = e0/sum (:164-176),
+ *          binary_crossentropy + accuracy (:182).
+ * semQ (B, H); semD (B*(1+J), H), document row b*(1+J)+j, j = 0 the positive.
+ * out: cosv, prob (B, 1+J); loss_acc[0] = mean_b -log clip(p0), [1] = mean_b (p0 > 0.5)
+ * (means over B; gradients scaled by 1/batch_total so data-parallel ranks pass the global
+ * batch);  dSemQ (B, H), dSemD (B*(1+J), H) may be NULL for evaluation. */
+int clsm_sim_loss(const float* semQ, const float* semD, int64_t B, int J, int H, float gamma,
+                  int64_t batch_total, float* cosv, float* prob, float* loss_acc,
+                  float* dSemQ, float* dSemD, void* stream);
+
+/* ---- conv backward (arg-max sparse) -------------------------------------------------------
+ * gradient of Convolution1D + global max-pool: only the arg-max window of each (s, f) gets
+ * gradient.  G, argmax (S, ldp) at columns [col0, col0+F).  X, Wt as in the forward.
+ *   dW_ref (k, D, F) fp32 = sum_s G[s,f] X[s, a+j, c];  db (F) = sum_s G[s,f]
+ *   dX (S*L, Dpad) fp32 += / = sum_{f,j: a+j==t} G[s,f] W[j,c,f]
+ * first_window != 0 overwrites dX, otherwise accumulates (several window sizes). */
+size_t clsm_conv_bwd_workspace_bytes(int64_t S, int k, int D, int F);
+int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
+                       const void* Wt, int k, int F, int Fpad,
+                       const float* G, const int32_t* argmax, int ldp, int col0,
+                       float* dW_ref, float* db, float* dX, int first_window,
+                       void* ws, size_t ws_bytes, void* stream);
+
+/* ---- embedding gradient: deterministic sort + segmented reduce -------------------------------
+ * replaces the gradient of Embedding (AdvancedIncSubtensor1 / UnsortedSegmentSum).
+ * dX (n_tok, Dpad) fp32; if keep < 1 the dropout mask of the forward is re-applied.
+ * out: n_uniq_out[0] = number of distinct ids; uniq_ids[0:n_uniq]; dE_rows (n_uniq, Dpad) fp32 =
+ * sum over the tokens with that id, added in ascending token position, independent of the
+ * grid -- the same input gives the same bits on every run and every GPU.
+ * row_of_id (n_rows) int32: -1, or the row of dE_rows holding that id's gradient (for Adam). */
+size_t clsm_emb_scatter_workspace_bytes(int64_t n_tok, int D);
+int clsm_emb_scatter(const int32_t* tok, int64_t n_tok, const float* dX, int Dpad, int D,
+                     float keep, uint64_t seed, int64_t n_rows,
+                     int32_t* uniq_ids, int32_t* n_uniq_out, float* dE_rows, int32_t* row_of_id,
+                     void* ws, size_t ws_bytes, void* stream);
+
+/* ---- optimizer -----------------------------------------------------------------------------
+ * replaces optimizer="adam" (Keras-1 Adam, cnn_dssm_tf.py:182):
+ *   t = step (1-based); lr_t = lr sqrt(1-b2^t)/(1-b1^t); m = b1 m + (1-b1) g;
+ *   v = b2 v + (1-b2) g^2; p -= lr_t m / (sqrt(v) + eps).
+ * clsm_adam_dense: flat tensors.  clsm_adam_table: the (n_rows, D) embedding table with its
+ * gradient given row-sparsely (row_of_id / dE_rows (n_uniq, ldg) from clsm_emb_scatter); EVERY row is
+ * updated (rows without gradient use g = 0), which is what Keras does.  bf16_copy (n_rows,
+ * ld_copy) is refreshed in the same pass when not NULL. */
+int clsm_adam_dense(float* p, float* m, float* v, const float* g, int64_t n, int step,
+                    float lr, float b1, float b2, float eps, void* stream);
+int clsm_adam_table(float* p, float* m, float* v, int64_t n_rows, int D,
+                    const int32_t* row_of_id, const float* dE_rows, int ldg, int step,
+                    float lr, float b1, float b2, float eps,
+                    void* bf16_copy, int ld_copy, void* stream);
+/* lazy (row-sparse) Adam: only rows in uniq_ids move.  NOT the reference's semantics. */
+int clsm_adam_rows(float* p, float* m, float* v, int D, const int32_t* uniq_ids,
+                   const int32_t* n_uniq, int64_t max_uniq, const float* dE_rows, int ldg, int step,
+                   float lr, float b1, float b2, float eps, void* bf16_copy, int ld_copy, void* stream);
+/* fp32 (n_rows, D) -> bf16 (n_rows, ld_copy) with zero pad columns */
+int clsm_table_to_bf16(const float* p, int64_t n_rows, int D, void* bf16_copy, int ld_copy, void* stream);
+
+/* ---- page vectors + retrieval (no script in the reference; composition of model() and RTF) ---
+ * clsm_normalize_rows: vec (N, H) = sem / sqrt(max(|sem|^2, FLT_MIN))   (RTF's norm, :63-72)
+ * clsm_cos_topk: scores = Qn . Cn^T over corpus rows [0, N), top-k per query ordered by
+ *   (score desc, id asc); ids are id_base + row.  out_score (nQ, k) fp32, out_id (nQ, k) int64.
+ * clsm_topk_merge: merge n_parts lists (n_parts, nQ, k) -> (nQ, k), same order. */
+int clsm_normalize_rows(const float* sem, int64_t N, int H, float* vec, void* stream);
+size_t clsm_cos_topk_workspace_bytes(int64_t nQ, int64_t N, int k);
+int clsm_cos_topk(const float* Qn, int64_t nQ, const float* Cn, int64_t N, int H, int k,
+                  int64_t id_base, float* out_score, int64_t* out_id,
+                  void* ws, size_t ws_bytes, void* stream);
+size_t clsm_topk_merge_workspace_bytes(int n_parts, int64_t nQ, int k);
+int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_t nQ, int k,
+                    float* out_score, int64_t* out_id, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- host-buffer convenience (the e2e / drop-in call): ids on the HOST ------------------------
+ * Copies tok_h (pinned or pageable) to tok_d on `stream`, then clsm_emb_gather. */
+int clsm_emb_gather_h(const int32_t* tok_h, int32_t* tok_d, int64_t n_tok, const void* table,
+                      int64_t n_rows, int D, int ld_table, int dtype, void* X, int ldx,
+                      float keep, uint64_t seed, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CLSM_B200_H_ */
