@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py -- CLSM training throughput (train pairs/s) on BASELINE.json configs[1]:
+bf16 CLSM, D=300 w2v, window 3, 300 filters, 128-d semantic, J=4, 20-token query / 100-token page,
+batch 4096 per GPU, 1M-word embedding table, dense Keras Adam.  One pair = 1 query + 1 positive +
+J negatives through forward, loss, backward and the optimizer step.
+
+  python bench.py [--gpus N --steps K --warmup W]          our arm (one process per GPU under torchrun)
+  python bench.py --impl reference [...]                   CPU arm: torch-CPU port of the reference graph
+
+Prints ONE JSON line (rank 0).  Extra keys beyond the contract: roofline, cpu_baseline, kernels
+(per-phase device times of one instrumented step), encode / topk (page-encode and retrieval rates).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFG2 = dict(V=1_000_000, D=300, windows=(3,), F=300, H=128, J=4, Lq=20, Ld=100, B=4096, act="tanh")
+WORKLOAD = "cfg2: CLSM bf16 train step, B=4096/GPU, J=4, Lq=20, Ld=100, D=300, window 3, F=300, H=128, V=1M, dense Adam"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return {"hbm": p["hbm_gbs"], "tf_burst": p["bf16_tflops"], "tf_sust": p.get("bf16_tflops_sustained", p["bf16_tflops"]),
+                "src": "measured"}
+    except Exception:
+        return {"hbm": 6650.0, "tf_burst": 1590.0, "tf_sust": 1400.0, "src": "fallback"}
+
+
+def flops_pair_fwd(c):
+    def seq(L):
+        return sum(2 * (L - k + 1) * k * c["D"] * c["F"] for k in c["windows"]) + 2 * len(c["windows"]) * c["F"] * c["H"]
+    return seq(c["Lq"]) + (1 + c["J"]) * seq(c["Ld"])
+
+
+def zipf_tokens(rng, V, n, L, s=1.07):
+    """Zipf(s) ids over [0, V), true length ~ U[L/4, L], right-padded with PAD id V-1."""
+    ranks = np.arange(1, V + 1, dtype=np.float64)
+    cdf = np.cumsum(ranks ** (-s))
+    cdf /= cdf[-1]
+    tok = np.searchsorted(cdf, rng.random_sample((n, L))).astype(np.int32)
+    lens = rng.randint(max(L // 4, 1), L + 1, size=n)
+    tok[np.arange(L)[None, :] >= lens[:, None]] = V - 1
+    return tok
+
+
+def make_batches(c, n_batches, seed):
+    rng = np.random.RandomState(seed)
+    out = []
+    for _ in range(n_batches):
+        q = zipf_tokens(rng, c["V"], c["B"], c["Lq"])
+        docs = [zipf_tokens(rng, c["V"], c["B"], c["Ld"]) for _ in range(1 + c["J"])]
+        out.append([q] + docs)
+    return out
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks + throttle reasons every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+                for n, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------ reference arm
+def run_reference(args, rank, world):
+    if rank != 0:
+        return 0
+    from oracle import torch_cpu_port as CP
+    c = dict(CFG2)
+    Bs = 64                                   # bounded sample of the cfg2 workload per step
+    steps, warmup = max(args.steps, 1), max(args.warmup, 1)
+    steps = min(steps, 5)
+    pps, threads, dt = CP.time_train(c, Bs, steps, min(warmup, 2))
+    line = {
+        "impl": "reference", "metric": "train_pairs_per_s", "value": pps, "unit": "pairs/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": min(warmup, 2), "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": "batch %d per step (same shapes, uniform ids)" % Bs},
+        "cpu_baseline": {"value": pps, "unit": "pairs/s", "cores": threads, "kind": "port",
+                         "sample": "torch-CPU fp32 port of the reference graph, B=%d per step, %d steps" % (Bs, steps)},
+        "e2e": {"value": pps, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference stack (Keras 1.0.x / Theano 0.8 / TF 0.x, Python 2) not installable here; oracle port timed",
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------ our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=CFG2["B"])
+    ap.add_argument("--vocab", type=int, default=CFG2["V"])
+    ap.add_argument("--conv-impl", default="auto")
+    ap.add_argument("--lazy-adam", action="store_true", help="row-sparse table Adam (NOT the reference's semantics)")
+    ap.add_argument("--no-extras", action="store_true", help="skip cpu_baseline / encode / topk / breakdown")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from dnn_page_vectors_b200 import CLSM, ModelParams
+    from dnn_page_vectors_b200._lib import lib
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    warmup = max(args.warmup, 3)
+    steps = max(args.steps, 1)
+    c = dict(CFG2, B=args.batch, V=args.vocab)
+    mp = ModelParams(embedding_dim=c["D"], batch_size=c["B"], filter_sizes=c["windows"], num_filters=c["F"],
+                     hidden_dims=c["H"], J=c["J"], dropout_prob=(0.25, 0.5), activation=c["act"], precision="bf16")
+    rng = np.random.RandomState(1337)
+    table = rng.uniform(-0.25, 0.25, size=(c["V"] + 1, c["D"])).astype(np.float32)   # data_helpers.py:62
+    table[-1] = 0.0
+    net = CLSM(mp, c["Lq"], c["Ld"], embedding_weights=table, device="cuda:%d" % local_rank,
+               conv_impl=args.conv_impl, lazy_table_adam=args.lazy_adam).compile()
+    del table
+    if world > 1:
+        from dnn_page_vectors_b200.parallel import DataParallel
+        DataParallel(net)
+    batches = make_batches(c, 4, 1337 + rank)
+    B = c["B"]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: tokens resident in HBM before the timed region
+    bq = net.query_model.buffers(B, True)
+    bd = net.doc_model.buffers(B * (1 + c["J"]), True)
+    dev_batches = []
+    for x in batches:
+        q = torch.as_tensor(x[0]).cuda()
+        d = torch.as_tensor(np.stack(x[1:], axis=1)).cuda().view(B * (1 + c["J"]), c["Ld"])
+        dev_batches.append((q, d))
+
+    def resident_step(i):
+        q, d = dev_batches[i % len(dev_batches)]
+        bq["tok"].copy_(q)
+        bd["tok"].copy_(d)
+        return net.step_resident(B, bq, bd)
+
+    for i in range(warmup):
+        resident_step(i)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = lib.clsm_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        h = resident_step(i)
+    e1.record()
+    barrier()
+    launches = int(lib.clsm_launch_count() - l0)
+    ms = e0.elapsed_time(e1)
+    # ---- e2e: host numpy batches through the public API (train_on_batch), loss read back each step
+    for i in range(2):
+        net.train_on_batch(batches[i % len(batches)])
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    last = None
+    for i in range(steps):
+        last = net.train_on_batch(batches[i % len(batches)])
+    e3.record()
+    barrier()
+    ms_e2e = e2.elapsed_time(e3)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    pairs = B * world * steps
+    value = pairs / (ms * 1e-3)
+    e2e_value = pairs / (ms_e2e * 1e-3)
+    tok_bytes = 4 * B * (c["Lq"] + (1 + c["J"]) * c["Ld"])
+
+    line = {
+        "metric": "train_pairs_per_s", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": steps,
+        "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "global_batch": B * world, "activation": c["act"], "dropout": 0.25,
+                   "table_adam": "lazy-rows" if args.lazy_adam else "dense (Keras semantics)",
+                   "conv_impl": args.conv_impl, "parallelism": "dp%d" % world,
+                   "l2": "inputs larger than L2: each step streams both 1M x 300 tables and their Adam state (14 GB)",
+                   "tokens": "Zipf(1.07) ids, true length U[L/4,L], right-padded with one PAD id"},
+        "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": tok_bytes, "d2h_bytes_per_step": 8,
+                "ms_per_step": ms_e2e / steps, "loss": last[0] if last else None},
+        "gpu_launches": launches,
+        "clocks": clocks,
+    }
+
+    if rank == 0 and not args.no_extras:
+        pk = peaks()
+        # ---- per-phase device times of instrumented steps (events between C-ABI calls)
+        phases = profile_phases(net, B, bq, bd, resident_step, torch)
+        line["kernels"] = phases
+        fwd = flops_pair_fwd(c) * B
+        conv_flops = sum(2 * (L - k + 1) * k * c["D"] * c["F"] * n for k in c["windows"]
+                         for L, n in ((c["Lq"], B), (c["Ld"], B * (1 + c["J"]))))
+        n_table = 2 * (c["V"] + 1) * c["D"]
+        cand = {
+            "conv_pool_fwd": ("tensor", conv_flops / 1e12, phases.get("conv_pool_fwd_ms", 0), pk["tf_sust"], "TFLOP/s"),
+            "adam_table": ("hbm", 24.0 * n_table / 1e9, phases.get("adam_table_ms", 0), pk["hbm"], "GB/s"),
+        }
+        top = max(cand, key=lambda k: cand[k][2])
+        bound, work, tms, peak, unit = cand[top]
+        ach = work / (tms * 1e-3) if tms > 0 else 0.0
+        line["roofline"] = {"kernel": top, "bound": bound, "achieved": ach, "peak": peak, "unit": unit,
+                            "frac": ach / peak if peak else None, "traffic": None, "peak_source": pk["src"],
+                            "algorithmic_work_per_launch": work}
+        line["roofline_all"] = {k: {"bound": v[0], "achieved": (v[1] / (v[2] * 1e-3) if v[2] > 0 else 0.0),
+                                    "peak": v[3], "unit": v[4]} for k, v in cand.items()}
+        line["train_flops_per_pair_3x"] = 3 * flops_pair_fwd(c)
+        line["model_tflops_3x"] = 3 * fwd * (steps / (ms * 1e-3)) / 1e12
+        try:
+            line["encode"], line["topk"] = bench_inference(net, c, torch, pk)
+        except Exception as e:          # keep the headline line even if the extra leg fails
+            line["encode"] = {"error": repr(e)}
+        try:
+            from oracle import torch_cpu_port as CP
+            Bs = 64
+            pps, threads, dt = CP.time_train(dict(c), Bs, 3, 1)
+            line["cpu_baseline"] = {"value": pps, "unit": "pairs/s", "cores": threads, "kind": "port",
+                                    "sample": "torch-CPU fp32 port of the reference graph, cfg2 shapes, B=%d per step, 3 steps" % Bs}
+        except Exception as e:
+            line["cpu_baseline"] = {"value": None, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": "failed: %r" % (e,)}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def profile_phases(net, B, bq, bd, resident_step, torch):
+    """Device time of each C-ABI call class over 3 instrumented steps (median)."""
+    from dnn_page_vectors_b200 import _lib
+    import dnn_page_vectors_b200.model as M
+    import dnn_page_vectors_b200.parallel  # noqa: F401
+    orig = _lib.call
+    rec = []
+
+    def timed(name, *a):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        r = orig(name, *a)
+        e.record()
+        rec.append((name, s, e))
+        return r
+    out = {}
+    M.call = timed
+    try:
+        runs = []
+        for i in range(3):
+            rec.clear()
+            resident_step(i)
+            torch.cuda.synchronize()
+            agg = {}
+            for name, s, e in rec:
+                agg[name] = agg.get(name, 0.0) + s.elapsed_time(e)
+            runs.append(agg)
+        for name in runs[0]:
+            out[name.replace("clsm_", "") + "_ms"] = float(np.median([r.get(name, 0.0) for r in runs]))
+    finally:
+        M.call = orig
+    return out
+
+
+def bench_inference(net, c, torch, pk):
+    """Page-encode rate (pages/s) and retrieval rate (queries/s) on one GPU shard."""
+    rng = np.random.RandomState(7)
+    NB = 16384
+    pages = torch.as_tensor(zipf_tokens(rng, c["V"], NB, c["Ld"])).cuda()
+    b = net.doc_model.buffers(NB, False)
+    out = torch.empty((NB, c["H"]), dtype=torch.float32, device="cuda")
+    b["tok"].copy_(pages)
+    for _ in range(3):
+        net.encode_resident(net.doc_model, b, out)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 10
+    e0.record()
+    for _ in range(reps):
+        net.encode_resident(net.doc_model, b, out)
+    e1.record()
+    torch.cuda.synchronize()
+    enc_ms = e0.elapsed_time(e1) / reps
+    enc = {"value": NB / (enc_ms * 1e-3), "unit": "pages/s", "pages_per_call": NB, "ms_per_call": enc_ms}
+    # retrieval: 128 queries over a 1M-page shard of random unit vectors
+    N, Q, k = 1_000_000, 128, 100
+    g = torch.Generator(device="cuda").manual_seed(3)
+    corpus = torch.nn.functional.normalize(torch.randn((N, c["H"]), generator=g, device="cuda"), dim=1)
+    qv = torch.nn.functional.normalize(torch.randn((Q, c["H"]), generator=g, device="cuda"), dim=1)
+    for _ in range(2):
+        net.topk(qv, corpus, k=k)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        net.topk(qv, corpus, k=k)
+    e1.record()
+    torch.cuda.synchronize()
+    tk_ms = e0.elapsed_time(e1) / 5
+    scan_bytes = N * c["H"] * 4
+    tk = {"value": Q / (tk_ms * 1e-3), "unit": "queries/s", "corpus_rows": N, "queries_per_call": Q, "k": k,
+          "ms_per_call": tk_ms, "hbm_frac_of_one_scan": (scan_bytes / 1e9) / (tk_ms * 1e-3) / pk["hbm"]}
+    return enc, tk
+
+
+if __name__ == "__main__":
+    sys.exit(main())

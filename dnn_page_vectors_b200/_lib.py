@@ -24,6 +24,7 @@ SIGNATURES = {
     "clsm_version": (i32, []),
     "clsm_last_error": (C.c_char_p, []),
     "clsm_num_sms": (i32, []),
+    "clsm_launch_count": (C.c_ulonglong, []),
     "clsm_emb_gather": (i32, [vp, i64, vp, i64, i32, i32, i32, vp, i32, f32, u64, vp]),
     "clsm_emb_gather_h": (i32, [vp, vp, i64, vp, i64, i32, i32, i32, vp, i32, f32, u64, vp]),
     "clsm_dropout_mask": (i32, [i64, i32, f32, u64, vp, vp]),

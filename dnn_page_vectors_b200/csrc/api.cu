@@ -4,6 +4,7 @@
 #include <string.h>
 
 static thread_local char g_err[512] = "";
+unsigned long long g_clsm_launches = 0;
 
 void clsm_set_error(const char* fmt, ...) {
   va_list ap;
@@ -28,4 +29,5 @@ extern "C" {
 int clsm_version(void) { return 100; }
 const char* clsm_last_error(void) { return g_err; }
 int clsm_num_sms(void) { return clsm_sm_count(); }
+unsigned long long clsm_launch_count(void) { return g_clsm_launches; }
 }

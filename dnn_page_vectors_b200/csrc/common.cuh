@@ -28,7 +28,12 @@ void clsm_set_error(const char* fmt, ...);
     }                                                                             \
   } while (0)
 
-#define CLSM_LAUNCH_CHECK() CLSM_CUDA(cudaGetLastError())
+extern unsigned long long g_clsm_launches;      // kernels of this library launched so far (api.cu)
+#define CLSM_LAUNCH_CHECK()            \
+  do {                                 \
+    ++g_clsm_launches;                 \
+    CLSM_CUDA(cudaGetLastError());     \
+  } while (0)
 
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -124,6 +124,7 @@ int clsm_colsum(const float* A, int64_t rows, int ld, int col0, int n, float* ou
   dim3 g1((n + 127) / 128, n_chunks);
   colsum_stage1_kernel<<<g1, 128, 0, st>>>(A, rows, ld, col0, n, rpc, part);
   reduce_splits_kernel<<<(n + 255) / 256, 256, 0, st>>>(part, n_chunks, n, n, out);
+  g_clsm_launches += 2;
   return cudaGetLastError() == cudaSuccess ? CLSM_OK : CLSM_ECUDA;
 }
 

@@ -194,6 +194,7 @@ int run_merge_levels(u64* buf[2], int src, int64_t nQ, int64_t n_in, int k, cuda
     const int dst = src ^ 1;
     dim3 grid(static_cast<unsigned>(nQ), static_cast<unsigned>(n_chunks));
     topk_merge_kernel<<<grid, TPB, 0, st>>>(buf[src], n_in, n_in, k, buf[dst], n_chunks * k);
+    ++g_clsm_launches;
     src = dst;
     n_in = n_chunks * k;
     if (n_chunks == 1) break;
@@ -232,7 +233,7 @@ int clsm_cos_topk(const float* Qn, int64_t nQ, const float* Cn, int64_t N, int H
   topk_score_kernel<<<grid, TPB, static_cast<size_t>(QG) * H * 4, st>>>(Qn, nQ, Cn, N, H, k, buf[0], c0 * k);
   CLSM_LAUNCH_CHECK();
   int src = 0;
-  if (c0 > 1) { src = run_merge_levels(buf, 0, nQ, c0 * k, k, st); CLSM_LAUNCH_CHECK(); }
+  if (c0 > 1) { src = run_merge_levels(buf, 0, nQ, c0 * k, k, st); CLSM_CUDA(cudaGetLastError()); }
   const int64_t n = nQ * k;
   topk_decode_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(buf[src], n, id_base, out_score, out_id);
   CLSM_LAUNCH_CHECK();

@@ -36,6 +36,8 @@ int clsm_version(void);
 const char* clsm_last_error(void);
 /* number of SMs of the current device (grid sizing is done inside the library) */
 int clsm_num_sms(void);
+/* kernels of this library launched by this process so far (bench.py's gpu_launches) */
+unsigned long long clsm_launch_count(void);
 
 /* ---- embedding gather (+ optional inverted dropout) ------------------------------------
  * replaces Embedding(...)            dssm_cnn_v2/cnn_dssm_tf.py:111-116

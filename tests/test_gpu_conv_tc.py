@@ -1,0 +1,52 @@
+"""tcgen05/TMEM/TMA convolution + max-pool kernel against the oracle and the CUDA-core kernel
+(-m gpu).  Exact-arithmetic inputs (multiples of 1/8) make every partial sum representable, so
+values AND arg-max positions must match bit for bit whatever the accumulation order."""
+import numpy as np
+import pytest
+import torch
+
+from tests.gpu_util import bf16_round
+from tests.test_gpu_kernels import conv_case, oracle_conv, run_conv
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(3, 9, 10, 2, 5), (5, 20, 100, 3, 150), (2, 100, 300, 3, 300), (40, 100, 300, 3, 300),
+          (64, 20, 100, 4, 150), (3, 1000, 64, 5, 256), (300, 7, 64, 1, 16), (11, 33, 128, 7, 500),
+          (1, 128, 64, 3, 32), (2, 129, 64, 2, 48), (37, 975, 100, 3, 150)]
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "S%d-L%d-D%d-k%d-F%d" % s)
+def test_tc_exact_arithmetic_bit_exact(shape):
+    S, L, D, k, F = shape
+    X, W = conv_case(20, S, L, D, k, F, exact=True)
+    mx, am, _ = run_conv(X, W, True, "tcgen05")
+    omx, oam, _ = oracle_conv(X, W)
+    np.testing.assert_array_equal(mx, omx.astype(np.float32))
+    np.testing.assert_array_equal(am, oam)
+
+
+@pytest.mark.parametrize("shape", [(6, 100, 300, 3, 300), (33, 20, 300, 3, 300), (9, 60, 100, 4, 150)])
+def test_tc_random_matches_simt_and_oracle(shape):
+    S, L, D, k, F = shape
+    X, W = conv_case(21, S, L, D, k, F, exact=False)
+    X[2, L // 2:] = X[2, L // 2]                 # right padding -> exact ties
+    X[3, :] = X[3, 0]
+    X, W = bf16_round(X).astype(np.float64), bf16_round(W).astype(np.float64)
+    mx, am, _ = run_conv(X, W, True, "tcgen05")
+    smx, sam, _ = run_conv(X, W, True, "simt")
+    omx, oam, Y = oracle_conv(X, W)
+    np.testing.assert_allclose(mx, omx, rtol=1e-4, atol=1e-5)       # fp32 accumulate of exact bf16 products
+    np.testing.assert_allclose(mx, smx, rtol=1e-4, atol=1e-5)
+    assert (am[3] == 0).all()
+    for s, f in np.argwhere(am != oam):
+        assert abs(Y[s, am[s, f], f] - Y[s, oam[s, f], f]) < 1e-4
+
+
+def test_tc_is_default_for_bf16_and_rejects_fp32():
+    from dnn_page_vectors_b200 import _lib
+    X, W = conv_case(22, 4, 30, 64, 3, 32, exact=True)
+    a = run_conv(X, W, True, "auto")
+    b = run_conv(X, W, True, "tcgen05")
+    assert torch.equal(a[2], b[2])
+    with pytest.raises(_lib.ClsmError):
+        run_conv(X, W, False, "tcgen05")

@@ -1,0 +1,429 @@
+"""Per-kernel parity on the GPU, through the C ABI, against the CPU oracle (-m gpu)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import clsm_oracle as O
+from tests.gpu_util import DEV, P, ST, bf16_round, call, decode_keys, dev, lib, make_X, pack_w, rup
+from dnn_page_vectors_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+F32, BF16 = _lib.F32, _lib.BF16
+
+
+# ------------------------------------------------------------------ gather / dropout
+@pytest.mark.parametrize("bf16", [True, False])
+@pytest.mark.parametrize("D", [100, 300, 64])
+def test_gather_bit_exact(bf16, D):
+    rng = np.random.RandomState(0)
+    V1, n_tok = 1000, 777
+    Dpad = rup(D, 64)
+    E = rng.uniform(-0.25, 0.25, size=(V1, D)).astype(np.float32)
+    tok = rng.randint(0, V1, size=n_tok).astype(np.int32)
+    tok[:5] = [0, V1 - 1, 0, V1 - 1, 7]
+    if bf16:
+        table = torch.zeros((V1, Dpad), dtype=torch.bfloat16, device=DEV)
+        call("clsm_table_to_bf16", P(dev(E)), V1, D, P(table), Dpad, ST())
+        ld, ref = Dpad, bf16_round(E)
+    else:
+        table, ld, ref = dev(E), D, E
+    X = torch.full((n_tok, Dpad), 7.0, dtype=table.dtype, device=DEV)
+    call("clsm_emb_gather", P(dev(tok)), n_tok, P(table), V1, D, ld, BF16 if bf16 else F32, P(X), Dpad, 1.0, 0, ST())
+    got = X.float().cpu().numpy()
+    np.testing.assert_array_equal(got[:, :D], ref[tok])
+    assert (got[:, D:] == 0).all()
+
+
+def test_gather_host_ids_entry_point():
+    rng = np.random.RandomState(1)
+    V1, D, n_tok = 50, 64, 33
+    E = rng.randn(V1, D).astype(np.float32)
+    tok_h = torch.as_tensor(rng.randint(0, V1, size=n_tok).astype(np.int32)).pin_memory()
+    tok_d = torch.empty(n_tok, dtype=torch.int32, device=DEV)
+    X = torch.empty((n_tok, 64), dtype=torch.float32, device=DEV)
+    call("clsm_emb_gather_h", tok_h.data_ptr(), P(tok_d), n_tok, P(dev(E)), V1, D, D, F32, P(X), 64, 1.0, 0, ST())
+    np.testing.assert_array_equal(X.cpu().numpy(), E[tok_h.numpy()])
+
+
+@pytest.mark.parametrize("bf16", [True, False])
+def test_gather_dropout_matches_exported_mask(bf16):
+    rng = np.random.RandomState(2)
+    V1, D, n_tok, keep, seed = 300, 100, 4096, 0.75, 123456789
+    Dpad = rup(D, 64)
+    E = rng.uniform(-0.25, 0.25, size=(V1, D)).astype(np.float32)
+    tok = rng.randint(0, V1, size=n_tok).astype(np.int32)
+    mask = torch.empty((n_tok, D), dtype=torch.uint8, device=DEV)
+    call("clsm_dropout_mask", n_tok, D, keep, seed, P(mask), ST())
+    m = mask.cpu().numpy().astype(np.float32)
+    assert abs(m.mean() - keep) < 0.01
+    assert abs(m[:, 0].mean() - keep) < 0.05 and abs(m[0].mean() - keep) < 0.15
+    if bf16:
+        table = torch.zeros((V1, Dpad), dtype=torch.bfloat16, device=DEV)
+        call("clsm_table_to_bf16", P(dev(E)), V1, D, P(table), Dpad, ST())
+        src, ld = bf16_round(E), Dpad
+    else:
+        table, src, ld = dev(E), E, D
+    X = torch.empty((n_tok, Dpad), dtype=table.dtype, device=DEV)
+    call("clsm_emb_gather", P(dev(tok)), n_tok, P(table), V1, D, ld, BF16 if bf16 else F32, P(X), Dpad, keep, seed, ST())
+    want = src[tok] * m * np.float32(1.0 / keep)
+    if bf16:
+        want = bf16_round(want)
+    np.testing.assert_array_equal(X.float().cpu().numpy()[:, :D], want)
+    # a different seed gives a different mask
+    mask2 = torch.empty_like(mask)
+    call("clsm_dropout_mask", n_tok, D, keep, seed + 1, P(mask2), ST())
+    assert (mask2 != mask).float().mean().item() > 0.2
+
+
+# ------------------------------------------------------------------ conv + pool (CUDA-core path)
+def conv_case(seed, S, L, D, k, F, exact):
+    rng = np.random.RandomState(seed)
+    if exact:       # multiples of 1/8 in a small range: every product and sum is exact in fp32
+        X = rng.randint(-4, 5, size=(S, L, D)) / 8.0
+        W = rng.randint(-4, 5, size=(k, D, F)) / 8.0
+    else:
+        X = rng.uniform(-0.25, 0.25, size=(S, L, D))
+        W = rng.uniform(-0.05, 0.05, size=(k, D, F))
+    return X, W
+
+
+def run_conv(X, W, bf16, impl, col0=0, ldk=None):
+    S, L, D = X.shape
+    k, _, F = W.shape
+    Dpad, Fpad = rup(D, 64), rup(F, 16)
+    Xd, Wt = make_X(X, Dpad, bf16), pack_w(W, Dpad, Fpad, bf16)
+    ldk = ldk or (col0 + F)
+    keys = torch.full((S, ldk), -1, dtype=torch.int64, device=DEV)
+    call("clsm_conv_pool_fwd", P(Xd), BF16 if bf16 else F32, S, L, Dpad, P(Wt), k, F, Fpad, P(keys), ldk, col0,
+         _lib.IMPL[impl], ST())
+    torch.cuda.synchronize()
+    mx, am = decode_keys(keys[:, col0:col0 + F])
+    return mx, am, keys
+
+
+def oracle_conv(X, W):
+    S, L, D = X.shape
+    k = W.shape[0]
+    T = L - k + 1
+    Y = np.zeros((S, T, W.shape[2]))
+    for j in range(k):
+        Y += X[:, j:j + T, :] @ W[j]
+    return Y.max(axis=1), Y.argmax(axis=1), Y
+
+
+@pytest.mark.parametrize("bf16", [False, True])
+@pytest.mark.parametrize("shape", [(3, 9, 10, 2, 5), (5, 20, 100, 3, 150), (2, 100, 300, 3, 300),
+                                   (4, 7, 64, 7, 33), (1, 3, 16, 3, 1), (7, 33, 100, 1, 70), (3, 130, 100, 4, 150)])
+def test_conv_pool_simt_exact_arithmetic(bf16, shape):
+    S, L, D, k, F = shape
+    X, W = conv_case(10, S, L, D, k, F, exact=True)
+    mx, am, _ = run_conv(X, W, bf16, "simt")
+    omx, oam, _ = oracle_conv(X, W)
+    np.testing.assert_array_equal(mx, omx.astype(np.float32))     # bit-exact values
+    np.testing.assert_array_equal(am, oam)                        # bit-exact arg-max, ties -> lowest t
+
+
+@pytest.mark.parametrize("bf16", [False, True])
+def test_conv_pool_simt_random_and_ties(bf16):
+    S, L, D, k, F = 6, 100, 300, 3, 300
+    X, W = conv_case(11, S, L, D, k, F, exact=False)
+    X[2, 40:] = X[2, 40]                     # right-padded document: identical windows from t=40 on
+    X[3, :] = X[3, 0]                        # all-PAD document
+    if bf16:
+        X, W = bf16_round(X).astype(np.float64), bf16_round(W).astype(np.float64)
+    mx, am, _ = run_conv(X, W, bf16, "simt")
+    omx, oam, Y = oracle_conv(X, W)
+    np.testing.assert_allclose(mx, omx, rtol=1e-5, atol=1e-6)
+    assert (am[3] == 0).all()                # ties -> lowest index
+    # arg-max may differ from the f64 oracle only where the top two are closer than fp32 noise
+    bad = np.argwhere(am != oam)
+    for s, f in bad:
+        assert abs(Y[s, am[s, f], f] - Y[s, oam[s, f], f]) < 1e-5
+
+
+def test_conv_pool_column_offset_and_clearing():
+    X, W = conv_case(12, 4, 12, 64, 2, 20, exact=True)
+    mx, am, keys = run_conv(X, W, False, "simt", col0=7, ldk=40)
+    omx, oam, _ = oracle_conv(X, W)
+    np.testing.assert_array_equal(mx, omx.astype(np.float32))
+    k = keys.cpu().numpy()
+    assert (k[:, :7] == -1).all() and (k[:, 27:] == -1).all()     # other columns untouched
+
+
+@pytest.mark.parametrize("act", ["relu", "tanh", "linear"])
+def test_pool_finalize(act):
+    rng = np.random.RandomState(3)
+    X, W = conv_case(13, 5, 15, 64, 3, 24, exact=False)
+    b = rng.uniform(-0.2, 0.2, size=24)
+    _, _, keys = run_conv(X, W, False, "simt")
+    pooled = torch.empty((5, 24), dtype=torch.float32, device=DEV)
+    am = torch.empty((5, 24), dtype=torch.int32, device=DEV)
+    call("clsm_pool_finalize", P(keys), 5, 24, 24, P(dev(b, torch.float32)), _lib.ACT[act], P(pooled), P(am), 24, ST())
+    op, oa = O.conv_pool_fwd(X, W, b, act)
+    np.testing.assert_allclose(pooled.cpu().numpy(), op, rtol=1e-5, atol=1e-6)
+    np.testing.assert_array_equal(am.cpu().numpy(), oa)
+
+
+# ------------------------------------------------------------------ dense
+@pytest.mark.parametrize("S,Pn,H", [(5, 7, 3), (130, 300, 128), (257, 600, 150), (1, 1, 1)])
+@pytest.mark.parametrize("act", ["relu", "tanh"])
+def test_dense_fwd_bwd(S, Pn, H, act):
+    rng = np.random.RandomState(4)
+    pooled = rng.uniform(0, 1, size=(S, Pn)) * (rng.rand(S, Pn) > 0.3)
+    Wd = rng.uniform(-0.2, 0.2, size=(Pn, H))
+    bd = rng.uniform(-0.1, 0.1, size=H)
+    dsem = rng.randn(S, H)
+    sem = torch.empty((S, H), dtype=torch.float32, device=DEV)
+    pd_, wd_, bd_ = dev(pooled, torch.float32), dev(Wd, torch.float32), dev(bd, torch.float32)
+    call("clsm_dense_fwd", P(pd_), S, Pn, Pn, P(wd_), P(bd_), H, _lib.ACT[act], P(sem), ST())
+    Z = O.act_fwd(pooled @ Wd + bd, act)
+    np.testing.assert_allclose(sem.cpu().numpy(), Z, rtol=2e-5, atol=2e-6)
+
+    ws_bytes = lib.clsm_dense_bwd_workspace_bytes(S, Pn, H)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    dWd = torch.empty((Pn, H), dtype=torch.float32, device=DEV)
+    dbd = torch.empty(H, dtype=torch.float32, device=DEV)
+    G = torch.empty((S, Pn), dtype=torch.float32, device=DEV)
+    call("clsm_dense_bwd", P(pd_), P(sem), P(dev(dsem, torch.float32)), S, Pn, Pn, P(wd_), H, _lib.ACT[act],
+         P(dWd), P(dbd), P(G), P(ws), ws_bytes, ST())
+    semn = sem.cpu().numpy().astype(np.float64)
+    dpre = dsem * O.act_grad_from_output(semn, act)
+    np.testing.assert_allclose(dWd.cpu().numpy(), pooled.T @ dpre, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(dbd.cpu().numpy(), dpre.sum(0), rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(G.cpu().numpy(), (dpre @ Wd.T) * O.act_grad_from_output(pooled, act), rtol=1e-4, atol=1e-5)
+    with pytest.raises(_lib.ClsmError):
+        call("clsm_dense_bwd", P(pd_), P(sem), P(sem), S, Pn, Pn, P(wd_), H, _lib.ACT[act], P(dWd), P(dbd), P(G), P(ws), 8, ST())
+
+
+# ------------------------------------------------------------------ cosine / softmax / loss
+@pytest.mark.parametrize("B,J,H", [(7, 3, 150), (64, 4, 128), (5, 50, 128), (3, 0, 8)])
+def test_sim_loss_fwd_bwd(B, J, H):
+    rng = np.random.RandomState(5)
+    zq = np.maximum(rng.randn(B, H), 0)          # post-ReLU vectors
+    zd = np.maximum(rng.randn(B, 1 + J, H), 0)
+    zq[0] = 0.0                                   # dead query -> cosine exactly 0
+    if J >= 1:
+        zd[1, 1] = 0.0
+        zd[2, 0] = zq[2] * 3.0                    # cosine exactly at the upper clip
+    fw = O.sim_loss_fwd(zq, zd, 10.0)
+    dq, dd = O.sim_loss_bwd(zq, zd, fw, 10.0, batch_total=2 * B)
+    q_, d_ = dev(zq, torch.float32), dev(zd.reshape(B * (1 + J), H), torch.float32)
+    cosv = torch.empty((B, 1 + J), dtype=torch.float32, device=DEV)
+    prob = torch.empty_like(cosv)
+    la = torch.empty(2, dtype=torch.float32, device=DEV)
+    gq = torch.empty((B, H), dtype=torch.float32, device=DEV)
+    gd = torch.empty((B * (1 + J), H), dtype=torch.float32, device=DEV)
+    call("clsm_sim_loss", P(q_), P(d_), B, J, H, 10.0, 2 * B, P(cosv), P(prob), P(la), P(gq), P(gd), ST())
+    c = cosv.cpu().numpy()
+    assert (c[0] == 0.0).all() and np.isfinite(gq.cpu().numpy()).all()
+    np.testing.assert_allclose(c, fw["cos"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(prob.cpu().numpy(), fw["prob"], rtol=1e-4, atol=1e-7)
+    np.testing.assert_allclose(la.cpu().numpy(), [fw["loss"], fw["acc"]], rtol=1e-5)
+    # rows whose cosine sits exactly on a clip edge may legitimately differ in the gate
+    edge = (np.abs(fw["raw"] - 1.0) < 1e-6) | (np.abs(fw["raw"]) < 1e-9)
+    keep_rows = ~edge.any(axis=1)
+    np.testing.assert_allclose(gq.cpu().numpy()[keep_rows], dq[keep_rows], rtol=2e-4, atol=1e-7)
+    np.testing.assert_allclose(gd.cpu().numpy().reshape(B, 1 + J, H)[keep_rows], dd[keep_rows], rtol=2e-4, atol=1e-7)
+
+
+# ------------------------------------------------------------------ conv backward
+@pytest.mark.parametrize("bf16", [False, True])
+@pytest.mark.parametrize("shape", [(5, 20, 100, 3, 150), (9, 12, 64, 2, 20), (3, 100, 300, 3, 300), (4, 30, 100, 5, 130),
+                                   (6, 9, 40, 1, 17)])
+def test_conv_pool_bwd(bf16, shape):
+    S, L, D, k, F = shape
+    rng = np.random.RandomState(6)
+    X, W = conv_case(14, S, L, D, k, F, exact=False)
+    if bf16:
+        X, W = bf16_round(X).astype(np.float64), bf16_round(W).astype(np.float64)
+    Dpad, Fpad = rup(D, 64), rup(F, 16)
+    Pn, col0 = F + 9, 4
+    G = np.zeros((S, Pn)); A = np.zeros((S, Pn), dtype=np.int32)
+    G[:, col0:col0 + F] = rng.randn(S, F) * (rng.rand(S, F) > 0.4)      # ~40 % dead (ReLU)
+    A[:, col0:col0 + F] = rng.randint(0, L - k + 1, size=(S, F))
+    A[0, col0:col0 + F] = 0; A[1, col0:col0 + F] = L - k                  # edges
+    Xd, Wt = make_X(X, Dpad, bf16), pack_w(W, Dpad, Fpad, bf16)
+    ws_bytes = lib.clsm_conv_bwd_workspace_bytes(S, k, D, F)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    dW = torch.empty((k, D, F), dtype=torch.float32, device=DEV)
+    db = torch.empty(F, dtype=torch.float32, device=DEV)
+    dX = torch.full((S * L, Dpad), 3.0, dtype=torch.float32, device=DEV)
+    args = (P(Xd), BF16 if bf16 else F32, S, L, D, Dpad, P(Wt), k, F, Fpad, P(dev(G, torch.float32)), P(dev(A)), Pn, col0,
+            P(dW), P(db), P(dX))
+    call("clsm_conv_pool_bwd", *args, 1, P(ws), ws_bytes, ST())
+    Gi, Ai = G[:, col0:col0 + F], A[:, col0:col0 + F].astype(np.int64)
+    odW = np.zeros_like(W); odX = np.zeros_like(X)
+    sidx = np.arange(S)
+    for j in range(k):
+        odW[j] = np.einsum("sfd,sf->df", X[sidx[:, None], Ai + j, :], Gi)
+        np.add.at(odX, (np.repeat(sidx, F), (Ai + j).ravel()), (Gi[:, :, None] * W[j].T[None]).reshape(S * F, D))
+    np.testing.assert_allclose(dW.cpu().numpy(), odW, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(db.cpu().numpy(), Gi.sum(0), rtol=1e-4, atol=1e-5)
+    got = dX.cpu().numpy()
+    np.testing.assert_allclose(got[:, :D], odX.reshape(S * L, D), rtol=1e-4, atol=1e-5)
+    assert (got[:, D:] == 0).all()
+    # second window accumulates into dX
+    call("clsm_conv_pool_bwd", *args, 0, P(ws), ws_bytes, ST())
+    np.testing.assert_allclose(dX.cpu().numpy()[:, :D], 2 * odX.reshape(S * L, D), rtol=1e-4, atol=1e-5)
+
+
+# ------------------------------------------------------------------ embedding scatter
+def run_scatter(tok, dX, D, V1, keep=1.0, seed=0):
+    n_tok, Dpad = dX.shape
+    ws_bytes = lib.clsm_emb_scatter_workspace_bytes(n_tok, D)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    uniq = torch.full((n_tok,), -7, dtype=torch.int32, device=DEV)
+    nu = torch.zeros(1, dtype=torch.int32, device=DEV)
+    rows = torch.full((min(n_tok, V1), Dpad), 9.0, dtype=torch.float32, device=DEV)
+    roi = torch.empty(V1, dtype=torch.int32, device=DEV)
+    call("clsm_emb_scatter", P(tok), n_tok, P(dX), Dpad, D, keep, seed, V1, P(uniq), P(nu), P(rows), P(roi),
+         P(ws), ws_bytes, ST())
+    torch.cuda.synchronize()
+    n = int(nu.item())
+    return uniq[:n].cpu().numpy(), rows[:n].cpu().numpy(), roi.cpu().numpy()
+
+
+@pytest.mark.parametrize("n_tok,V1,D,skew", [(1, 10, 100, 0.0), (63, 10, 100, 0.5), (64, 1000, 100, 0.0), (65, 5, 64, 0.9),
+                                             (5000, 200, 100, 0.6), (70000, 50000, 300, 0.4), (4097, 3, 100, 0.0),
+                                             (140000, 10, 64, 0.97)])
+def test_emb_scatter_matches_add_at_and_is_deterministic(n_tok, V1, D, skew):
+    rng = np.random.RandomState(7)
+    Dpad = rup(D, 64)
+    tok = rng.randint(0, V1, size=n_tok).astype(np.int32)
+    tok[rng.rand(n_tok) < skew] = V1 // 2                 # PAD-like heavy id
+    dXn = np.zeros((n_tok, Dpad), dtype=np.float32)
+    dXn[:, :D] = rng.randn(n_tok, D)
+    tok_d, dX_d = dev(tok), dev(dXn)
+    u1, r1, roi = run_scatter(tok_d, dX_d, D, V1)
+    want = np.zeros((V1, D)); np.add.at(want, tok, dXn[:, :D].astype(np.float64))
+    ids = np.unique(tok)
+    np.testing.assert_array_equal(u1, ids)                 # sorted unique ids
+    np.testing.assert_allclose(r1[:, :D], want[ids], rtol=2e-5, atol=2e-4 if n_tok > 50000 else 2e-5)
+    assert (r1[:, D:] == 0).all()
+    exp_roi = np.full(V1, -1); exp_roi[ids] = np.arange(len(ids))
+    np.testing.assert_array_equal(roi, exp_roi)
+    u2, r2, _ = run_scatter(tok_d, dX_d, D, V1)
+    assert np.array_equal(r1, r2) and np.array_equal(u1, u2)      # bit-identical rerun
+
+
+def test_emb_scatter_reapplies_dropout_mask():
+    rng = np.random.RandomState(8)
+    n_tok, V1, D, keep, seed = 3000, 40, 100, 0.75, 99
+    Dpad = rup(D, 64)
+    tok = rng.randint(0, V1, size=n_tok).astype(np.int32)
+    dXn = np.zeros((n_tok, Dpad), dtype=np.float32); dXn[:, :D] = rng.randn(n_tok, D)
+    mask = torch.empty((n_tok, D), dtype=torch.uint8, device=DEV)
+    call("clsm_dropout_mask", n_tok, D, keep, seed, P(mask), ST())
+    m = mask.cpu().numpy().astype(np.float64)
+    u, r, _ = run_scatter(dev(tok), dev(dXn), D, V1, keep, seed)
+    want = np.zeros((V1, D)); np.add.at(want, tok, dXn[:, :D] * m / keep)
+    np.testing.assert_allclose(r[:, :D], want[u], rtol=2e-5, atol=2e-5)
+
+
+# ------------------------------------------------------------------ Adam
+def test_adam_dense_and_table():
+    rng = np.random.RandomState(9)
+    n = 1001
+    p0, g = rng.randn(n), rng.randn(n)
+    p, m, v = p0.copy(), np.zeros(n), np.zeros(n)
+    pd_, md_, vd_ = dev(p0, torch.float32), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    for t in (1, 2, 3):
+        O.adam_step(p, m, v, g * t, t)
+        call("clsm_adam_dense", P(pd_), P(md_), P(vd_), P(dev(g * t, torch.float32)), n, t, 1e-3, 0.9, 0.999, 1e-8, ST())
+    np.testing.assert_allclose(pd_.cpu().numpy(), p, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(vd_.cpu().numpy(), v, rtol=1e-5, atol=1e-9)
+
+    for D in (100, 30, 7):           # vectorised and scalar variants
+        V1, Dpad = 50, rup(D, 64)
+        E0 = rng.randn(V1, D)
+        ids = np.array([3, 7, 8, 49], dtype=np.int32)
+        rows = np.zeros((4, Dpad), dtype=np.float32); rows[:, :D] = rng.randn(4, D)
+        roi = np.full(V1, -1, dtype=np.int32); roi[ids] = np.arange(4)
+        Ed, Em, Ev = dev(E0, torch.float32), torch.zeros((V1, D), device=DEV), torch.zeros((V1, D), device=DEV)
+        copy = torch.full((V1, Dpad), 5.0, dtype=torch.bfloat16, device=DEV) if D % 4 == 0 else None
+        p, m, v = E0.copy(), np.zeros((V1, D)), np.zeros((V1, D))
+        gfull = np.zeros((V1, D)); gfull[ids] = rows[:, :D]
+        for t in (1, 2):
+            O.adam_step(p, m, v, gfull, t)
+            call("clsm_adam_table", P(Ed), P(Em), P(Ev), V1, D, P(dev(roi)), P(dev(rows)), Dpad, t,
+                 1e-3, 0.9, 0.999, 1e-8, P(copy), Dpad, ST())
+        np.testing.assert_allclose(Ed.cpu().numpy(), p, rtol=1e-5, atol=1e-6)
+        assert np.abs(Ed.cpu().numpy()[0] - E0[0]).max() == 0          # zero-grad rows with m=v=0 stay put
+        if copy is not None:
+            np.testing.assert_array_equal(copy.float().cpu().numpy()[:, :D], bf16_round(Ed.cpu().numpy()))
+        # lazy variant touches only the listed rows
+        E2, m2, v2 = dev(E0, torch.float32), torch.zeros((V1, D), device=DEV), torch.zeros((V1, D), device=DEV)
+        call("clsm_adam_rows", P(E2), P(m2), P(v2), D, P(dev(ids)), P(dev(np.array([4], dtype=np.int32))), 4,
+             P(dev(rows)), Dpad, 1, 1e-3, 0.9, 0.999, 1e-8, P(None), Dpad, ST())
+        pp, mm, vv = E0.copy(), np.zeros((V1, D)), np.zeros((V1, D))
+        O.adam_step(pp, mm, vv, gfull, 1)
+        np.testing.assert_allclose(E2.cpu().numpy(), pp, rtol=1e-5, atol=1e-6)
+
+
+# ------------------------------------------------------------------ top-k
+@pytest.mark.parametrize("Q,N,H,k", [(3, 50, 8, 10), (9, 5000, 128, 100), (130, 2048, 128, 100), (2, 2049, 16, 128),
+                                     (1, 7, 4, 10), (5, 300000, 32, 100)])
+def test_cos_topk_matches_oracle(Q, N, H, k):
+    rng = np.random.RandomState(10)
+    c = O.normalise_rows(rng.randn(N, H)).astype(np.float32)
+    q = O.normalise_rows(rng.randn(Q, H)).astype(np.float32)
+    if N > 40:
+        c[17] = c[5]; c[N - 1] = c[5]; q[0] = c[5]            # exact ties -> lowest id first
+    cd, qd = dev(c), dev(q)
+    ws_bytes = lib.clsm_cos_topk_workspace_bytes(Q, N, k)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    sc = torch.empty((Q, k), dtype=torch.float32, device=DEV)
+    ids = torch.empty((Q, k), dtype=torch.int64, device=DEV)
+    call("clsm_cos_topk", P(qd), Q, P(cd), N, H, k, 1000, P(sc), P(ids), P(ws), ws_bytes, ST())
+    # oracle on the GPU's own fp32 scores is not available; use f64 scores and compare ids where the
+    # margin to the next candidate exceeds fp32 noise, and scores everywhere
+    osc, oid = O.cos_topk(q.astype(np.float64), c.astype(np.float64), k, id_base=1000)
+    kk = min(k, N)
+    got_s, got_i = sc.cpu().numpy(), ids.cpu().numpy()
+    np.testing.assert_allclose(got_s[:, :kk], osc, rtol=1e-5, atol=1e-6)
+    if kk < k:
+        assert (got_i[:, kk:] == -1).all()
+    mism = got_i[:, :kk] != oid
+    assert mism.mean() < 0.02
+    for r, j in np.argwhere(mism):
+        assert abs(got_s[r, j] - osc[r, j]) < 1e-5
+    if N > 40:
+        assert list(got_i[0, :3]) == [1005, 1017, 1000 + N - 1]
+    assert (np.diff(got_s[:, :kk], axis=1) <= 0).all()
+
+
+def test_topk_merge_equals_single_pass():
+    rng = np.random.RandomState(11)
+    Q, N, H, k, parts = 6, 9000, 32, 100, 4
+    c = O.normalise_rows(rng.randn(N, H)).astype(np.float32)
+    q = O.normalise_rows(rng.randn(Q, H)).astype(np.float32)
+    c[8000] = c[10]; q[1] = c[10]
+    cd, qd = dev(c), dev(q)
+
+    def topk(c_t, base):
+        n = c_t.shape[0]
+        wsb = lib.clsm_cos_topk_workspace_bytes(Q, n, k)
+        ws = torch.empty(wsb, dtype=torch.uint8, device=DEV)
+        sc = torch.empty((Q, k), dtype=torch.float32, device=DEV)
+        ids = torch.empty((Q, k), dtype=torch.int64, device=DEV)
+        call("clsm_cos_topk", P(qd), Q, P(c_t), n, H, k, base, P(sc), P(ids), P(ws), wsb, ST())
+        return sc, ids
+    full_s, full_i = topk(cd, 0)
+    step = N // parts
+    ps = [topk(cd[i * step:(i + 1) * step].contiguous(), i * step) for i in range(parts)]
+    S_ = torch.stack([p[0] for p in ps]); I_ = torch.stack([p[1] for p in ps])
+    wsb = lib.clsm_topk_merge_workspace_bytes(parts, Q, k)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=DEV)
+    ms = torch.empty((Q, k), dtype=torch.float32, device=DEV)
+    mi = torch.empty((Q, k), dtype=torch.int64, device=DEV)
+    call("clsm_topk_merge", P(S_), P(I_), parts, Q, k, P(ms), P(mi), P(ws), wsb, ST())
+    assert torch.equal(mi, full_i) and torch.equal(ms, full_s)     # independent of the sharding
+
+
+def test_normalize_rows():
+    rng = np.random.RandomState(12)
+    z = np.maximum(rng.randn(100, 128), 0).astype(np.float32); z[3] = 0
+    out = torch.empty((100, 128), dtype=torch.float32, device=DEV)
+    call("clsm_normalize_rows", P(dev(z)), 100, 128, P(out), ST())
+    np.testing.assert_allclose(out.cpu().numpy(), O.normalise_rows(z.astype(np.float64)), rtol=1e-5, atol=1e-7)
+    assert (out[3] == 0).all()

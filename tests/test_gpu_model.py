@@ -1,0 +1,207 @@
+"""Whole-path parity on the GPU (-m gpu): build / train / predict entry points against the
+oracle on the same weights and token ids: forward, loss, gradients via the
+N-step training trajectory, dropout replay through the exported mask, encode + top-k."""
+import copy
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import clsm_oracle as O
+from tests.gpu_util import DEV, P, ST, bf16_round, call, dev
+from dnn_page_vectors_b200 import CLSM, Configuration, DataHelpers, ModelParams, RTF, ModelCheckpoint
+
+pytestmark = pytest.mark.gpu
+
+
+def synth(seed, B, J, Lq, Ld, V, pad_id=0):
+    rng = np.random.RandomState(seed)
+
+    def seqs(n, L):
+        t = rng.zipf(1.3, size=(n, L)) % V
+        lens = rng.randint(max(L // 4, 1), L + 1, size=n)
+        t[np.arange(L)[None, :] >= lens[:, None]] = pad_id      # right padding
+        return t.astype(np.int32)
+    return [seqs(B, Lq)] + [seqs(B, Ld) for _ in range(1 + J)]
+
+
+def oracle_params(rng, V1, D, windows, F, H):
+    p = O.init_tower(rng, V1, D, windows, F, H)
+    p["convb"] = [rng.uniform(-0.05, 0.05, size=F) for _ in windows]
+    p["bd"] = rng.uniform(-0.05, 0.05, size=H)
+    return p
+
+
+def to_model_weights(p):
+    w = {"E": p["E"], "Wd": p["Wd"], "bd": p["bd"]}
+    for i, (W, b) in enumerate(zip(p["convW"], p["convb"])):
+        w["convW%d" % i], w["convb%d" % i] = W, b
+    return w
+
+
+def build(precision, act, B, J, Lq, Ld, V, D, windows, F, H, dropout=0.0, seed=0, conv_impl="auto"):
+    mp = ModelParams(embedding_dim=D, batch_size=B, filter_sizes=windows, num_filters=F, hidden_dims=H, J=J,
+                     dropout_prob=(dropout, 0.5), activation=act, precision=precision)
+    rng = np.random.RandomState(seed)
+    pq = oracle_params(rng, V + 1, D, windows, F, H)
+    pd_ = oracle_params(rng, V + 1, D, windows, F, H)
+    net = CLSM(mp, Lq, Ld, embedding_weights=pq["E"], device=DEV, conv_impl=conv_impl).compile()
+    net.set_weights({"query": to_model_weights(pq), "doc": to_model_weights(pd_)})
+    return net, pq, pd_
+
+
+def oracle_train(x, pq, pd_, act, steps, masks=None, keep=1.0):
+    pq, pd_ = copy.deepcopy(pq), copy.deepcopy(pd_)
+    q = x[0].astype(np.int64)
+    d = np.stack(x[1:], axis=1).astype(np.int64)
+    st = {}
+    losses = []
+    for t in range(1, steps + 1):
+        mq, md = masks[t - 1] if masks else (None, None)
+        head, gq, gd, _, _ = O.model_loss_and_grads(q, d, pq, pd_, act=act, mask_q=mq, mask_d=md, keep=keep)
+        losses.append((head["loss"], head["acc"]))
+        for tag, p, g in (("q", pq, gq), ("d", pd_, gd)):
+            for (name, arr), (_, grad) in zip(O.flat_params(p), O.flat_grads(g)):
+                m, v = st.setdefault((tag, name), (np.zeros_like(arr), np.zeros_like(arr)))
+                O.adam_step(arr, m, v, grad, t)
+    return losses, pq, pd_
+
+
+CFG_SMALL = dict(B=16, J=3, Lq=8, Ld=30, V=200, D=100, windows=(3, 4), F=150, H=150)     # reference literals, short
+CFG_ONE = dict(B=32, J=4, Lq=20, Ld=100, V=500, D=300, windows=(3,), F=300, H=128)        # BASELINE cfg1 shape, B cut
+
+
+@pytest.mark.parametrize("cfg", [CFG_SMALL, CFG_ONE], ids=["ref-literal", "cfg1"])
+@pytest.mark.parametrize("act", ["relu", "tanh"])
+def test_fp32_training_trajectory_matches_oracle(cfg, act):
+    net, pq, pd_ = build("fp32", act, conv_impl="simt", **cfg)
+    x = synth(1, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"])
+    steps = 3
+    ol, oq, od = oracle_train(x, pq, pd_, act, steps)
+    # evaluation path first: loss and p0 on the initial weights
+    l0, a0 = net.test_on_batch(x)
+    assert abs(l0 - ol[0][0]) <= 1e-5 * max(1.0, abs(ol[0][0])) and abs(a0 - ol[0][1]) < 1e-6
+    for t in range(steps):
+        l, a = net.train_on_batch(x, np.ones(cfg["B"]))
+        assert abs(l - ol[t][0]) <= 2e-5 * max(1.0, abs(ol[t][0])), (t, l, ol[t])
+    w = net.get_weights()
+    for tag, op in (("query", oq), ("doc", od)):
+        # Adam moves every weight by ~lr per step; compare the MOVEMENT, which is what gradients drive
+        np.testing.assert_allclose(w[tag]["Wd"], op["Wd"], atol=2e-5)
+        np.testing.assert_allclose(w[tag]["bd"], op["bd"], atol=2e-5)
+        np.testing.assert_allclose(w[tag]["convW0"], op["convW"][0], atol=2e-5)
+        np.testing.assert_allclose(w[tag]["convb0"], op["convb"][0], atol=2e-5)
+        np.testing.assert_allclose(w[tag]["E"], op["E"], atol=2e-5)
+
+
+def test_bf16_forward_and_loss_within_tolerance():
+    cfg = CFG_ONE
+    net, pq, pd_ = build("bf16", "relu", conv_impl="simt", **cfg)
+    x = synth(2, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"])
+    ol, _, _ = oracle_train(x, pq, pd_, "relu", 2)
+    l0, _ = net.test_on_batch(x)
+    assert abs(l0 - ol[0][0]) <= 2e-2 * max(1.0, abs(ol[0][0]))
+    l1, _ = net.train_on_batch(x)
+    l2, _ = net.train_on_batch(x)
+    assert abs(l1 - ol[0][0]) <= 2e-2 * max(1.0, abs(ol[0][0]))
+    assert abs(l2 - ol[1][0]) <= 2e-2 * max(1.0, abs(ol[1][0]))
+    # page vectors and cosines
+    q = x[0].astype(np.int64)
+    fq = O.tower_fwd(q, pq, "relu")
+    np.testing.assert_allclose(net.get_weights()["query"]["E"].shape, pq["E"].shape)
+
+
+def test_dropout_step_replays_in_the_oracle():
+    cfg = dict(CFG_SMALL, B=8)
+    net, pq, pd_ = build("fp32", "relu", dropout=0.25, conv_impl="simt", **cfg)
+    x = synth(3, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"])
+    sq, sd = net._seeds()
+    D, keep = cfg["D"], 0.75
+    nq, nd = cfg["B"] * cfg["Lq"], cfg["B"] * (1 + cfg["J"]) * cfg["Ld"]
+    mq = torch.empty((nq, D), dtype=torch.uint8, device=DEV)
+    md = torch.empty((nd, D), dtype=torch.uint8, device=DEV)
+    call("clsm_dropout_mask", nq, D, keep, sq, P(mq), ST())
+    call("clsm_dropout_mask", nd, D, keep, sd, P(md), ST())
+    masks = [(mq.cpu().numpy().reshape(cfg["B"], cfg["Lq"], D).astype(np.float64),
+              md.cpu().numpy().reshape(cfg["B"] * (1 + cfg["J"]), cfg["Ld"], D).astype(np.float64))]
+    ol, oq, od = oracle_train(x, pq, pd_, "relu", 1, masks, keep)
+    l, _ = net.train_on_batch(x)
+    assert abs(l - ol[0][0]) <= 2e-5 * max(1.0, ol[0][0])
+    w = net.get_weights()
+    np.testing.assert_allclose(w["doc"]["E"], od["E"], atol=2e-5)
+    np.testing.assert_allclose(w["query"]["convW0"], oq["convW"][0], atol=2e-5)
+    # evaluation does not drop
+    l_eval, _ = net.test_on_batch(x)
+    h, _, _, _, _ = O.model_loss_and_grads(x[0].astype(np.int64), np.stack(x[1:], 1).astype(np.int64), oq, od)
+    assert abs(l_eval - h["loss"]) <= 5e-5 * max(1.0, h["loss"])
+
+
+def test_predict_rtf_encode_topk_and_persistence(tmp_path):
+    cfg = CFG_SMALL
+    net, pq, pd_ = build("fp32", "relu", conv_impl="simt", **cfg)
+    x = synth(4, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"])
+    q, d = x[0].astype(np.int64), np.stack(x[1:], 1).astype(np.int64)
+    head, _, _, fq, fd = O.model_loss_and_grads(q, d, pq, pd_)
+    prob = net.predict(x)
+    assert prob.shape == (cfg["B"], 1)
+    np.testing.assert_allclose(prob[:, 0], head["p0"], rtol=1e-4, atol=1e-7)
+    zq = net.query_model.predict(x[0])
+    np.testing.assert_allclose(zq, fq["sem"], rtol=1e-4, atol=1e-6)
+    zd0 = fd["sem"].reshape(cfg["B"], 1 + cfg["J"], -1)[:, 0]
+    np.testing.assert_allclose(RTF([zq, zd0.astype(np.float32)])[:, 0], head["cos"][:, 0], rtol=1e-4, atol=1e-6)
+    # encode + top-k against the oracle composition
+    pages = synth(5, 300, 0, cfg["Lq"], cfg["Ld"], cfg["V"])[1]
+    vec = net.encode_pages(pages, batch_size=128)
+    ovec = O.normalise_rows(O.tower_fwd(pages.astype(np.int64), pd_, "relu")["sem"])
+    np.testing.assert_allclose(vec.cpu().numpy(), ovec, rtol=1e-4, atol=1e-6)
+    qv = net.encode_queries(x[0])
+    sc, ids = net.topk(qv, vec, k=10)
+    osc, oid = O.cos_topk(O.normalise_rows(fq["sem"]), ovec, 10)
+    np.testing.assert_allclose(sc.cpu().numpy(), osc, rtol=1e-4, atol=1e-6)
+    assert (ids.cpu().numpy() == oid).mean() > 0.97
+    # save / load round trip keeps the step and the optimizer state
+    net.train_on_batch(x)
+    net.save(str(tmp_path / "m.pt")); net.save_weights(str(tmp_path / "w.pt"))
+    l_next, _ = net.train_on_batch(x)
+    net2, _, _ = build("fp32", "relu", conv_impl="simt", **cfg)
+    net2.load(str(tmp_path / "m.pt"))
+    l_next2, _ = net2.train_on_batch(x)
+    assert l_next == l_next2
+    assert json.loads(net.to_json())["config"]["num_filters"] == cfg["F"]
+
+
+def test_fit_generator_on_synthetic_file(tmp_path):
+    import os
+    conf = Configuration(experiment_root_directory=str(tmp_path), feature_level="word", num_negative_examples=3,
+                         query_length=6, document_length=16)
+    os.makedirs(conf.data_dir); os.makedirs(conf.vectors_directory); os.makedirs(conf.trained_model_dir)
+    words = ["w%d" % i for i in range(60)]
+    rng = np.random.RandomState(0)
+
+    def sent(n):
+        return " ".join(rng.choice(words, size=n))
+    lines = []
+    for _ in range(96):
+        qy = sent(4)
+        lines.append(json.dumps({"q": qy, "doc_corr": qy + " " + sent(6), "doc_incorr": [sent(10) for _ in range(3)]}))
+    for path in conf.input_file_list:
+        with open(path, "w") as f:
+            f.write("\n".join(lines) + "\n")
+    with open(conf.word_vectors_file, "w") as f:
+        for w in words[:30]:
+            f.write(w + " " + " ".join("%.4f" % v for v in rng.uniform(-0.25, 0.25, size=100)) + "\n")
+    dh = DataHelpers(conf)
+    np.random.seed(1337)
+    W, vocab = dh.get_vocab_index_embedding_weights(100, False)
+    mp = ModelParams(batch_size=32, nb_epoch=4, precision="fp32", dropout_prob=(0.25, 0.5), lr=1e-2)
+    net = CLSM(mp, conf.query_length, conf.document_length, embedding_weights=W, device=DEV, conv_impl="simt").compile()
+    gen = dh.load_data_generator(vocab, mode="training", batch_size=32, nb_epochs=4)
+    val = dh.load_data_generator(vocab, mode="validation", batch_size=32, nb_epochs=4)
+    ck = ModelCheckpoint(conf.trained_model_dir + "/weights.{epoch:02d}.pt")
+    hist = net.fit_generator(gen, samples_per_epoch=96, nb_epoch=4, validation_data=val, nb_val_samples=96,
+                             callbacks=[ck], verbose=0)
+    h = hist.history
+    assert set(h) == {"loss", "acc", "val_loss", "val_acc"} and len(h["loss"]) == 4
+    assert h["loss"][-1] < h["loss"][0] and h["val_loss"][-1] < h["val_loss"][0]    # it learns
+    assert os.path.exists(conf.trained_model_dir + "/weights.03.pt")
