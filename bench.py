@@ -25,7 +25,11 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-CFG2 = dict(V=1_000_000, D=300, windows=(3,), F=300, H=128, J=4, Lq=20, Ld=100, B=4096, act="tanh")
+# activation: the reference's own literal is ReLU (cnn_dssm_tf.py:88,126).  north_star says "tanh" (the CLSM paper),
+# but tanh + the reference's cosine clip to [0, 1] (cnn_dssm_tf.py:75-76) dies after one Adam step on random
+# init: every cosine goes negative, is clipped, and all gradients are zero from then on (measured).
+# A dead backward would be skipped work, so the benchmark trains the reference's ReLU model.
+CFG2 = dict(V=1_000_000, D=300, windows=(3,), F=300, H=128, J=4, Lq=20, Ld=100, B=4096, act="relu")
 WORKLOAD = "cfg2: CLSM bf16 train step, B=4096/GPU, J=4, Lq=20, Ld=100, D=300, window 3, F=300, H=128, V=1M, dense Adam"
 
 

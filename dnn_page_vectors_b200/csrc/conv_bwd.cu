@@ -28,6 +28,9 @@ template <> struct Pair<__nv_bfloat16> {
 };
 
 // grid (n_groups, Dpad/64, ceil(F/FT)); part[g][f][j][c]
+// Each warp owns FPW filters and one 64-column slice; lane owns 2 columns.  The (G, argmax) entries
+// of 32 sequences are fetched in one go (lane l holds sequence s0+l), so the only dependent global
+// loads left in the inner loop are the row reads themselves, which are independent of each other.
 template <typename T, int KW>
 __global__ void __launch_bounds__(DW_WARPS * 32, 1)
 conv_bwd_dw_kernel(const T* __restrict__ X, int L, int Dpad, int64_t S, int64_t seq_per_group,
@@ -44,23 +47,29 @@ conv_bwd_dw_kernel(const T* __restrict__ X, int L, int Dpad, int64_t S, int64_t 
 #pragma unroll
     for (int j = 0; j < KW; ++j) acc[i][j] = make_float2(0.f, 0.f);
 
-  for (int64_t s = s0; s < s1; ++s) {
-    float g = 0.0f; int a = 0;
-    if (lane < FPW && f0 + lane < F) {
-      g = __ldg(G + s * ldp + col0 + f0 + lane);
-      a = __ldg(A + s * ldp + col0 + f0 + lane);
-    }
-    const T* xs = X + s * L * static_cast<int64_t>(Dpad) + cbase;
+  for (int64_t sb = s0; sb < s1; sb += 32) {
+    float gv[FPW]; int av[FPW];
+    const int64_t sl = sb + lane;
 #pragma unroll
     for (int i = 0; i < FPW; ++i) {
-      const float gi = __shfl_sync(0xffffffffu, g, i);
-      const int ai = __shfl_sync(0xffffffffu, a, i);
-      if (gi != 0.0f) {
+      const bool ok = sl < s1 && f0 + i < F;
+      gv[i] = ok ? __ldg(G + sl * ldp + col0 + f0 + i) : 0.0f;
+      av[i] = ok ? __ldg(A + sl * ldp + col0 + f0 + i) : 0;
+    }
+    const int cnt = static_cast<int>((s1 - sb < 32) ? s1 - sb : 32);
+    for (int q = 0; q < cnt; ++q) {
+      const T* xs = X + (sb + q) * L * static_cast<int64_t>(Dpad) + cbase;
 #pragma unroll
-        for (int j = 0; j < KW; ++j) {
-          const float2 x = Pair<T>::ld(xs + static_cast<int64_t>(ai + j) * Dpad);
-          acc[i][j].x = fmaf(gi, x.x, acc[i][j].x);
-          acc[i][j].y = fmaf(gi, x.y, acc[i][j].y);
+      for (int i = 0; i < FPW; ++i) {
+        const float gi = __shfl_sync(0xffffffffu, gv[i], q);
+        const int ai = __shfl_sync(0xffffffffu, av[i], q);
+        if (gi != 0.0f) {
+#pragma unroll
+          for (int j = 0; j < KW; ++j) {
+            const float2 x = Pair<T>::ld(xs + static_cast<int64_t>(ai + j) * Dpad);
+            acc[i][j].x = fmaf(gi, x.x, acc[i][j].x);
+            acc[i][j].y = fmaf(gi, x.y, acc[i][j].y);
+          }
         }
       }
     }
@@ -95,52 +104,73 @@ __global__ void conv_bwd_dw_reduce_kernel(const float* __restrict__ part, int n_
   dW[(static_cast<int64_t>(j) * D + c) * F + f] = s;
 }
 
-// one warp per output row (s, t); lane owns columns {2*lane + 64*p, +1}, p < Dpad/64
+// dX: one CTA per (sequence, chunk of DX_ROWS output rows).  The CTA first turns the sequence's F
+// (arg-max, gradient) pairs into a bitmap  position -> set of filters  in shared memory (atomicOr:
+// the RESULT is order independent), then each warp produces whole output rows: for row t and window
+// offset j it walks the set bits of position t-j in ascending filter order and accumulates
+// g * Wt[f, j, :] -- a fixed order, no floating-point atomics, every row written exactly once.
+constexpr int DX_ROWS = 128;
+constexpr int DX_MAXF = 512;                    // filters per window supported by the bitmap (16 words)
+constexpr int DX_WORDS = DX_MAXF / 32;
+
 template <typename T>
 __global__ void __launch_bounds__(256)
-conv_bwd_dx_kernel(const T* __restrict__ Wt, int k, int Dpad, int64_t n_rows, int L,
+conv_bwd_dx_kernel(const T* __restrict__ Wt, int k, int Dpad, int L, int chunks_per_seq,
                    const float* __restrict__ G, const int32_t* __restrict__ A, int ldp, int col0, int F,
                    float* __restrict__ dX, int accumulate) {
+  __shared__ float s_g[DX_MAXF];
+  __shared__ unsigned s_bits[(DX_ROWS + 8) * DX_WORDS];     // positions t0-(k-1) .. t0+DX_ROWS-1, k <= 8
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
-  const int64_t r = static_cast<int64_t>(blockIdx.x) * 8 + warp;
-  if (r >= n_rows) return;
-  const int64_t s = r / L;
-  const int t = static_cast<int>(r - s * L);
+  const int64_t s = blockIdx.x / chunks_per_seq;
+  const int t0 = (blockIdx.x % chunks_per_seq) * DX_ROWS;
+  const int nwords = (F + 31) / 32;
+  const int pos_lo = t0 - (k - 1);                           // first window start that can touch this chunk
+  const int npos = DX_ROWS + k - 1;
+  for (int i = threadIdx.x; i < npos * nwords; i += blockDim.x) s_bits[i] = 0u;
+  __syncthreads();
+  for (int f = threadIdx.x; f < F; f += blockDim.x) {
+    const float g = __ldg(G + s * ldp + col0 + f);
+    const int a = __ldg(A + s * ldp + col0 + f);
+    s_g[f] = g;
+    const int p = a - pos_lo;
+    if (g != 0.0f && p >= 0 && p < npos) atomicOr(&s_bits[p * nwords + (f >> 5)], 1u << (f & 31));
+  }
+  __syncthreads();
   const int np = Dpad / 64;
   const int64_t K = static_cast<int64_t>(k) * Dpad;
-  float2 acc[8];
+  const int rows = (L - t0 < DX_ROWS) ? L - t0 : DX_ROWS;
+  for (int r = warp; r < rows; r += 8) {
+    float2 acc[8];
 #pragma unroll
-  for (int p = 0; p < 8; ++p) acc[p] = make_float2(0.f, 0.f);
-  for (int fb = 0; fb < F; fb += 32) {
-    const int f = fb + lane;
-    float g = 0.0f; int a = -0x40000000;
-    if (f < F) { g = __ldg(G + s * ldp + col0 + f); a = __ldg(A + s * ldp + col0 + f); }
-    const int j = t - a;                       // window offset that lands on this row
-    const bool hit = (g != 0.0f) && j >= 0 && j < k;
-    unsigned m = __ballot_sync(0xffffffffu, hit);
-    while (m) {
-      const int src = __ffs(m) - 1;
-      m &= m - 1;
-      const float gs = __shfl_sync(0xffffffffu, g, src);
-      const int js = __shfl_sync(0xffffffffu, j, src);
-      const T* w = Wt + static_cast<int64_t>(fb + src) * K + static_cast<int64_t>(js) * Dpad + lane * 2;
+    for (int p = 0; p < 8; ++p) acc[p] = make_float2(0.f, 0.f);
+    for (int j = 0; j < k; ++j) {
+      const unsigned* bits = s_bits + (r + (k - 1) - j) * nwords;      // position t - j
+      for (int w = 0; w < nwords; ++w) {
+        unsigned m = bits[w];
+        while (m) {
+          const int f = w * 32 + __ffs(m) - 1;
+          m &= m - 1;
+          const float g = s_g[f];
+          const T* wrow = Wt + static_cast<int64_t>(f) * K + static_cast<int64_t>(j) * Dpad + lane * 2;
 #pragma unroll
-      for (int p = 0; p < 8; ++p) {
-        if (p < np) {
-          const float2 x = Pair<T>::ld(w + p * 64);
-          acc[p].x = fmaf(gs, x.x, acc[p].x);
-          acc[p].y = fmaf(gs, x.y, acc[p].y);
+          for (int p = 0; p < 8; ++p) {
+            if (p < np) {
+              const float2 x = Pair<T>::ld(wrow + p * 64);
+              acc[p].x = fmaf(g, x.x, acc[p].x);
+              acc[p].y = fmaf(g, x.y, acc[p].y);
+            }
+          }
         }
       }
     }
-  }
-  float* dst = dX + r * Dpad + lane * 2;
+    float* dst = dX + (s * L + t0 + r) * Dpad + lane * 2;
 #pragma unroll
-  for (int p = 0; p < 8; ++p) {
-    if (p < np) {
-      float2 v = acc[p];
-      if (accumulate) { const float2 o = *reinterpret_cast<const float2*>(dst + p * 64); v.x += o.x; v.y += o.y; }
-      *reinterpret_cast<float2*>(dst + p * 64) = v;
+    for (int p = 0; p < 8; ++p) {
+      if (p < np) {
+        float2 v = acc[p];
+        if (accumulate) { const float2 o = *reinterpret_cast<const float2*>(dst + p * 64); v.x += o.x; v.y += o.y; }
+        *reinterpret_cast<float2*>(dst + p * 64) = v;
+      }
     }
   }
 }
@@ -187,7 +217,8 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
                        float* dW_ref, float* db, float* dX, int first_window,
                        void* ws, size_t ws_bytes, void* stream) {
   CLSM_REQUIRE(dtype == CLSM_BF16 || dtype == CLSM_F32, "conv_pool_bwd: bad dtype");
-  CLSM_REQUIRE(S > 0 && L >= k && k >= 1 && k <= 7 && F >= 1 && Fpad >= F, "conv_pool_bwd: bad sizes (k must be 1..7)");
+  CLSM_REQUIRE(S > 0 && L >= k && k >= 1 && k <= 7 && F >= 1 && Fpad >= F && F <= DX_MAXF, "conv_pool_bwd: bad sizes (k must be 1..7, F <= 512)");
+  CLSM_REQUIRE(S * ((L + DX_ROWS - 1) / DX_ROWS) < (1ll << 31), "conv_pool_bwd: too many sequences for one launch");
   CLSM_REQUIRE(Dpad == (D + 63) / 64 * 64 && Dpad <= 512, "conv_pool_bwd: Dpad must be D rounded up to 64 and <= 512");
   CLSM_REQUIRE(ldp >= col0 + F, "conv_pool_bwd: G row too short");
   if (ws_bytes < clsm_conv_bwd_workspace_bytes(S, k, D, F)) {
@@ -213,12 +244,12 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
   CLSM_LAUNCH_CHECK();
   if (clsm_colsum(G, S, ldp, col0, F, db, cs, kColsumChunks, st) != CLSM_OK) { clsm_set_error("conv_pool_bwd: colsum launch failed"); return CLSM_ECUDA; }
 
-  const int64_t n_rows = S * L;
-  const unsigned gx = static_cast<unsigned>(ceil_div64(n_rows, 8));
+  const int cps = (L + DX_ROWS - 1) / DX_ROWS;
+  const unsigned gx = static_cast<unsigned>(S * cps);
   if (dtype == CLSM_BF16)
-    conv_bwd_dx_kernel<__nv_bfloat16><<<gx, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(Wt), k, Dpad, n_rows, L, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1);
+    conv_bwd_dx_kernel<__nv_bfloat16><<<gx, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(Wt), k, Dpad, L, cps, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1);
   else
-    conv_bwd_dx_kernel<float><<<gx, 256, 0, st>>>(static_cast<const float*>(Wt), k, Dpad, n_rows, L, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1);
+    conv_bwd_dx_kernel<float><<<gx, 256, 0, st>>>(static_cast<const float*>(Wt), k, Dpad, L, cps, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1);
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
 }

@@ -70,7 +70,7 @@ seg_reduce_l0_kernel(const int32_t* __restrict__ spos, const int32_t* __restrict
     while (e1 < cnt && s_seg[e1] == g) ++e1;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (active) {
-      for (int q = e; q < e1; ++q) {
+      auto fetch = [&](int q) {
         const int64_t row = s_pos[q];
         float4 v = __ldg(dX + row * ldx4 + col);
         if (DROPOUT) {
@@ -82,6 +82,18 @@ seg_reduce_l0_kernel(const int32_t* __restrict__ spos, const int32_t* __restrict
           v.z = dropout_keep(bytes, o + 2, thr) ? v.z * inv_keep : 0.f;
           v.w = dropout_keep(bytes, o + 3, thr) ? v.w * inv_keep : 0.f;
         }
+        return v;
+      };
+      int q = e;
+      for (; q + 4 <= e1; q += 4) {            // 4 independent row loads in flight, added in order
+        const float4 v0 = fetch(q), v1 = fetch(q + 1), v2 = fetch(q + 2), v3 = fetch(q + 3);
+        acc.x += v0.x; acc.y += v0.y; acc.z += v0.z; acc.w += v0.w;
+        acc.x += v1.x; acc.y += v1.y; acc.z += v1.z; acc.w += v1.w;
+        acc.x += v2.x; acc.y += v2.y; acc.z += v2.z; acc.w += v2.w;
+        acc.x += v3.x; acc.y += v3.y; acc.z += v3.z; acc.w += v3.w;
+      }
+      for (; q < e1; ++q) {
+        const float4 v = fetch(q);
         acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       }
     }

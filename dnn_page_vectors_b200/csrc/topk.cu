@@ -115,13 +115,21 @@ topk_score_kernel(const float* __restrict__ Qn, int64_t nQ, const float* __restr
   for (int i = 0; i < KPT; ++i) {
     const int64_t row = row0 + tid + i * TPB;
     if (row < N) {
-      const float4* c4 = reinterpret_cast<const float4*>(Cn + row * H);
-      for (int h = 0; h < H / 4; ++h) {
-        const float4 c = __ldg(c4 + h);
+      if ((H & 3) == 0) {
+        const float4* c4 = reinterpret_cast<const float4*>(Cn + row * H);
+        for (int h = 0; h < H / 4; ++h) {
+          const float4 c = __ldg(c4 + h);
 #pragma unroll
-        for (int q = 0; q < QG; ++q) {
-          const float4 w = *reinterpret_cast<const float4*>(s_q + q * H + h * 4);
-          sc[i][q] = fmaf(c.x, w.x, fmaf(c.y, w.y, fmaf(c.z, w.z, fmaf(c.w, w.w, sc[i][q]))));
+          for (int q = 0; q < QG; ++q) {
+            const float4 w = *reinterpret_cast<const float4*>(s_q + q * H + h * 4);
+            sc[i][q] = fmaf(c.x, w.x, fmaf(c.y, w.y, fmaf(c.z, w.z, fmaf(c.w, w.w, sc[i][q]))));
+          }
+        }
+      } else {
+        for (int h = 0; h < H; ++h) {
+          const float c = __ldg(Cn + row * H + h);
+#pragma unroll
+          for (int q = 0; q < QG; ++q) sc[i][q] = fmaf(c, s_q[q * H + h], sc[i][q]);
         }
       }
     }
@@ -217,7 +225,7 @@ size_t clsm_cos_topk_workspace_bytes(int64_t nQ, int64_t N, int k) {
 int clsm_cos_topk(const float* Qn, int64_t nQ, const float* Cn, int64_t N, int H, int k,
                   int64_t id_base, float* out_score, int64_t* out_id,
                   void* ws, size_t ws_bytes, void* stream) {
-  CLSM_REQUIRE(nQ > 0 && N > 0 && N < (1ll << 32) && H > 0 && H % 4 == 0, "cos_topk: bad sizes (H must be a multiple of 4)");
+  CLSM_REQUIRE(nQ > 0 && N > 0 && N < (1ll << 32) && H > 0, "cos_topk: bad sizes");
   CLSM_REQUIRE(k >= 1 && k <= KMAX, "cos_topk: k must be in [1, %d]", KMAX);
   CLSM_REQUIRE(static_cast<size_t>(QG) * H * 4 <= 40 * 1024, "cos_topk: H too large");
   if (ws_bytes < clsm_cos_topk_workspace_bytes(nQ, N, k)) {

@@ -23,12 +23,14 @@ def test_gather_bit_exact(bf16, D):
     tok[:5] = [0, V1 - 1, 0, V1 - 1, 7]
     if bf16:
         table = torch.zeros((V1, Dpad), dtype=torch.bfloat16, device=DEV)
-        call("clsm_table_to_bf16", P(dev(E)), V1, D, P(table), Dpad, ST())
+        E_d = dev(E)
+        call("clsm_table_to_bf16", P(E_d), V1, D, P(table), Dpad, ST())
         ld, ref = Dpad, bf16_round(E)
     else:
         table, ld, ref = dev(E), D, E
     X = torch.full((n_tok, Dpad), 7.0, dtype=table.dtype, device=DEV)
-    call("clsm_emb_gather", P(dev(tok)), n_tok, P(table), V1, D, ld, BF16 if bf16 else F32, P(X), Dpad, 1.0, 0, ST())
+    tok_d = dev(tok)
+    call("clsm_emb_gather", P(tok_d), n_tok, P(table), V1, D, ld, BF16 if bf16 else F32, P(X), Dpad, 1.0, 0, ST())
     got = X.float().cpu().numpy()
     np.testing.assert_array_equal(got[:, :D], ref[tok])
     assert (got[:, D:] == 0).all()
@@ -41,7 +43,8 @@ def test_gather_host_ids_entry_point():
     tok_h = torch.as_tensor(rng.randint(0, V1, size=n_tok).astype(np.int32)).pin_memory()
     tok_d = torch.empty(n_tok, dtype=torch.int32, device=DEV)
     X = torch.empty((n_tok, 64), dtype=torch.float32, device=DEV)
-    call("clsm_emb_gather_h", tok_h.data_ptr(), P(tok_d), n_tok, P(dev(E)), V1, D, D, F32, P(X), 64, 1.0, 0, ST())
+    E_d = dev(E)
+    call("clsm_emb_gather_h", tok_h.data_ptr(), P(tok_d), n_tok, P(E_d), V1, D, D, F32, P(X), 64, 1.0, 0, ST())
     np.testing.assert_array_equal(X.cpu().numpy(), E[tok_h.numpy()])
 
 
@@ -59,12 +62,14 @@ def test_gather_dropout_matches_exported_mask(bf16):
     assert abs(m[:, 0].mean() - keep) < 0.05 and abs(m[0].mean() - keep) < 0.15
     if bf16:
         table = torch.zeros((V1, Dpad), dtype=torch.bfloat16, device=DEV)
-        call("clsm_table_to_bf16", P(dev(E)), V1, D, P(table), Dpad, ST())
+        E_d = dev(E)
+        call("clsm_table_to_bf16", P(E_d), V1, D, P(table), Dpad, ST())
         src, ld = bf16_round(E), Dpad
     else:
         table, src, ld = dev(E), E, D
     X = torch.empty((n_tok, Dpad), dtype=table.dtype, device=DEV)
-    call("clsm_emb_gather", P(dev(tok)), n_tok, P(table), V1, D, ld, BF16 if bf16 else F32, P(X), Dpad, keep, seed, ST())
+    tok_d = dev(tok)
+    call("clsm_emb_gather", P(tok_d), n_tok, P(table), V1, D, ld, BF16 if bf16 else F32, P(X), Dpad, keep, seed, ST())
     want = src[tok] * m * np.float32(1.0 / keep)
     if bf16:
         want = bf16_round(want)
@@ -158,7 +163,8 @@ def test_pool_finalize(act):
     _, _, keys = run_conv(X, W, False, "simt")
     pooled = torch.empty((5, 24), dtype=torch.float32, device=DEV)
     am = torch.empty((5, 24), dtype=torch.int32, device=DEV)
-    call("clsm_pool_finalize", P(keys), 5, 24, 24, P(dev(b, torch.float32)), _lib.ACT[act], P(pooled), P(am), 24, ST())
+    b_d = dev(b, torch.float32)
+    call("clsm_pool_finalize", P(keys), 5, 24, 24, P(b_d), _lib.ACT[act], P(pooled), P(am), 24, ST())
     op, oa = O.conv_pool_fwd(X, W, b, act)
     np.testing.assert_allclose(pooled.cpu().numpy(), op, rtol=1e-5, atol=1e-6)
     np.testing.assert_array_equal(am.cpu().numpy(), oa)
@@ -184,7 +190,8 @@ def test_dense_fwd_bwd(S, Pn, H, act):
     dWd = torch.empty((Pn, H), dtype=torch.float32, device=DEV)
     dbd = torch.empty(H, dtype=torch.float32, device=DEV)
     G = torch.empty((S, Pn), dtype=torch.float32, device=DEV)
-    call("clsm_dense_bwd", P(pd_), P(sem), P(dev(dsem, torch.float32)), S, Pn, Pn, P(wd_), H, _lib.ACT[act],
+    dsem_d = dev(dsem, torch.float32)
+    call("clsm_dense_bwd", P(pd_), P(sem), P(dsem_d), S, Pn, Pn, P(wd_), H, _lib.ACT[act],
          P(dWd), P(dbd), P(G), P(ws), ws_bytes, ST())
     semn = sem.cpu().numpy().astype(np.float64)
     dpre = dsem * O.act_grad_from_output(semn, act)
@@ -218,7 +225,7 @@ def test_sim_loss_fwd_bwd(B, J, H):
     assert (c[0] == 0.0).all() and np.isfinite(gq.cpu().numpy()).all()
     np.testing.assert_allclose(c, fw["cos"], rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(prob.cpu().numpy(), fw["prob"], rtol=1e-4, atol=1e-7)
-    np.testing.assert_allclose(la.cpu().numpy(), [fw["loss"], fw["acc"]], rtol=1e-5)
+    np.testing.assert_allclose(la.cpu().numpy(), [fw["loss"], fw["acc"]], rtol=1e-5, atol=2e-7)   # 1-1e-7 is not an fp32 number
     # rows whose cosine sits exactly on a clip edge may legitimately differ in the gate
     edge = (np.abs(fw["raw"] - 1.0) < 1e-6) | (np.abs(fw["raw"]) < 1e-9)
     keep_rows = ~edge.any(axis=1)
@@ -248,7 +255,8 @@ def test_conv_pool_bwd(bf16, shape):
     dW = torch.empty((k, D, F), dtype=torch.float32, device=DEV)
     db = torch.empty(F, dtype=torch.float32, device=DEV)
     dX = torch.full((S * L, Dpad), 3.0, dtype=torch.float32, device=DEV)
-    args = (P(Xd), BF16 if bf16 else F32, S, L, D, Dpad, P(Wt), k, F, Fpad, P(dev(G, torch.float32)), P(dev(A)), Pn, col0,
+    G_d, A_d = dev(G, torch.float32), dev(A)        # keep the device buffers alive across the calls
+    args = (P(Xd), BF16 if bf16 else F32, S, L, D, Dpad, P(Wt), k, F, Fpad, P(G_d), P(A_d), Pn, col0,
             P(dW), P(db), P(dX))
     call("clsm_conv_pool_bwd", *args, 1, P(ws), ws_bytes, ST())
     Gi, Ai = G[:, col0:col0 + F], A[:, col0:col0 + F].astype(np.int64)
@@ -329,9 +337,12 @@ def test_adam_dense_and_table():
     pd_, md_, vd_ = dev(p0, torch.float32), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
     for t in (1, 2, 3):
         O.adam_step(p, m, v, g * t, t)
-        call("clsm_adam_dense", P(pd_), P(md_), P(vd_), P(dev(g * t, torch.float32)), n, t, 1e-3, 0.9, 0.999, 1e-8, ST())
+        g_d = dev(g * t, torch.float32)
+        call("clsm_adam_dense", P(pd_), P(md_), P(vd_), P(g_d), n, t, 1e-3, 0.9, 0.999, 1e-8, ST())
+        torch.cuda.synchronize()
     np.testing.assert_allclose(pd_.cpu().numpy(), p, rtol=1e-5, atol=1e-6)
-    np.testing.assert_allclose(vd_.cpu().numpy(), v, rtol=1e-5, atol=1e-9)
+    # (1 - 0.999) evaluated in fp32, as Keras does on the device, is 1.00005e-3: 5e-5 relative on v
+    np.testing.assert_allclose(vd_.cpu().numpy(), v, rtol=1e-4, atol=1e-9)
 
     for D in (100, 30, 7):           # vectorised and scalar variants
         V1, Dpad = 50, rup(D, 64)
@@ -343,18 +354,19 @@ def test_adam_dense_and_table():
         copy = torch.full((V1, Dpad), 5.0, dtype=torch.bfloat16, device=DEV) if D % 4 == 0 else None
         p, m, v = E0.copy(), np.zeros((V1, D)), np.zeros((V1, D))
         gfull = np.zeros((V1, D)); gfull[ids] = rows[:, :D]
+        roi_d, rows_d, ids_d, cnt_d = dev(roi), dev(rows), dev(ids), dev(np.array([4], dtype=np.int32))
         for t in (1, 2):
             O.adam_step(p, m, v, gfull, t)
-            call("clsm_adam_table", P(Ed), P(Em), P(Ev), V1, D, P(dev(roi)), P(dev(rows)), Dpad, t,
+            call("clsm_adam_table", P(Ed), P(Em), P(Ev), V1, D, P(roi_d), P(rows_d), Dpad, t,
                  1e-3, 0.9, 0.999, 1e-8, P(copy), Dpad, ST())
         np.testing.assert_allclose(Ed.cpu().numpy(), p, rtol=1e-5, atol=1e-6)
-        assert np.abs(Ed.cpu().numpy()[0] - E0[0]).max() == 0          # zero-grad rows with m=v=0 stay put
+        assert np.abs(Ed.cpu().numpy()[0] - E0[0].astype(np.float32)).max() == 0   # zero-grad rows with m=v=0 stay put
         if copy is not None:
             np.testing.assert_array_equal(copy.float().cpu().numpy()[:, :D], bf16_round(Ed.cpu().numpy()))
         # lazy variant touches only the listed rows
         E2, m2, v2 = dev(E0, torch.float32), torch.zeros((V1, D), device=DEV), torch.zeros((V1, D), device=DEV)
-        call("clsm_adam_rows", P(E2), P(m2), P(v2), D, P(dev(ids)), P(dev(np.array([4], dtype=np.int32))), 4,
-             P(dev(rows)), Dpad, 1, 1e-3, 0.9, 0.999, 1e-8, P(None), Dpad, ST())
+        call("clsm_adam_rows", P(E2), P(m2), P(v2), D, P(ids_d), P(cnt_d), 4,
+             P(rows_d), Dpad, 1, 1e-3, 0.9, 0.999, 1e-8, P(None), Dpad, ST())
         pp, mm, vv = E0.copy(), np.zeros((V1, D)), np.zeros((V1, D))
         O.adam_step(pp, mm, vv, gfull, 1)
         np.testing.assert_allclose(E2.cpu().numpy(), pp, rtol=1e-5, atol=1e-6)
@@ -424,6 +436,7 @@ def test_normalize_rows():
     rng = np.random.RandomState(12)
     z = np.maximum(rng.randn(100, 128), 0).astype(np.float32); z[3] = 0
     out = torch.empty((100, 128), dtype=torch.float32, device=DEV)
-    call("clsm_normalize_rows", P(dev(z)), 100, 128, P(out), ST())
+    z_d = dev(z)
+    call("clsm_normalize_rows", P(z_d), 100, 128, P(out), ST())
     np.testing.assert_allclose(out.cpu().numpy(), O.normalise_rows(z.astype(np.float64)), rtol=1e-5, atol=1e-7)
     assert (out[3] == 0).all()

@@ -82,17 +82,43 @@ def test_fp32_training_trajectory_matches_oracle(cfg, act):
     # evaluation path first: loss and p0 on the initial weights
     l0, a0 = net.test_on_batch(x)
     assert abs(l0 - ol[0][0]) <= 1e-5 * max(1.0, abs(ol[0][0])) and abs(a0 - ol[0][1]) < 1e-6
+    q64, d64 = x[0].astype(np.int64), np.stack(x[1:], axis=1).astype(np.int64)
+    _, ogq, ogd, _, _ = O.model_loss_and_grads(q64, d64, pq, pd_, act=act)
     for t in range(steps):
         l, a = net.train_on_batch(x, np.ones(cfg["B"]))
         assert abs(l - ol[t][0]) <= 2e-5 * max(1.0, abs(ol[t][0])), (t, l, ol[t])
+        if t == 0:
+            # gradients of the first step, tensor by tensor.  One arg-max or ReLU-gate decision that
+            # falls the other way in fp32 changes a whole filter's column, so compare per filter and
+            # allow 1 % of filters to differ; everything else must agree to 1e-4 of the tensor's scale.
+            for tower, og in ((net.query_model, ogq), (net.doc_model, ogd)):
+                def close(got, want, axis_filter=-1):
+                    got, want = np.asarray(got, dtype=np.float64), np.asarray(want)
+                    scale = np.abs(want).max() + 1e-30
+                    bad = np.abs(got - want) > 1e-4 * scale
+                    per_filter = bad.reshape(-1, bad.shape[axis_filter]).any(axis=0) if bad.ndim > 1 else bad
+                    assert per_filter.mean() <= 0.01, per_filter.mean()
+                close(tower.g_Wd.cpu().numpy(), og["Wd"])
+                close(tower.g_bd.cpu().numpy(), og["bd"])
+                for i in range(len(tower.windows)):
+                    close(tower.g_convW[i].cpu().numpy(), og["convW"][i])
+                    close(tower.g_convb[i * tower.F:(i + 1) * tower.F].cpu().numpy(), og["convb"][i])
+                b = tower.buffers(cfg["B"] if tower is net.query_model else cfg["B"] * (1 + cfg["J"]), True)
+                n_u = int(b["n_uniq"].item())
+                ids = b["uniq"][:n_u].cpu().numpy()
+                rows = b["dE_rows"][:n_u, :tower.D].cpu().numpy().astype(np.float64)
+                want = og["E"][ids]
+                scale = np.abs(want).max()
+                assert (np.abs(rows - want) > 1e-4 * scale).any(axis=1).mean() <= 0.02
+                assert np.abs(np.delete(og["E"], ids, axis=0)).max() == 0.0
     w = net.get_weights()
     for tag, op in (("query", oq), ("doc", od)):
-        # Adam moves every weight by ~lr per step; compare the MOVEMENT, which is what gradients drive
-        np.testing.assert_allclose(w[tag]["Wd"], op["Wd"], atol=2e-5)
-        np.testing.assert_allclose(w[tag]["bd"], op["bd"], atol=2e-5)
-        np.testing.assert_allclose(w[tag]["convW0"], op["convW"][0], atol=2e-5)
-        np.testing.assert_allclose(w[tag]["convb0"], op["convb"][0], atol=2e-5)
-        np.testing.assert_allclose(w[tag]["E"], op["E"], atol=2e-5)
+        # after 3 Adam steps every weight has moved ~3e-3; Adam normalises the step, so a weight whose
+        # gradient differs (see above) can be off by a good part of that.  Bulk must agree to 2e-5.
+        for got, want in ((w[tag]["Wd"], op["Wd"]), (w[tag]["bd"], op["bd"]), (w[tag]["convW0"], op["convW"][0]),
+                          (w[tag]["convb0"], op["convb"][0]), (w[tag]["E"], op["E"])):
+            err = np.abs(got - want)
+            assert err.max() < 7e-3 and (err > 2e-5).mean() < 2e-2, (tag, err.max(), (err > 2e-5).mean())
 
 
 def test_bf16_forward_and_loss_within_tolerance():
