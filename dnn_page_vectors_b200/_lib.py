@@ -35,7 +35,7 @@ SIGNATURES = {
     "clsm_dense_bwd_workspace_bytes": (sz, [i64, i32, i32]),
     "clsm_dense_bwd": (i32, [vp, vp, vp, i64, i32, i32, vp, i32, i32, vp, vp, vp, vp, sz, vp]),
     "clsm_sim_loss": (i32, [vp, vp, i64, i32, i32, f32, i64, vp, vp, vp, vp, vp, vp]),
-    "clsm_conv_bwd_workspace_bytes": (sz, [i64, i32, i32, i32]),
+    "clsm_conv_bwd_workspace_bytes": (sz, [i64, i32, i32, i32, i32]),
     "clsm_conv_pool_bwd": (i32, [vp, i32, i64, i32, i32, i32, vp, i32, i32, i32, vp, vp, i32, i32,
                                  vp, vp, vp, i32, vp, sz, vp]),
     "clsm_emb_scatter_workspace_bytes": (sz, [i64, i32]),

@@ -11,6 +11,12 @@
 int clsm_colsum(const float* A, int64_t rows, int ld, int col0, int n, float* out, float* part,
                 int n_chunks, cudaStream_t st);   // dense.cu
 
+int clsm_conv_bwd_dw_fast(const void* X, int dtype, int L, int Dpad, int64_t S, int n_groups, const float* G,
+                          const int32_t* A, int ldp, int col0, int F, int k, float* part, cudaStream_t st);   // conv_bwd_fast.cu
+size_t clsm_conv_bwd_dx_fast_bytes(int64_t S, int L, int F);
+int clsm_conv_bwd_dx_fast(const void* Wt, int dtype, int k, int Dpad, int L, int64_t S, const float* G, const int32_t* A,
+                          int ldp, int col0, int F, float* dX, int accumulate, void* scratch, cudaStream_t st);
+
 namespace {
 
 constexpr int FPW = 4;            // filters per warp
@@ -176,7 +182,9 @@ conv_bwd_dx_kernel(const T* __restrict__ Wt, int k, int Dpad, int L, int chunks_
 }
 
 int dw_groups(int64_t S, int Dpad, int F) {
-  const int per = (Dpad / 64) * ((F + FT - 1) / FT);
+  // sized for the coarser of the two dW tilings (generic: 128 filters / CTA, staged: 160) so that
+  // both fit the same partial-sum workspace
+  const int per = (Dpad / 64) * ((F + 160 - 1) / 160);
   int64_t g = (4 * static_cast<int64_t>(clsm_sm_count()) + per - 1) / per;
   if (g > S) g = S;
   if (g < 1) g = 1;
@@ -204,11 +212,11 @@ int launch_dw(const T* X, int L, int Dpad, int64_t S, int64_t spg, const float* 
 
 extern "C" {
 
-size_t clsm_conv_bwd_workspace_bytes(int64_t S, int k, int D, int F) {
+size_t clsm_conv_bwd_workspace_bytes(int64_t S, int L, int k, int D, int F) {
   const int Dpad = (D + 63) / 64 * 64;
   const size_t part = align_up(static_cast<size_t>(dw_groups(S, Dpad, F)) * F * k * Dpad * 4, 256);
   const size_t cs = align_up(static_cast<size_t>(kColsumChunks) * F * 4, 256);
-  return part + cs;
+  return part + cs + clsm_conv_bwd_dx_fast_bytes(S, L, F);
 }
 
 int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
@@ -221,8 +229,8 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
   CLSM_REQUIRE(S * ((L + DX_ROWS - 1) / DX_ROWS) < (1ll << 31), "conv_pool_bwd: too many sequences for one launch");
   CLSM_REQUIRE(Dpad == (D + 63) / 64 * 64 && Dpad <= 512, "conv_pool_bwd: Dpad must be D rounded up to 64 and <= 512");
   CLSM_REQUIRE(ldp >= col0 + F, "conv_pool_bwd: G row too short");
-  if (ws_bytes < clsm_conv_bwd_workspace_bytes(S, k, D, F)) {
-    clsm_set_error("conv_pool_bwd: workspace too small (%zu < %zu)", ws_bytes, clsm_conv_bwd_workspace_bytes(S, k, D, F));
+  if (ws_bytes < clsm_conv_bwd_workspace_bytes(S, L, k, D, F)) {
+    clsm_set_error("conv_pool_bwd: workspace too small (%zu < %zu)", ws_bytes, clsm_conv_bwd_workspace_bytes(S, L, k, D, F));
     return CLSM_EWORKSPACE;
   }
   cudaStream_t st = as_stream(stream);
@@ -232,18 +240,28 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
   float* part = reinterpret_cast<float*>(w);
   w += align_up(static_cast<size_t>(n_groups) * F * k * Dpad * 4, 256);
   float* cs = reinterpret_cast<float*>(w);
+  w += align_up(static_cast<size_t>(kColsumChunks) * F * 4, 256);
+  void* sort_scratch = w;
 
-  dim3 grid(n_groups, Dpad / 64, (F + FT - 1) / FT);
-  int rc = dtype == CLSM_BF16
-      ? launch_dw<__nv_bfloat16>(static_cast<const __nv_bfloat16*>(X), L, Dpad, S, spg, G, argmax, ldp, col0, F, k, part, grid, st)
-      : launch_dw<float>(static_cast<const float*>(X), L, Dpad, S, spg, G, argmax, ldp, col0, F, k, part, grid, st);
-  if (rc != CLSM_OK) { clsm_set_error("conv_pool_bwd: unsupported window %d", k); return rc; }
-  CLSM_LAUNCH_CHECK();
+  int rc = clsm_conv_bwd_dw_fast(X, dtype, L, Dpad, S, n_groups, G, argmax, ldp, col0, F, k, part, st);
+  if (rc == CLSM_EUNSUPPORTED) {            // shape outside the shared-memory plan: generic kernel
+    dim3 grid(n_groups, Dpad / 64, (F + FT - 1) / FT);
+    rc = dtype == CLSM_BF16
+        ? launch_dw<__nv_bfloat16>(static_cast<const __nv_bfloat16*>(X), L, Dpad, S, spg, G, argmax, ldp, col0, F, k, part, grid, st)
+        : launch_dw<float>(static_cast<const float*>(X), L, Dpad, S, spg, G, argmax, ldp, col0, F, k, part, grid, st);
+    if (rc != CLSM_OK) { clsm_set_error("conv_pool_bwd: unsupported window %d", k); return rc; }
+    CLSM_LAUNCH_CHECK();
+  } else if (rc != CLSM_OK) {
+    return rc;
+  }
   const int64_t ne = static_cast<int64_t>(k) * D * F;
   conv_bwd_dw_reduce_kernel<<<static_cast<unsigned>(ceil_div64(ne, 256)), 256, 0, st>>>(part, n_groups, k, D, Dpad, F, dW_ref);
   CLSM_LAUNCH_CHECK();
   if (clsm_colsum(G, S, ldp, col0, F, db, cs, kColsumChunks, st) != CLSM_OK) { clsm_set_error("conv_pool_bwd: colsum launch failed"); return CLSM_ECUDA; }
 
+  rc = clsm_conv_bwd_dx_fast(Wt, dtype, k, Dpad, L, S, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1, sort_scratch, st);
+  if (rc == CLSM_OK) return CLSM_OK;
+  if (rc != CLSM_EUNSUPPORTED) return rc;
   const int cps = (L + DX_ROWS - 1) / DX_ROWS;
   const unsigned gx = static_cast<unsigned>(S * cps);
   if (dtype == CLSM_BF16)

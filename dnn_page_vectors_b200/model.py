@@ -169,7 +169,7 @@ class Tower(object):
             b["row_of_id"] = torch.empty(self.V1, dtype=torch.int32, device=dev)
             ws = max(
                 lib.clsm_dense_bwd_workspace_bytes(S, self.P, self.H),
-                max(lib.clsm_conv_bwd_workspace_bytes(S, k, self.D, self.F) for k in self.windows),
+                max(lib.clsm_conv_bwd_workspace_bytes(S, self.L, k, self.D, self.F) for k in self.windows),
                 lib.clsm_emb_scatter_workspace_bytes(n_tok, self.D))
             b["ws"] = torch.empty(ws, dtype=torch.uint8, device=dev)
             b["ws_bytes"] = ws

@@ -111,7 +111,7 @@ int clsm_sim_loss(const float* semQ, const float* semD, int64_t B, int J, int H,
  *   dW_ref (k, D, F) fp32 = sum_s G[s,f] X[s, a+j, c];  db (F) = sum_s G[s,f]
  *   dX (S*L, Dpad) fp32 += / = sum_{f,j: a+j==t} G[s,f] W[j,c,f]
  * first_window != 0 overwrites dX, otherwise accumulates (several window sizes). */
-size_t clsm_conv_bwd_workspace_bytes(int64_t S, int k, int D, int F);
+size_t clsm_conv_bwd_workspace_bytes(int64_t S, int L, int k, int D, int F);
 int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
                        const void* Wt, int k, int F, int Fpad,
                        const float* G, const int32_t* argmax, int ldp, int col0,

@@ -236,7 +236,7 @@ def test_sim_loss_fwd_bwd(B, J, H):
 # ------------------------------------------------------------------ conv backward
 @pytest.mark.parametrize("bf16", [False, True])
 @pytest.mark.parametrize("shape", [(5, 20, 100, 3, 150), (9, 12, 64, 2, 20), (3, 100, 300, 3, 300), (4, 30, 100, 5, 130),
-                                   (6, 9, 40, 1, 17)])
+                                   (6, 9, 40, 1, 17), (2, 1100, 64, 3, 40), (3, 500, 100, 4, 150), (70, 100, 300, 3, 300)])
 def test_conv_pool_bwd(bf16, shape):
     S, L, D, k, F = shape
     rng = np.random.RandomState(6)
@@ -250,7 +250,7 @@ def test_conv_pool_bwd(bf16, shape):
     A[:, col0:col0 + F] = rng.randint(0, L - k + 1, size=(S, F))
     A[0, col0:col0 + F] = 0; A[1, col0:col0 + F] = L - k                  # edges
     Xd, Wt = make_X(X, Dpad, bf16), pack_w(W, Dpad, Fpad, bf16)
-    ws_bytes = lib.clsm_conv_bwd_workspace_bytes(S, k, D, F)
+    ws_bytes = lib.clsm_conv_bwd_workspace_bytes(S, L, k, D, F)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
     dW = torch.empty((k, D, F), dtype=torch.float32, device=DEV)
     db = torch.empty(F, dtype=torch.float32, device=DEV)
