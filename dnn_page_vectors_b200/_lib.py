@@ -49,6 +49,7 @@ SIGNATURES = {
     "clsm_cos_topk": (i32, [vp, i64, vp, i64, i32, i32, i64, vp, vp, vp, sz, vp]),
     "clsm_topk_merge_workspace_bytes": (sz, [i32, i64, i32]),
     "clsm_topk_merge": (i32, [vp, vp, i32, i64, i32, vp, vp, vp, sz, vp]),
+    "clsm_topk_merge_static": (i32, [vp, vp, i32, i64, i32, vp, vp, vp]),
 }
 
 

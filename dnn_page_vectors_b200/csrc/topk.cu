@@ -7,6 +7,7 @@
 // candidates a CTA holds in registers, then a bitonic sort of the k survivors; levels repeat on
 // the survivors until one list per query is left.
 #include "common.cuh"
+#include <mutex>
 
 namespace {
 
@@ -273,6 +274,54 @@ int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_
   topk_decode_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(buf[src], n, 0, out_score, out_id);
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
+}
+
+// ---- clsm_topk_merge_static: the same merge, for callers that must not allocate ---------------------
+// Built-in scratch.  It lives in every GPU context that loads this library, from load until the process
+// exits, so it is kept small (CLSM_TOPK_MERGE_STATIC_MAX_BYTES = 2 MiB: e.g. 8 shards x 128 queries x
+// k=100 needs 0.9 MiB).  In host code the NAME of a __device__ array is only a host-side stand-in and
+// must never be handed to a kernel; its real device address comes from cudaGetSymbolAddress below.
+static __device__ __align__(256) unsigned char g_topk_merge_scratch[CLSM_TOPK_MERGE_STATIC_MAX_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kMaxDevices];          // device address of g_topk_merge_scratch, per device ordinal
+
+// One-time set-up for the CURRENT device: resolve the array's device address and remember it.
+int topk_merge_static_setup(void** out) {
+  int dev = -1;
+  CLSM_CUDA(cudaGetDevice(&dev));
+  CLSM_REQUIRE(dev >= 0 && dev < kMaxDevices, "topk_merge_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (g_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    CLSM_CUDA(cudaGetSymbolAddress(&p, g_topk_merge_scratch));      // device `dev` is current here
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return CLSM_OK;
+}
+}  // namespace
+
+int clsm_topk_merge_static(const float* scores, const int64_t* ids, int n_parts, int64_t nQ, int k,
+                           float* out_score, int64_t* out_id, void* stream) {
+  CLSM_REQUIRE(n_parts >= 1 && nQ > 0 && k >= 1 && k <= KMAX, "topk_merge_static: bad sizes");
+  const size_t need = clsm_topk_merge_workspace_bytes(n_parts, nQ, k);
+  if (need > static_cast<size_t>(CLSM_TOPK_MERGE_STATIC_MAX_BYTES)) {
+    clsm_set_error("topk_merge_static: %d lists x %lld queries x k=%d needs %zu bytes of scratch but the built-in "
+                   "array holds %d; call clsm_topk_merge with a caller-provided workspace instead",
+                   n_parts, static_cast<long long>(nQ), k, need, CLSM_TOPK_MERGE_STATIC_MAX_BYTES);
+    return CLSM_EWORKSPACE;
+  }
+  void* scratch = nullptr;
+  const int rc = topk_merge_static_setup(&scratch);
+  if (rc != CLSM_OK) return rc;
+  // Every byte the merge kernels read from the scratch is written earlier in the same call (the key
+  // encoding pass fills level 0 completely, each level fills the next), so nothing has to start at zero
+  // even though the array still holds the previous call's keys.
+  return clsm_topk_merge(scores, ids, n_parts, nQ, k, out_score, out_id, scratch,
+                         static_cast<size_t>(CLSM_TOPK_MERGE_STATIC_MAX_BYTES), stream);
 }
 
 }  // extern "C"

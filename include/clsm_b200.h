@@ -166,6 +166,27 @@ size_t clsm_topk_merge_workspace_bytes(int n_parts, int64_t nQ, int k);
 int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_t nQ, int k,
                     float* out_score, int64_t* out_id, void* ws, size_t ws_bytes, void* stream);
 
+/* clsm_topk_merge_static: clsm_topk_merge without a workspace argument and without any allocation.
+ * (No counterpart in the reference, which has no retrieval code at all.)
+ * Who needs it: a caller that is not allowed to obtain device memory at the moment it has to merge --
+ * a per-request handler inside an inference server whose rules forbid allocating on the request path
+ * (a device allocation can stall every stream of the process), or a host that has already given all
+ * free HBM to its own pool and has no raw workspace left to lend.  Such a caller still passes the input
+ * lists and the output buffers; only the scratch comes from the library: a fixed array of
+ * CLSM_TOPK_MERGE_STATIC_MAX_BYTES that every GPU loading the library carries until the process ends.
+ *  - Sizes whose scratch need (clsm_topk_merge_workspace_bytes) exceeds that limit are refused with
+ *    CLSM_EWORKSPACE and a message naming both numbers; use clsm_topk_merge for those.
+ *  - The first call on each device looks up the array's device address (once, with that device
+ *    current).  Make that first call during start-up, before any stream capture is begun.
+ *  - All calls on a device share the one array.  Two calls whose kernels can overlap on the GPU (two
+ *    streams, two threads) race on it; serialise them on one stream.  Nothing needs clearing between
+ *    calls: each call overwrites what it later reads.
+ *  - Calls neither cudaMalloc/cudaFree nor any allocating library routine.  Results are identical to
+ *    clsm_topk_merge on the same inputs. */
+#define CLSM_TOPK_MERGE_STATIC_MAX_BYTES (2 * 1024 * 1024)
+int clsm_topk_merge_static(const float* scores, const int64_t* ids, int n_parts, int64_t nQ, int k,
+                           float* out_score, int64_t* out_id, void* stream);
+
 /* ---- host-buffer convenience (the e2e / drop-in call): ids on the HOST ------------------------
  * Copies tok_h (pinned or pageable) to tok_d on `stream`, then clsm_emb_gather. */
 int clsm_emb_gather_h(const int32_t* tok_h, int32_t* tok_d, int64_t n_tok, const void* table,
