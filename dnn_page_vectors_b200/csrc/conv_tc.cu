@@ -1,40 +1,52 @@
 // n-gram window convolution + max over time on the 5th-generation tensor cores (sm_100a).
 //   replaces Convolution1D(valid) + MaxPooling1D + Flatten, dssm_cnn_v2/cnn_dssm_tf.py:84-100.
 //
-// Implicit GEMM, no im2col: the gathered token matrix X (S*L, Dpad) bf16 is tiled in 128 flat rows;
-// output row r = (s, t) needs input rows r .. r+k-1, so K-chunk (j, c) of the A operand is simply the
-// TMA box at row coordinate r0 + j, column c*64 of the SAME 2-D tensor map.  B = Wt (Fpad, k*Dpad)
-// K-major.  Accumulators (128 x Fpad fp32) live in TMEM; the epilogue reads them back 32 columns at a
-// time (tcgen05.ld 32x32b), takes the per-sequence max over the 32 time steps a warp owns with
-// CREDUX.MAX.F32 + a ballot for the first arg-max lane, and folds the result into the (S, P) key
-// array with one 64-bit atomicMax per (warp, sequence, filter).  Pre-activations never reach HBM.
+// Implicit GEMM, no im2col, computed TRANSPOSED:  D[f, t] = sum_{j,c} Wt[f, j*Dpad + c] * X[r0 + t + j, c].
+//   A operand = filter weights Wt (Fpad, k*Dpad) K-major, in M tiles of 128 filters;
+//   B operand = the gathered token matrix X (S*L, Dpad) bf16, NT flat token rows per tile.  Output
+//   column t needs input rows t .. t+k-1, so K-chunk (j, c) of B is simply the TMA box at row coordinate
+//   r0 + j, column c*64 of the SAME 2-D tensor map.
+// Filters sit on TMEM lanes and time on TMEM columns, so the max over time is a per-thread running
+// maximum over the columns a thread reads back (tcgen05.ld 32x32b) -- no cross-lane reduction at all
+// (a 32x32 cross-lane max costs ~700-850 cycles per warp whichever way it is done: measured
+// CREDUX+ballot 852, 64-bit butterfly 688; this orientation needs ~100).  Sequence boundaries inside
+// a tile are handled by flushing the running (max, first arg-max) at each boundary with one 64-bit
+// atomicMax per (thread, sequence piece) into the (S, P) key array.  Pre-activations never reach HBM.
 //
-// Warp roles (192 threads, 1 CTA / SM, persistent over tiles):
+// Warp roles (320 threads, 1 CTA / SM, persistent over tiles):
 //   warp 0  lane 0 : TMA producer   (smem ring: full/empty mbarriers)
 //   warp 1  lane 0 : tcgen05.mma issuer; warp 1 also owns the TMEM allocation
-//   warps 2..5     : epilogue, TMEM lane quarter = warp % 4
+//   warps 2..9     : epilogue; TMEM lane quarter = warp % 4, column half = (warp - 2) / 4
+// Optional CTA pairs (cluster of 2): both CTAs run neighbouring tiles in K-lockstep and each loads HALF
+// of every weight chunk, multicast into both CTAs' shared memory.
 #include "common.cuh"
 #include <cuda.h>
+#include <stdlib.h>
 
 namespace {
 
-constexpr int TILE_M = 128;
+constexpr int MT = 128;                       // filters per M tile (UMMA M)
 constexpr int KCHUNK = 64;                    // bf16 elements per 128-byte swizzle row
-constexpr int A_BYTES = TILE_M * 128;         // 16 KB
-constexpr int NUM_THREADS = 192;
+constexpr int MT_BYTES = MT * 128;            // one M tile of one K chunk: 16 KB
+constexpr int NUM_EPI_WARPS = 8;
+constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
 constexpr int SMEM_LIMIT = 227 * 1024;
 
 struct TcParams {
   int64_t n_rows;        // S * L
-  int L, k, F, Fpad;
+  int L, k, F;
   int cpj;               // 64-element chunks per window offset (Dpad / 64)
+  int n_mt;              // M tiles (ceil(F / 128))
+  int NT;                // token rows per tile (UMMA N), multiple of 32, n_mt * NT <= 512
   int n_tiles;
   int ldk, col0;
   unsigned long long* keys;
-  int n1, n2;            // MMA N split (n2 == 0: single MMA)
-  int wbox, n_wbox;      // TMA box rows for W and how many boxes
+  int wbox, n_wbox;      // TMA box rows for W and how many boxes per stage
   int stages;
-  int acc_stages, acc_cols;
+  int shift_mode;        // 0: one X box per (j, c) chunk.  >0: one X box (NT + halo rows) per c chunk, reused for all j
+                         //    through a B descriptor whose start is advanced by j rows (1/2/3 = base_offset 0 / j / 8-j)
+  int xrows;             // rows of the X box in shift mode (NT + k - 1 rounded up to 8)
+  int xstages, wstages;
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -65,6 +77,21 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void tc_commit_mc(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t cluster_id_x() { uint32_t r; asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t n_clusters_x() { uint32_t r; asm volatile("mov.u32 %0, %%nclusterid.x;" : "=r"(r)); return r; }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -90,6 +117,24 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
       : "r"(taddr));
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_ld16_async(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float credux_max(float v) {
   float m;
   asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(m) : "f"(v));
@@ -102,30 +147,40 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
          (static_cast<uint64_t>(1024 >> 4) << 32) | (static_cast<uint64_t>(1) << 46) |
          (static_cast<uint64_t>(2) << 61);
 }
+__device__ __forceinline__ uint64_t make_sw128_desc_bo(uint32_t saddr, uint32_t base_offset) {
+  return make_sw128_desc(saddr) | (static_cast<uint64_t>(base_offset & 7u) << 49);
+}
 // kind::f16, A/B = bf16 (1), D = fp32 (1), both K-major, M = 128
 __device__ __forceinline__ uint32_t make_idesc(int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) |
-         (static_cast<uint32_t>(TILE_M >> 4) << 24);
+         (static_cast<uint32_t>(MT >> 4) << 24);
 }
 
+template <bool CLUSTER, int NCH>     // NCH = 16-column chunks per epilogue warp (NT / 32)
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW, const TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t stage_bytes = A_BYTES + static_cast<uint32_t>(p.Fpad) * 128u;
-  const uint32_t bars = base + static_cast<uint32_t>(p.stages) * stage_bytes;
-  // barrier layout: full[stages] | empty[stages] | tfull[2] | tempty[2] | tmem ptr
+  const uint32_t a_bytes = static_cast<uint32_t>(p.n_mt) * MT_BYTES;           // weights of one K chunk
+  const uint32_t b_bytes = static_cast<uint32_t>(p.NT) * 128u;                 // token rows of one K chunk
+  const uint32_t stage_bytes = a_bytes + ((b_bytes + 1023u) & ~1023u);
+  const uint32_t data_bytes = p.shift_mode == 0
+      ? static_cast<uint32_t>(p.stages) * stage_bytes
+      : static_cast<uint32_t>(p.wstages) * a_bytes + static_cast<uint32_t>(p.xstages) * (((static_cast<uint32_t>(p.xrows) * 128u) + 1023u) & ~1023u);
+  const uint32_t bars = base + data_bytes;
+  // barrier layout: full[stages] | empty[stages] | tfull | tempty | tmem ptr
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (p.stages + s); };
-  auto tfull_bar = [&](int a) { return bars + 8u * (2 * p.stages + a); };
-  auto tempty_bar = [&](int a) { return bars + 8u * (2 * p.stages + 2 + a); };
-  const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 4);
+  const uint32_t tfull_bar = bars + 8u * (2 * p.stages);
+  const uint32_t tempty_bar = bars + 8u * (2 * p.stages + 1);
+  const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 2);
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), CLUSTER ? 2 : 1); }
+    mbar_init(tfull_bar, 1);
+    mbar_init(tempty_bar, NUM_EPI_WARPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -138,112 +193,224 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   }
   tc_fence_before();
   __syncthreads();
+  if (CLUSTER) cluster_sync_all();                  // the peer's barriers exist before anything is multicast to them
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
   const int nk = p.k * p.cpj;
+  // tile schedule: alone, CTA b takes tiles b, b+grid, ..; in a cluster, pair q = clusterid + i*nclusters
+  // and this CTA takes tile 2q + rank (a tile index past the end is a dummy: all rows out of range)
+  const int crank = CLUSTER ? static_cast<int>(cluster_ctarank()) : 0;
+  const int tile_first = CLUSTER ? 2 * static_cast<int>(cluster_id_x()) + crank : static_cast<int>(blockIdx.x);
+  const int tile_step = CLUSTER ? 2 * static_cast<int>(n_clusters_x()) : static_cast<int>(gridDim.x);
+  const int tile_end = CLUSTER ? ((p.n_tiles + 1) / 2) * 2 : p.n_tiles;     // both CTAs run the same count
+
+  // ---- shift mode: separate rings for weights (one (j, c) chunk per slot) and tokens (one c chunk per slot)
+  const uint32_t x_slot_bytes = ((static_cast<uint32_t>(p.xrows) * 128u) + 1023u) & ~1023u;
+  const uint32_t w_ring = base;                                             // wstages * a_bytes
+  const uint32_t x_ring = base + static_cast<uint32_t>(p.wstages) * a_bytes;   // xstages * x_slot_bytes
+  // barriers in shift mode reuse the same array: full[i]/empty[i] for i < wstages are the weight ring,
+  // i in [wstages, wstages + xstages) the token ring (p.stages == wstages + xstages)
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (lane == 0 && p.shift_mode == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-        const int r0 = tile * TILE_M;
-        for (int kc = 0; kc < nk; ++kc) {
+      for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+        const int r0 = tile * p.NT;
+        for (int kc0 = 0; kc0 < nk; ++kc0) {
+          const int kc = kc0;
           const int j = kc / p.cpj, cc = kc - j * p.cpj;
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          mbar_expect_tx(full_bar(stage), stage_bytes);
+          mbar_expect_tx(full_bar(stage), a_bytes + b_bytes);
           const uint32_t a_dst = base + stage * stage_bytes;
-          tma_load_2d(a_dst, &tmX, cc * KCHUNK, r0 + j, full_bar(stage));
-          for (int b = 0; b < p.n_wbox; ++b)
-            tma_load_2d(a_dst + A_BYTES + static_cast<uint32_t>(b * p.wbox) * 128u, &tmW, kc * KCHUNK, b * p.wbox, full_bar(stage));
+          if (CLUSTER) {      // my half of the weight chunk, written into both CTAs of the pair
+            tma_load_2d_mc(a_dst + static_cast<uint32_t>(crank * p.wbox) * 128u, &tmW, kc * KCHUNK, crank * p.wbox,
+                           full_bar(stage), static_cast<uint16_t>(3));
+          } else {
+            for (int b = 0; b < p.n_wbox; ++b)
+              tma_load_2d(a_dst + static_cast<uint32_t>(b * p.wbox) * 128u, &tmW, kc * KCHUNK, b * p.wbox, full_bar(stage));
+          }
+          tma_load_2d(a_dst + a_bytes, &tmX, cc * KCHUNK, r0 + j, full_bar(stage));
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    } else if (lane == 0) {
+      int ws = 0, xs = 0; uint32_t wphase = 0, xphase = 0;
+      for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+        const int r0 = tile * p.NT;
+        for (int cc = 0; cc < p.cpj; ++cc) {
+          mbar_wait(empty_bar(p.wstages + xs), xphase ^ 1u);
+          mbar_expect_tx(full_bar(p.wstages + xs), static_cast<uint32_t>(p.xrows) * 128u);
+          tma_load_2d(x_ring + xs * x_slot_bytes, &tmX, cc * KCHUNK, r0, full_bar(p.wstages + xs));
+          if (++xs == p.xstages) { xs = 0; xphase ^= 1u; }
+          for (int j = 0; j < p.k; ++j) {
+            const int kc = j * p.cpj + cc;
+            mbar_wait(empty_bar(ws), wphase ^ 1u);
+            mbar_expect_tx(full_bar(ws), a_bytes);
+            for (int b = 0; b < p.n_wbox; ++b)
+              tma_load_2d(w_ring + ws * a_bytes + static_cast<uint32_t>(b * p.wbox) * 128u, &tmW, kc * KCHUNK, b * p.wbox, full_bar(ws));
+            if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
+          }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc1 = make_idesc(p.n1);
-      const uint32_t idesc2 = make_idesc(p.n2 > 0 ? p.n2 : 16);
+    if (lane == 0 && p.shift_mode == 0) {
+      const uint32_t idesc = make_idesc(p.NT);
       int stage = 0; uint32_t phase = 0;
-      int acc = 0; uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+      uint32_t acc_phase = 0;
+      for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+        mbar_wait(tempty_bar, acc_phase ^ 1u);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * p.acc_cols);
         for (int kc = 0; kc < nk; ++kc) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t a_src = base + stage * stage_bytes;
-          const uint32_t b_src = a_src + A_BYTES;
+          const uint32_t b_src = a_src + a_bytes;
 #pragma unroll
           for (int ks = 0; ks < KCHUNK / 16; ++ks) {
             const uint32_t accum = (kc | ks) != 0 ? 1u : 0u;
-            const uint64_t adesc = make_sw128_desc(a_src + ks * 32);
-            tc_mma_bf16(d_tmem, adesc, make_sw128_desc(b_src + ks * 32), idesc1, accum);
-            if (p.n2 > 0)
-              tc_mma_bf16(d_tmem + p.n1, adesc, make_sw128_desc(b_src + static_cast<uint32_t>(p.n1) * 128u + ks * 32), idesc2, accum);
+            const uint64_t bdesc = make_sw128_desc(b_src + ks * 32);
+            for (int m = 0; m < p.n_mt; ++m)
+              tc_mma_bf16(tmem_base + static_cast<uint32_t>(m * p.NT), make_sw128_desc(a_src + m * MT_BYTES + ks * 32), bdesc, idesc, accum);
           }
-          tc_commit(empty_bar(stage));                 // smem slot free once these MMAs retire
+          if (CLUSTER) tc_commit_mc(empty_bar(stage), static_cast<uint16_t>(3));   // frees the slot in BOTH CTAs
+          else tc_commit(empty_bar(stage));            // smem slot free once these MMAs retire
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
-        tc_commit(tfull_bar(acc));                     // accumulator complete
-        if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1u; }
+        tc_commit(tfull_bar);                          // accumulators complete
+        acc_phase ^= 1u;
+      }
+    } else if (lane == 0) {
+      const uint32_t idesc = make_idesc(p.NT);
+      int ws = 0, xs = 0; uint32_t wphase = 0, xphase = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+        mbar_wait(tempty_bar, acc_phase ^ 1u);
+        tc_fence_after();
+        for (int cc = 0; cc < p.cpj; ++cc) {
+          mbar_wait(full_bar(p.wstages + xs), xphase);
+          const uint32_t x_src = x_ring + xs * x_slot_bytes;
+          for (int j = 0; j < p.k; ++j) {
+            mbar_wait(full_bar(ws), wphase);
+            tc_fence_after();
+            const uint32_t a_src = w_ring + ws * a_bytes;
+            const uint32_t bo = p.shift_mode == 2 ? static_cast<uint32_t>(j) : (p.shift_mode == 3 ? static_cast<uint32_t>(8 - j) : 0u);
+#pragma unroll
+            for (int ks = 0; ks < KCHUNK / 16; ++ks) {
+              const uint32_t accum = (cc | j | ks) != 0 ? 1u : 0u;
+              // token rows j .. j+NT-1 of the resident box: start address advanced by j rows of 128 B
+              const uint64_t bdesc = make_sw128_desc_bo(x_src + static_cast<uint32_t>(j) * 128u + ks * 32, bo);
+              for (int m = 0; m < p.n_mt; ++m)
+                tc_mma_bf16(tmem_base + static_cast<uint32_t>(m * p.NT), make_sw128_desc(a_src + m * MT_BYTES + ks * 32), bdesc, idesc, accum);
+            }
+            tc_commit(empty_bar(ws));
+            if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
+          }
+          tc_commit(empty_bar(p.wstages + xs));        // token box free once all k offsets have used it
+          if (++xs == p.xstages) { xs = 0; xphase ^= 1u; }
+        }
+        tc_commit(tfull_bar);
+        acc_phase ^= 1u;
       }
     }
   } else {
     const int lq = warp & 3;                           // TMEM lane quarter this warp may read
+    const int half = (warp - 2) >> 2;                  // which half of the tile's columns
     const int Tn = p.L - p.k + 1;
-    int acc = 0; uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-      const int64_t rowbase = static_cast<int64_t>(tile) * TILE_M + lq * 32;
-      const int64_t r = rowbase + lane;
-      const bool rv = r < p.n_rows;
-      const int64_t s = rv ? r / p.L : -1;
-      const int t = static_cast<int>(r - s * p.L);
-      const bool valid = rv && t < Tn;
-      int64_t s_lo = 0, s_hi = -1;
-      if (rowbase < p.n_rows) {
-        s_lo = rowbase / p.L;
-        const int64_t rl = (rowbase + 31 < p.n_rows) ? rowbase + 31 : p.n_rows - 1;
-        s_hi = rl / p.L;
-      }
-      mbar_wait(tfull_bar(acc), acc_phase);
+    const int ncol = p.NT / 2;                         // columns this warp walks, multiple of 16
+    uint32_t acc_phase = 0;
+    for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+      const int64_t rbeg = static_cast<int64_t>(tile) * p.NT + half * ncol;       // flat row of my first column
+      mbar_wait(tfull_bar, acc_phase);
       tc_fence_after();
-      const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(acc * p.acc_cols);
-      const int n_chunks = (p.F + 31) / 32;
-      for (int ch = 0; ch < n_chunks; ++ch) {
-        uint32_t v[32];
-        tc_ld32(taddr0 + ch * 32, v);
-        if (ch == n_chunks - 1) {                      // everything is in registers: release TMEM
-          tc_fence_before();
-          if (lane == 0) mbar_arrive(tempty_bar(acc));
-        }
-        for (int64_t sg = s_lo; sg <= s_hi; ++sg) {
-          const bool in = valid && s == sg;
-          if (!__any_sync(0xffffffffu, in)) continue;
-          float mym = 0.0f; unsigned myb = 0u;
+      for (int m = 0; m < p.n_mt; ++m) {
+        const int f = m * MT + lq * 32 + lane;
+        unsigned long long* kcol = p.keys + p.col0 + f;
+        // running (max, first arg-max) of the current sequence piece
+        int64_t s = rbeg / p.L;
+        int t = static_cast<int>(rbeg - s * p.L);
+        float best = -INFINITY; int bt = -1;
+        const bool fok = f < p.F;
+        auto flush = [&](int64_t last_row) {
+          if (bt >= 0 && fok && last_row < p.n_rows) atomicMax(kcol + s * p.ldk, pool_key(best + 0.0f, static_cast<uint32_t>(bt)));
+          best = -INFINITY; bt = -1;
+        };
+        // 16 columns held in registers.  Common case: no sequence boundary strictly inside the chunk ->
+        // tree max over the 16 values, then (only if it beats the running max) a backward scan for the
+        // FIRST column that attains it; everything independent, no long select chain.
+        // columns [lo, hi) of the chunk (relative indices) belong to the current sequence piece and start
+        // at time step t0: fold them into the running (best, bt).  Tree max, then a backward scan for the
+        // FIRST column that attains it -- all independent instructions, static register indices.
+        auto fold = [&](const uint32_t (&v)[16], int lo, int hi, int t0) {
+          const int vhi = min(hi, lo + (Tn - t0));           // columns >= vhi are not valid windows
+          float x[16];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const float x = in ? __uint_as_float(v[i]) + 0.0f : -INFINITY;
-            const float m = credux_max(x);
-            const unsigned b = __ballot_sync(0xffffffffu, x == m);
-            if (lane == i) { mym = m; myb = b; }
+          for (int i = 0; i < 16; ++i) x[i] = (i >= lo && i < vhi) ? __uint_as_float(v[i]) : -INFINITY;
+          const float m01 = fmaxf(x[0], x[1]), m23 = fmaxf(x[2], x[3]), m45 = fmaxf(x[4], x[5]), m67 = fmaxf(x[6], x[7]);
+          const float m89 = fmaxf(x[8], x[9]), mab = fmaxf(x[10], x[11]), mcd = fmaxf(x[12], x[13]), mef = fmaxf(x[14], x[15]);
+          const float m16 = fmaxf(fmaxf(fmaxf(m01, m23), fmaxf(m45, m67)), fmaxf(fmaxf(m89, mab), fmaxf(mcd, mef)));
+          if (m16 > best) {                                  // strict >: an earlier chunk keeps a tie
+            int idx = 15;
+#pragma unroll
+            for (int i = 14; i >= 0; --i) idx = (x[i] == m16) ? i : idx;
+            best = m16; bt = t0 + idx - lo;
           }
-          const int f = ch * 32 + lane;
-          if (f < p.F && myb != 0u) {
-            const int lstar = __ffs(myb) - 1;
-            const uint32_t tstar = static_cast<uint32_t>(rowbase + lstar - sg * p.L);
-            atomicMax(p.keys + sg * p.ldk + p.col0 + f, pool_key(mym, tstar));
+        };
+        // same, for a chunk that lies wholly inside one sequence and holds only valid windows (no masks)
+        auto fold_all = [&](const uint32_t (&v)[16], int t0) {
+          float x[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) x[i] = __uint_as_float(v[i]);
+          const float m01 = fmaxf(x[0], x[1]), m23 = fmaxf(x[2], x[3]), m45 = fmaxf(x[4], x[5]), m67 = fmaxf(x[6], x[7]);
+          const float m89 = fmaxf(x[8], x[9]), mab = fmaxf(x[10], x[11]), mcd = fmaxf(x[12], x[13]), mef = fmaxf(x[14], x[15]);
+          const float m16 = fmaxf(fmaxf(fmaxf(m01, m23), fmaxf(m45, m67)), fmaxf(fmaxf(m89, mab), fmaxf(mcd, mef)));
+          if (m16 > best) {
+            int idx = 15;
+#pragma unroll
+            for (int i = 14; i >= 0; --i) idx = (x[i] == m16) ? i : idx;
+            best = m16; bt = t0 + idx;
           }
-        }
+        };
+        auto process = [&](const uint32_t (&v)[16], int cb) {
+          const int nb = p.L - t;                            // columns left in the current sequence
+          if (nb > 16) {
+            if (t + 16 <= Tn) fold_all(v, t); else fold(v, 0, 16, t);
+            t += 16;
+          } else if (p.L >= 16) {                            // exactly one boundary at relative column nb
+            fold(v, 0, nb, t);
+            flush(rbeg + cb + nb - 1);
+            ++s;
+            if (nb < 16) fold(v, nb, 16, 0);
+            t = 16 - nb;
+          } else {                                           // very short sequences: several boundaries per chunk
+#pragma unroll                     // (static register indices: a rolled loop would push v[] to local memory)
+            for (int i = 0; i < 16; ++i) {
+              const float x = __uint_as_float(v[i]);
+              if (t < Tn && x > best) { best = x; bt = t; }
+              if (++t == p.L) { flush(rbeg + cb + i); t = 0; ++s; }
+            }
+          }
+        };
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(m * p.NT + half * ncol);
+        // all of this warp's columns of region m in one go: up to 8 x16 loads in flight, one wait
+        uint32_t v[NCH][16];
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) tc_ld16_async(taddr + c * 16, v[c]);
+        tc_wait_ld();
+        if (m == p.n_mt - 1) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar); }    // last read: release TMEM
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) process(v[c], c * 16);
+        flush(s * p.L + (bt >= 0 ? bt : 0));
       }
-      if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1u; }
+      acc_phase ^= 1u;
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if (CLUSTER) cluster_sync_all();                  // nobody leaves while the peer can still write here
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
@@ -284,36 +451,85 @@ bool make_map_2d(CUtensorMap* map, const void* ptr, uint64_t cols, uint64_t rows
 int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void* Wt, int k, int F, int Fpad,
                           uint64_t* keys, int ldk, int col0, cudaStream_t st) {
   const int64_t n_rows = S * L;
-  CLSM_REQUIRE(n_rows + TILE_M < (1ll << 31), "conv_pool_fwd(tcgen05): S*L too large for 32-bit TMA coordinates");
+  CLSM_REQUIRE(n_rows + 512 < (1ll << 31), "conv_pool_fwd(tcgen05): S*L too large for 32-bit TMA coordinates");
   CLSM_REQUIRE(Dpad % 64 == 0 && Fpad % 16 == 0 && Fpad >= 16 && Fpad <= 512, "conv_pool_fwd(tcgen05): bad Dpad/Fpad");
   TcParams p{};
-  p.n_rows = n_rows; p.L = L; p.k = k; p.F = F; p.Fpad = Fpad; p.cpj = Dpad / 64;
-  p.n_tiles = static_cast<int>(ceil_div64(n_rows, TILE_M));
+  p.n_rows = n_rows; p.L = L; p.k = k; p.F = F; p.cpj = Dpad / 64;
+  p.n_mt = (F + MT - 1) / MT;
+  p.NT = (512 / p.n_mt) / 32 * 32;
+  if (p.NT > 256) p.NT = 256;
+  p.n_tiles = static_cast<int>(ceil_div64(n_rows, p.NT));
   p.ldk = ldk; p.col0 = col0; p.keys = reinterpret_cast<unsigned long long*>(keys);
-  if (Fpad <= 256) { p.n1 = Fpad; p.n2 = 0; p.wbox = Fpad; p.n_wbox = 1; }
-  else {
-    p.n1 = ((Fpad / 2) + 15) / 16 * 16; p.n2 = Fpad - p.n1;
-    p.wbox = Fpad / 2; p.n_wbox = 2;
+  // variant: 0 (default) = independent CTAs, 1 = CTA pairs with multicast weights.  CLSM_CONV_TC_VARIANT overrides.
+  static int variant = -1;
+  if (variant < 0) {
+    const char* e = getenv("CLSM_CONV_TC_VARIANT");
+    variant = (e != nullptr && e[0] == '1') ? 1 : 0;
   }
-  p.acc_cols = Fpad <= 256 ? 256 : 512;
-  p.acc_stages = Fpad <= 256 ? 2 : 1;
-  const int stage_bytes = A_BYTES + Fpad * 128;
-  int stages = (SMEM_LIMIT - 2048) / stage_bytes;
-  if (stages > 8) stages = 8;
-  CLSM_REQUIRE(stages >= 2, "conv_pool_fwd(tcgen05): Fpad too large for a 2-stage pipeline");
-  p.stages = stages;
-  const int smem_bytes = stages * stage_bytes + 1024 /*alignment slack*/ + 8 * (2 * stages + 5);
+  const bool cluster = variant == 1 && clsm_sm_count() >= 2;
+  const int a_rows = p.n_mt * MT;
+  if (cluster) { p.wbox = a_rows / 2; p.n_wbox = 2; }
+  else { p.wbox = MT; p.n_wbox = p.n_mt; }
+  { const char* e = getenv("CLSM_CONV_TC_SHIFT"); p.shift_mode = (e != nullptr && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 0; }
+  if (cluster) p.shift_mode = 0;
+  int smem_bytes = 0;
+  p.xrows = (p.NT + k - 1 + 7) / 8 * 8;
+  if (p.shift_mode != 0 && p.xrows <= 256) {
+    const int x_slot = (p.xrows * 128 + 1023) / 1024 * 1024;
+    p.xstages = 2;
+    p.wstages = (SMEM_LIMIT - 2048 - p.xstages * x_slot) / (a_rows * 128);
+    if (p.wstages > 6) p.wstages = 6;
+    if (p.wstages < 2) p.shift_mode = 0;
+    else {
+      p.stages = p.wstages + p.xstages;
+      smem_bytes = p.wstages * a_rows * 128 + p.xstages * x_slot + 1024 + 8 * (2 * p.stages + 4);
+    }
+  } else {
+    p.shift_mode = 0;
+  }
+  if (p.shift_mode == 0) {
+    const int stage_bytes = a_rows * 128 + ((p.NT * 128 + 1023) / 1024) * 1024;
+    int stages = (SMEM_LIMIT - 2048) / stage_bytes;
+    if (stages > 8) stages = 8;
+    CLSM_REQUIRE(stages >= 2, "conv_pool_fwd(tcgen05): tile too large for a 2-stage pipeline");
+    p.stages = stages;
+    smem_bytes = stages * stage_bytes + 1024 /*alignment slack*/ + 8 * (2 * stages + 4);
+  }
 
   CUtensorMap tmX, tmW;
-  if (!make_map_2d(&tmX, X, static_cast<uint64_t>(Dpad), static_cast<uint64_t>(n_rows), KCHUNK, TILE_M) ||
+  // rows of Wt past Fpad (the last M tile is usually partial) are zero-filled by TMA
+  if (!make_map_2d(&tmX, X, static_cast<uint64_t>(Dpad), static_cast<uint64_t>(n_rows), KCHUNK,
+                   static_cast<uint32_t>(p.shift_mode ? p.xrows : p.NT)) ||
       !make_map_2d(&tmW, Wt, static_cast<uint64_t>(k) * Dpad, static_cast<uint64_t>(Fpad), KCHUNK, static_cast<uint32_t>(p.wbox))) {
     clsm_set_error("conv_pool_fwd(tcgen05): cuTensorMapEncodeTiled failed");
     return CLSM_ECUDA;
   }
-  CLSM_CUDA(cudaFuncSetAttribute(conv_pool_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
   int grid = clsm_sm_count();
-  if (grid > p.n_tiles) grid = p.n_tiles;
-  conv_pool_tc_kernel<<<grid, NUM_THREADS, smem_bytes, st>>>(tmX, tmW, p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  if (cluster) {
+    const int n_pairs = (p.n_tiles + 1) / 2;
+    grid = (grid / 2) * 2;
+    if (grid > 2 * n_pairs) grid = 2 * n_pairs;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+  } else if (grid > p.n_tiles) {
+    grid = p.n_tiles;
+  }
+  cfg.gridDim = dim3(grid);
+#define TC_LAUNCH(CL, N)                                                                                                 \
+  do {                                                                                                                   \
+    CLSM_CUDA(cudaFuncSetAttribute(conv_pool_tc_kernel<CL, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)); \
+    CLSM_CUDA(cudaLaunchKernelEx(&cfg, conv_pool_tc_kernel<CL, N>, tmX, tmW, p));                                        \
+  } while (0)
+  const int nch = p.NT / 32;
+  if (cluster) { if (nch == 4) TC_LAUNCH(true, 4); else if (nch == 5) TC_LAUNCH(true, 5); else TC_LAUNCH(true, 8); }
+  else { if (nch == 4) TC_LAUNCH(false, 4); else if (nch == 5) TC_LAUNCH(false, 5); else TC_LAUNCH(false, 8); }
+#undef TC_LAUNCH
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
 }
