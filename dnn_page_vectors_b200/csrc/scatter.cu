@@ -69,31 +69,52 @@ seg_reduce_l0_kernel(const int32_t* __restrict__ spos, const int32_t* __restrict
     int e1 = e + 1;
     while (e1 < cnt && s_seg[e1] == g) ++e1;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (active) {
-      auto fetch = [&](int q) {
-        const int64_t row = s_pos[q];
-        float4 v = __ldg(dX + row * ldx4 + col);
-        if (DROPOUT) {
-          uint32_t bytes[4];
-          dropout_bytes16(seed, static_cast<uint64_t>(row), static_cast<uint32_t>(col >> 2), bytes);
-          const int o = (col & 3) * 4;
-          v.x = dropout_keep(bytes, o + 0, thr) ? v.x * inv_keep : 0.f;
-          v.y = dropout_keep(bytes, o + 1, thr) ? v.y * inv_keep : 0.f;
-          v.z = dropout_keep(bytes, o + 2, thr) ? v.z * inv_keep : 0.f;
-          v.w = dropout_keep(bytes, o + 3, thr) ? v.w * inv_keep : 0.f;
-        }
+    {
+      // Dropout mask: one Philox call yields the 16 decision bytes of a (row, 16-column block); the 4 lanes
+      // that own that block's 4 float4 columns would each recompute it.  Instead lane (4b + j) computes the
+      // block for row q + j of the 4 rows in flight and the words are exchanged with shuffles: 1 call per
+      // lane per 4 rows instead of 4.  (All 32 lanes take part in the shuffles, active or not.)
+      const int lane = threadIdx.x & 31;
+      const int sub = lane & 3;                       // which float4 of the 16-column block this lane owns
+      auto load_row = [&](int q) {
+        return active ? __ldg(dX + static_cast<int64_t>(s_pos[q]) * ldx4 + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+      };
+      auto apply = [&](float4 v, uint32_t word) {
+        v.x = ((word & 0xffu) < thr) ? v.x * inv_keep : 0.f;
+        v.y = (((word >> 8) & 0xffu) < thr) ? v.y * inv_keep : 0.f;
+        v.z = (((word >> 16) & 0xffu) < thr) ? v.z * inv_keep : 0.f;
+        v.w = ((word >> 24) < thr) ? v.w * inv_keep : 0.f;
         return v;
       };
       int q = e;
       for (; q + 4 <= e1; q += 4) {            // 4 independent row loads in flight, added in order
-        const float4 v0 = fetch(q), v1 = fetch(q + 1), v2 = fetch(q + 2), v3 = fetch(q + 3);
+        float4 v0 = load_row(q), v1 = load_row(q + 1), v2 = load_row(q + 2), v3 = load_row(q + 3);
+        if (DROPOUT) {
+          uint32_t bytes[4];
+          dropout_bytes16(seed, static_cast<uint64_t>(s_pos[q + sub]), static_cast<uint32_t>(col >> 2), bytes);
+          const int base = lane & ~3;
+          // row q+j's bytes live in lane base+j; this lane needs word `sub` of each
+          uint32_t w[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t b0 = __shfl_sync(0xffffffffu, bytes[0], base + j), b1 = __shfl_sync(0xffffffffu, bytes[1], base + j);
+            const uint32_t b2 = __shfl_sync(0xffffffffu, bytes[2], base + j), b3 = __shfl_sync(0xffffffffu, bytes[3], base + j);
+            w[j] = sub == 0 ? b0 : sub == 1 ? b1 : sub == 2 ? b2 : b3;
+          }
+          v0 = apply(v0, w[0]); v1 = apply(v1, w[1]); v2 = apply(v2, w[2]); v3 = apply(v3, w[3]);
+        }
         acc.x += v0.x; acc.y += v0.y; acc.z += v0.z; acc.w += v0.w;
         acc.x += v1.x; acc.y += v1.y; acc.z += v1.z; acc.w += v1.w;
         acc.x += v2.x; acc.y += v2.y; acc.z += v2.z; acc.w += v2.w;
         acc.x += v3.x; acc.y += v3.y; acc.z += v3.z; acc.w += v3.w;
       }
       for (; q < e1; ++q) {
-        const float4 v = fetch(q);
+        float4 v = load_row(q);
+        if (DROPOUT) {
+          uint32_t bytes[4];
+          dropout_bytes16(seed, static_cast<uint64_t>(s_pos[q]), static_cast<uint32_t>(col >> 2), bytes);
+          v = apply(v, bytes[sub]);
+        }
         acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       }
     }
