@@ -96,6 +96,7 @@ class Tower(object):
         # compute-layout conv weights Wt (Fpad, k*Dpad)
         self.Wt = [torch.zeros((self.Fpad, k * self.Dpad), dtype=self.cdtype, device=dev) for k in self.windows]
         self._bufs = {}
+        self.shard = (0, self.V1)          # rows whose optimizer state this rank owns
         self._init_small(net.rng)
         self.refresh_compute_copies(table_too=True)
 
@@ -115,6 +116,8 @@ class Tower(object):
 
     # ---- numpy import/export in reference layouts
     def get_weights(self):
+        if self.net.dp is not None:
+            self.net.dp.gather_masters(self)
         out = {"E": self.E.cpu().numpy()}
         for i, w in enumerate(self.convW):
             out["convW%d" % i] = w.cpu().numpy().copy()
@@ -216,20 +219,24 @@ class Tower(object):
 
     def adam(self, b, step, sparse_grad=None):
         """sparse_grad: optional (row_of_id, dE_rows, uniq, n_uniq) replacing this rank's own
-        (the data-parallel path passes the globally reduced gradient)."""
+        (the data-parallel path passes the globally reduced gradient of the rows this rank owns).
+        self.shard = (lo, hi): table rows this rank's optimizer owns (all rows when not data parallel)."""
         p = self.net.params
         st = _stream()
         call("clsm_adam_dense", _ptr(self.flat), _ptr(self.flat_m), _ptr(self.flat_v), _ptr(self.flat_g),
              self.n_small, step, p.lr, p.beta_1, p.beta_2, p.epsilon, st)
         row_of_id, dE_rows, uniq, n_uniq = sparse_grad if sparse_grad is not None else (
             b["row_of_id"], b["dE_rows"], b["uniq"], b["n_uniq"])
+        lo, hi = self.shard
         if self.net.lazy_table_adam:
             call("clsm_adam_rows", _ptr(self.E), _ptr(self.E_m), _ptr(self.E_v), self.D, _ptr(uniq), _ptr(n_uniq),
                  dE_rows.shape[0], _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
                  _ptr(self.E_c), self.Dpad, st)
-        else:
-            call("clsm_adam_table", _ptr(self.E), _ptr(self.E_m), _ptr(self.E_v), self.V1, self.D, _ptr(row_of_id),
-                 _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon, _ptr(self.E_c), self.Dpad, st)
+        elif hi > lo:
+            copy = self.E_c[lo:hi] if self.E_c is not None else None
+            call("clsm_adam_table", _ptr(self.E[lo:hi]), _ptr(self.E_m[lo:hi]), _ptr(self.E_v[lo:hi]), hi - lo, self.D,
+                 _ptr(row_of_id[lo:hi]), _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
+                 _ptr(copy), self.Dpad, st)
         self.refresh_compute_copies(table_too=False)
 
     # ---- Keras-like predict on a tower: tokens (N, L) -> semantic vectors (N, H) numpy
@@ -367,6 +374,7 @@ class CLSM(object):
             gq, gd = self.dp.exchange(self, bq, bd)
             self.query_model.adam(bq, self.iterations, gq)
             self.doc_model.adam(bd, self.iterations, gd)
+            self.dp.after_adam(self)
         else:
             self.query_model.adam(bq, self.iterations)
             self.doc_model.adam(bd, self.iterations)
@@ -521,6 +529,9 @@ class CLSM(object):
     def save(self, path):
         """Whole model: architecture JSON, weights, optimizer state and step (resume-able,
         which the reference's save is not)."""
+        if self.dp is not None:
+            for tower in (self.query_model, self.doc_model):
+                self.dp.gather_masters(tower)
         st = {"json": self.to_json(), "iterations": self.iterations,
               "query": {k: v.cpu() for k, v in self.query_model.state().items()},
               "doc": {k: v.cpu() for k, v in self.doc_model.state().items()}}

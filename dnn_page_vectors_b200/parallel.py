@@ -4,10 +4,13 @@ NVLink 5 / NVSwitch on the GPU box, gloo in the CPU tests).
 The reference has no data parallelism (it pins tower instances to four devices with tf.device,
 dssm_cnn_v2/cnn_dssm_tf.py:139-156); SURVEY 8e replaces that with
 
-  training  : batch split over ranks; ONE allreduce of the flat small-parameter gradient per tower,
-              and a row-sparse exchange of the embedding gradient: allgather (unique ids, summed rows)
-              of every rank, then every rank runs the same deterministic sort + segmented reduce over
-              the gathered set, so replicas stay bit-identical without a (V, D) dense allreduce;
+  training  : batch split over ranks.  Small parameters: ONE allreduce of the two flat gradient buffers,
+              replicated Adam.  Embedding tables: the optimizer is SHARDED by vocabulary rows -- rank r owns
+              rows [r*R, (r+1)*R) of both tables.  Each rank's row-sparse gradient (ids sorted ascending) is
+              cut at the ownership boundaries and sent to the owners with one all-to-all; every owner runs
+              the deterministic sort + segmented reduce over what it received, applies the dense Keras Adam
+              to ITS rows only (1/N of the 14 GB optimizer pass), and the refreshed bf16 compute rows are
+              allgathered in place.  No (V, D) gradient is ever allreduced and replicas stay bit-identical.
   encode    : pages split by contiguous row ranges, no communication;
   retrieval : queries replicated, each rank scans its shard, allgather of the (Q, k) lists and a
               k-way merge ordered (score desc, id asc), so the answer does not depend on the shard count.
@@ -25,6 +28,11 @@ def shard_range(n, rank, world):
     base, rem = divmod(int(n), int(world))
     lo = rank * base + min(rank, rem)
     return lo, lo + base + (1 if rank < rem else 0)
+
+
+def owner_rows(n_rows, world):
+    """Rows per owner for the sharded table optimizer: equal slices of ceil(n/world) rows."""
+    return (int(n_rows) + world - 1) // world
 
 
 def allgather_padded(rows, count, group=None):
@@ -58,8 +66,16 @@ def allreduce_flat(tensors, group=None):
         off += n
 
 
+def split_points(sorted_ids, rows_per_owner, world):
+    """sorted_ids ascending (n,) -> (world,) counts of ids falling into each owner's row range."""
+    bounds = torch.arange(1, world, device=sorted_ids.device, dtype=sorted_ids.dtype) * rows_per_owner
+    cuts = torch.searchsorted(sorted_ids, bounds)
+    edges = torch.cat([cuts.new_zeros(1), cuts, cuts.new_full((1,), sorted_ids.numel())])
+    return edges[1:] - edges[:-1]
+
+
 class DataParallel(object):
-    """Attach to a CLSM: net.dp = DataParallel(net).  step_resident() then calls exchange()."""
+    """Attach to a CLSM: DataParallel(net) sets net.dp; step_resident() then calls exchange()/after_adam()."""
 
     def __init__(self, net, group=None):
         if not dist.is_initialized():
@@ -69,47 +85,90 @@ class DataParallel(object):
         self.world = dist.get_world_size(group)
         self.net = net
         self._bufs = {}
-        # identical replicas: rank 0's weights and optimizer state everywhere
         for tower in (net.query_model, net.doc_model):
+            # identical replicas: rank 0's weights and optimizer state everywhere
             for t in tower.state().values():
                 dist.broadcast(t, src=0, group=group)
+            R = owner_rows(tower.V1, self.world)
+            tower.rows_per_owner = R
+            tower.shard = (min(self.rank * R, tower.V1), min((self.rank + 1) * R, tower.V1))
+            if tower.E_c is not None and tower.E_c.shape[0] != R * self.world:
+                # compute copy padded to world * R rows so the in-place allgather has equal slices
+                tower.E_c = torch.zeros((R * self.world, tower.Dpad), dtype=tower.E_c.dtype, device=tower.E_c.device)
             tower.refresh_compute_copies(table_too=True)
         net.dp = self
 
-    def _global_sparse(self, tower, b, tag):
-        """allgather this tower's (uniq ids, rows) and re-reduce them identically on every rank."""
-        import ctypes as C
+    # ------------------------------------------------------------------ training exchange
+    def exchange(self, net, bq, bd):
+        """Allreduce the small gradients; route each tower's row-sparse table gradient to the row owners and
+        reduce it there.  Returns per tower (row_of_id, dE_rows, uniq, n_uniq) of the rows this rank owns."""
         from .model import _ptr, _stream
         from ._lib import call, lib
-        n_local = int(b["n_uniq"].item())                 # one small D2H sync per tower per step
-        ids_all, _ = allgather_padded(b["uniq"], n_local, self.group)
-        rows_all, _ = allgather_padded(b["dE_rows"], n_local, self.group)
-        n_all = int(ids_all.shape[0])
-        g = self._bufs.get(tag)
-        if g is None or g["cap"] < n_all:
-            cap = int(n_all * 1.25) + 64
-            dev = rows_all.device
-            g = {"cap": cap,
-                 "uniq": torch.empty(cap, dtype=torch.int32, device=dev),
-                 "n_uniq": torch.zeros(1, dtype=torch.int32, device=dev),
-                 "rows": torch.empty((min(cap, tower.V1), tower.Dpad), dtype=torch.float32, device=dev),
-                 "row_of_id": torch.empty(tower.V1, dtype=torch.int32, device=dev)}
-            g["ws_bytes"] = lib.clsm_emb_scatter_workspace_bytes(cap, tower.D)
-            g["ws"] = torch.empty(g["ws_bytes"], dtype=torch.uint8, device=dev)
-            self._bufs[tag] = g
-        ids_all = ids_all.contiguous()
-        rows_all = rows_all.contiguous()
-        call("clsm_emb_scatter", _ptr(ids_all), n_all, _ptr(rows_all), tower.Dpad, tower.D, 1.0, 0, tower.V1,
-             _ptr(g["uniq"]), _ptr(g["n_uniq"]), _ptr(g["rows"]), _ptr(g["row_of_id"]),
-             _ptr(g["ws"]), g["ws_bytes"], _stream())
-        g["keepalive"] = (ids_all, rows_all)
-        return g["row_of_id"], g["rows"], g["uniq"], g["n_uniq"]
-
-    def exchange(self, net, bq, bd):
         allreduce_flat([net.query_model.flat_g, net.doc_model.flat_g], self.group)
-        gq = self._global_sparse(net.query_model, bq, "q")
-        gd = self._global_sparse(net.doc_model, bd, "d")
-        return gq, gd
+        towers = ((net.query_model, bq, "q"), (net.doc_model, bd, "d"))
+        W = self.world
+        # one host sync for both towers' unique counts
+        n_loc = torch.cat([bq["n_uniq"], bd["n_uniq"]]).tolist()
+        send_cnt = torch.stack([split_points(b["uniq"][:n], t.rows_per_owner, W) for (t, b, _), n in zip(towers, n_loc)])
+        send_cnt = send_cnt.to(torch.int64).contiguous()                       # (2, W)
+        recv_cnt = torch.empty_like(send_cnt)
+        # counts: row i of send_cnt goes to ... transpose so that the all-to-all splits by destination rank
+        s_t = send_cnt.t().contiguous()                                        # (W, 2): what I send to each rank
+        r_t = torch.empty_like(s_t)
+        dist.all_to_all_single(r_t, s_t, group=self.group)
+        recv_cnt = r_t.t().contiguous()
+        sc, rc = send_cnt.tolist(), recv_cnt.tolist()                          # second (and last) host sync
+        out = []
+        for i, (tower, b, tag) in enumerate(towers):
+            n = n_loc[i]
+            n_in = int(sum(rc[i]))
+            g = self._bufs.get(tag)
+            if g is None or g["cap"] < n_in:
+                cap = int(n_in * 1.25) + 64
+                dev = b["dE_rows"].device
+                g = {"cap": cap,
+                     "ids_in": torch.empty(cap, dtype=torch.int32, device=dev),
+                     "rows_in": torch.empty((cap, tower.Dpad), dtype=torch.float32, device=dev),
+                     "uniq": torch.empty(cap, dtype=torch.int32, device=dev),
+                     "n_uniq": torch.zeros(1, dtype=torch.int32, device=dev),
+                     "rows": torch.empty((min(cap, tower.V1), tower.Dpad), dtype=torch.float32, device=dev),
+                     "row_of_id": torch.empty(tower.V1, dtype=torch.int32, device=dev)}
+                g["ws_bytes"] = lib.clsm_emb_scatter_workspace_bytes(cap, tower.D)
+                g["ws"] = torch.empty(g["ws_bytes"], dtype=torch.uint8, device=dev)
+                self._bufs[tag] = g
+            ids_in, rows_in = g["ids_in"][:n_in], g["rows_in"][:n_in]
+            dist.all_to_all_single(ids_in, b["uniq"][:n], rc[i], sc[i], group=self.group)
+            dist.all_to_all_single(rows_in, b["dE_rows"][:n], rc[i], sc[i], group=self.group)
+            if n_in > 0:
+                call("clsm_emb_scatter", _ptr(ids_in), n_in, _ptr(rows_in), tower.Dpad, tower.D, 1.0, 0, tower.V1,
+                     _ptr(g["uniq"]), _ptr(g["n_uniq"]), _ptr(g["rows"]), _ptr(g["row_of_id"]),
+                     _ptr(g["ws"]), g["ws_bytes"], _stream())
+            else:
+                g["row_of_id"].fill_(-1)
+                g["n_uniq"].zero_()
+            out.append((g["row_of_id"], g["rows"], g["uniq"], g["n_uniq"]))
+        return out[0], out[1]
+
+    def after_adam(self, net):
+        """Every owner has refreshed the bf16 compute rows of its slice: allgather them in place."""
+        for tower in (net.query_model, net.doc_model):
+            if tower.E_c is None:
+                self.gather_masters(tower, state=False)
+                continue
+            R = tower.rows_per_owner
+            dist.all_gather_into_tensor(tower.E_c, tower.E_c[self.rank * R:(self.rank + 1) * R], group=self.group)
+
+    def gather_masters(self, tower, state=True):
+        """Make the fp32 master table (and, with state=True, Adam m/v) complete on every rank
+        (each rank only keeps its own rows current).  Used by get_weights()/save() and by the fp32 mode."""
+        R = tower.rows_per_owner
+        lo, hi = tower.shard
+        for t in ([tower.E, tower.E_m, tower.E_v] if state else [tower.E]):
+            full = t.new_zeros((R * self.world, t.shape[1]))
+            mine = full[self.rank * R:(self.rank + 1) * R]
+            mine[:hi - lo].copy_(t[lo:hi])
+            dist.all_gather_into_tensor(full, mine, group=self.group)
+            t.copy_(full[:t.shape[0]])
 
     def reduce_metrics(self, loss_acc):
         """mean loss / accuracy over ranks (equal per-rank batch)."""

@@ -1,0 +1,90 @@
+"""Data-parallel equivalence check, run under torchrun on >= 2 GPUs (tests/test_gpu_dp.py launches it):
+
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/dp_check.py
+
+N ranks each train on 1/N of a global batch for 3 steps (dropout off) and must end with the weights a
+single process reaches on the whole batch: same loss gradient (1/B_global scaling), allreduced small
+gradients, table gradient routed to the row owners, sharded dense Adam, allgathered compute rows.
+Also checks that the bf16 compute tables are bit-identical on every rank, and sharded retrieval."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from dnn_page_vectors_b200 import CLSM, ModelParams                    # noqa: E402
+from dnn_page_vectors_b200.parallel import DataParallel, shard_range   # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dist.init_process_group("nccl")
+    ok = True
+    for precision, tol in (("fp32", 3e-6), ("bf16", 3e-6)):
+        V, D, F, H, J, Lq, Ld, Bg = 997, 100, 150, 64, 3, 8, 24, 16 * world
+        mp = ModelParams(embedding_dim=D, filter_sizes=(3, 4), num_filters=F, hidden_dims=H, J=J,
+                         dropout_prob=(0.0, 0.5), precision=precision, seed=7)
+        rng = np.random.RandomState(0)
+        table = rng.uniform(-0.25, 0.25, size=(V + 1, D))
+        x = [rng.randint(0, V, size=(Bg, Lq)).astype(np.int32)] + \
+            [rng.randint(0, V, size=(Bg, Ld)).astype(np.int32) for _ in range(1 + J)]
+        x[1][:, 12:] = V - 1                                               # PAD-like skew
+        conv = "simt" if precision == "fp32" else "auto"
+        # single-process reference on the whole batch (every rank computes it: deterministic)
+        ref = CLSM(mp, Lq, Ld, embedding_weights=table, conv_impl=conv).compile()
+        ref_losses = [ref.train_on_batch(x)[0] for _ in range(3)]
+        ref_w = ref.get_weights()
+        # data parallel
+        net = CLSM(mp, Lq, Ld, embedding_weights=table, conv_impl=conv).compile()
+        DataParallel(net)
+        lo, hi = shard_range(Bg, rank, world)
+        xl = [a[lo:hi] for a in x]
+        losses = []
+        for _ in range(3):
+            l, _ = net.train_on_batch(xl)
+            la = net.dp.reduce_metrics(torch.tensor([l, 0.0], device="cuda"))
+            losses.append(float(la[0]))
+        w = net.get_weights()                                              # collective: gathers the sharded masters
+        for a, b in zip(losses, ref_losses):
+            if abs(a - b) > 1e-5 * max(1.0, abs(b)):
+                ok = False
+                print("rank %d %s loss mismatch %r vs %r" % (rank, precision, losses, ref_losses))
+        for tag in ("query", "doc"):
+            for name in w[tag]:
+                err = np.abs(w[tag][name] - ref_w[tag][name])
+                # Adam amplifies a sign flip of a near-zero gradient to a full step: allow a few outliers
+                if not ((err > tol).mean() < 2e-3 and err.max() < 7e-3):
+                    ok = False
+                    print("rank %d %s %s/%s max err %.3g frac %.3g" % (rank, precision, tag, name, err.max(), (err > tol).mean()))
+        # replicas identical: compare a checksum of the compute tables and small params across ranks
+        for tower in (net.query_model, net.doc_model):
+            t = tower.E_c if tower.E_c is not None else tower.E
+            sig = torch.stack([t[:tower.V1].float().double().sum(), tower.flat.double().sum()])
+            sigs = [torch.zeros_like(sig) for _ in range(world)]
+            dist.all_gather(sigs, sig)
+            if any(not torch.equal(s, sigs[0]) for s in sigs):
+                ok = False
+                print("rank %d %s replicas differ" % (rank, precision))
+        # sharded retrieval == single-shard retrieval
+        pages = rng.randint(0, V, size=(211, Ld)).astype(np.int32)
+        vec = net.encode_pages(pages)
+        qv = net.encode_queries(x[0][:5])
+        full_s, full_i = net.topk(qv, vec, k=10)
+        plo, phi = shard_range(211, rank, world)
+        ms, mi = net.dp.sharded_topk(qv, vec[plo:phi].contiguous(), 10, plo)
+        if not (torch.equal(mi, full_i) and torch.equal(ms, full_s)):
+            ok = False
+            print("rank %d %s sharded top-k differs" % (rank, precision))
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("DP_CHECK_OK" if int(flag) == 1 else "DP_CHECK_FAILED")
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()
