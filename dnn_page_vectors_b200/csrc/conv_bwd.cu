@@ -17,6 +17,10 @@ size_t clsm_conv_bwd_dx_fast_bytes(int64_t S, int L, int F);
 int clsm_conv_bwd_dx_fast(const void* Wt, int dtype, int k, int Dpad, int L, int64_t S, const float* G, const int32_t* A,
                           int ldp, int col0, int F, float* dX, int accumulate, void* scratch, cudaStream_t st);
 
+size_t clsm_conv_bwd_dx_tc_bytes(int k, int Dpad, int F);                                               // conv_bwd_tc.cu
+int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64_t S, const float* G, const int32_t* A,
+                        int ldp, int col0, int F, float* dX, int accumulate, void* scratch, cudaStream_t st);
+
 namespace {
 
 constexpr int FPW = 4;            // filters per warp
@@ -216,7 +220,7 @@ size_t clsm_conv_bwd_workspace_bytes(int64_t S, int L, int k, int D, int F) {
   const int Dpad = (D + 63) / 64 * 64;
   const size_t part = align_up(static_cast<size_t>(dw_groups(S, Dpad, F)) * F * k * Dpad * 4, 256);
   const size_t cs = align_up(static_cast<size_t>(kColsumChunks) * F * 4, 256);
-  return part + cs + clsm_conv_bwd_dx_fast_bytes(S, L, F);
+  return part + cs + clsm_conv_bwd_dx_fast_bytes(S, L, F) + clsm_conv_bwd_dx_tc_bytes(k, Dpad, F);
 }
 
 int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
@@ -259,6 +263,11 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
   CLSM_LAUNCH_CHECK();
   if (clsm_colsum(G, S, ldp, col0, F, db, cs, kColsumChunks, st) != CLSM_OK) { clsm_set_error("conv_pool_bwd: colsum launch failed"); return CLSM_ECUDA; }
 
+  // dX: tensor cores (bf16 mode) -> shared-memory staged CUDA cores -> generic
+  void* wb_scratch = static_cast<char*>(sort_scratch) + clsm_conv_bwd_dx_fast_bytes(S, L, F);
+  rc = clsm_conv_bwd_dx_tc(Wt, dtype, k, Dpad, L, S, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1, wb_scratch, st);
+  if (rc == CLSM_OK) return CLSM_OK;
+  if (rc != CLSM_EUNSUPPORTED) return rc;
   rc = clsm_conv_bwd_dx_fast(Wt, dtype, k, Dpad, L, S, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1, sort_scratch, st);
   if (rc == CLSM_OK) return CLSM_OK;
   if (rc != CLSM_EUNSUPPORTED) return rc;

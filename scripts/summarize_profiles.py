@@ -1,0 +1,47 @@
+"""Turn gpurun_out/launches.csv (ncu launch list) and gpurun_out/prof_r01.ncu-rep (ncu --set full) into the
+tracked summaries under profiles/.  Usage: python scripts/summarize_profiles.py r01"""
+import collections, csv, io, json, os, subprocess, sys
+tag = sys.argv[1] if len(sys.argv) > 1 else "r01"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+out_dir = os.path.join(ROOT, "profiles")
+# ---- launch list
+lines = [l for l in open(os.path.join(ROOT, "gpurun_out", "launches.csv")) if not l.startswith("==")]
+agg = collections.OrderedDict()
+for row in csv.DictReader(lines):
+    try:
+        name, v, unit = row["Kernel Name"], float(row["Metric Value"].replace(",", "")), row.get("Metric Unit", "")
+    except Exception:
+        continue
+    v = v / 1e6 if unit == "ns" else v / 1e3 if unit in ("us", "usecond") else v
+    a = agg.setdefault(name, [0, 0.0]); a[0] += 1; a[1] += v
+tot = sum(a[1] for a in agg.values())
+with open(os.path.join(out_dir, "%s_launches_summary.txt" % tag), "w") as f:
+    f.write("# ncu --metrics gpu__time_duration.sum --clock-control none, python bench.py --steps 3 --warmup 3 --no-extras\n")
+    f.write("# (cold-cache, serialised launches: compare SHARES with bench.py's `kernels`, not absolutes)\n")
+    f.write("%-90s %5s %10s %9s %6s\n" % ("kernel", "n", "total_ms", "avg_ms", "share"))
+    for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        f.write("%-90s %5d %10.3f %9.4f %5.1f%%\n" % (k[:90], a[0], a[1], a[1] / a[0], 100 * a[1] / tot))
+    f.write("total %.3f ms over %d launches\n" % (tot, sum(a[0] for a in agg.values())))
+# ---- full capture
+rep = os.path.join(ROOT, "gpurun_out", "prof_%s.ncu-rep" % tag)
+if os.path.exists(rep):
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units = rows[0], rows[1]
+    want = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+            "dram__throughput.avg.pct_of_peak_sustained_elapsed", "sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed",
+            "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
+            "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic", "smsp__inst_executed.sum",
+            "smsp__issue_active.avg.pct_of_peak_sustained_active", "lts__t_sector_hit_rate.pct", "l1tex__m_xbar2l1tex_read_bytes.sum",
+            "sm__cycles_elapsed.avg.per_second", "lts__throughput.avg.pct_of_peak_sustained_elapsed"]
+    idx = []
+    for w in want:
+        for i, h in enumerate(hdr):
+            if h == w or h.endswith("." + w):
+                idx.append(i); break
+    with open(os.path.join(out_dir, "%s_ncu_full_summary.csv" % tag), "w") as f:
+        wr = csv.writer(f)
+        wr.writerow([hdr[i] for i in idx]); wr.writerow([units[i] for i in idx])
+        for r in rows[2:]:
+            wr.writerow([r[i] for i in idx])
+print("ok")

@@ -268,11 +268,23 @@ def test_conv_pool_bwd(bf16, shape):
     np.testing.assert_allclose(dW.cpu().numpy(), odW, rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(db.cpu().numpy(), Gi.sum(0), rtol=1e-4, atol=1e-5)
     got = dX.cpu().numpy()
-    np.testing.assert_allclose(got[:, :D], odX.reshape(S * L, D), rtol=1e-4, atol=1e-5)
+    # bf16 mode: dX comes from the tensor core with G rounded to bf16 (8-bit mantissa) -> 2e-2 class tolerance,
+    # checked per element against the sum of |terms|; fp32 mode is the exact CUDA-core path
+    if bf16:
+        mag = np.zeros_like(odX)
+        for j in range(k):
+            np.add.at(mag, (np.repeat(sidx, F), (Ai + j).ravel()), np.abs(Gi[:, :, None] * W[j].T[None]).reshape(S * F, D))
+        assert (np.abs(got[:, :D] - odX.reshape(S * L, D)) <= 8e-3 * mag.reshape(S * L, D) + 1e-6).all()
+    else:
+        np.testing.assert_allclose(got[:, :D], odX.reshape(S * L, D), rtol=1e-4, atol=1e-5)
     assert (got[:, D:] == 0).all()
     # second window accumulates into dX
     call("clsm_conv_pool_bwd", *args, 0, P(ws), ws_bytes, ST())
-    np.testing.assert_allclose(dX.cpu().numpy()[:, :D], 2 * odX.reshape(S * L, D), rtol=1e-4, atol=1e-5)
+    got2 = dX.cpu().numpy()[:, :D]
+    if bf16:
+        assert (np.abs(got2 - 2 * odX.reshape(S * L, D)) <= 1.6e-2 * mag.reshape(S * L, D) + 2e-6).all()
+    else:
+        np.testing.assert_allclose(got2, 2 * odX.reshape(S * L, D), rtol=1e-4, atol=1e-5)
 
 
 # ------------------------------------------------------------------ embedding scatter
