@@ -47,6 +47,9 @@ SIGNATURES = {
     "clsm_normalize_rows": (i32, [vp, i64, i32, vp, vp]),
     "clsm_cos_topk_workspace_bytes": (sz, [i64, i64, i32]),
     "clsm_cos_topk": (i32, [vp, i64, vp, i64, i32, i32, i64, vp, vp, vp, sz, vp]),
+    "clsm_normalize_rows_bf16": (i32, [vp, i64, i32, vp, vp]),
+    "clsm_cos_topk_bf16_workspace_bytes": (sz, [i64, i64, i32]),
+    "clsm_cos_topk_bf16": (i32, [vp, i64, vp, i64, i32, i32, i64, vp, vp, vp, sz, vp]),
     "clsm_topk_merge_workspace_bytes": (sz, [i32, i64, i32]),
     "clsm_topk_merge": (i32, [vp, vp, i32, i64, i32, vp, vp, vp, sz, vp]),
     "clsm_topk_merge_static": (i32, [vp, vp, i32, i64, i32, vp, vp, vp]),

@@ -153,6 +153,9 @@ topk_score_kernel(const float* __restrict__ Qn, int64_t nQ, const float* __restr
 }
 
 // level >= 1: grid (nQ, n_chunks); candidates in[q*in_stride + i], i < n_in
+// CLEAR: the (thresholded) key matrix of the tensor-core scan is mostly empty; non-empty entries are zeroed
+// after reading so that the matrix is all-empty again for the next segment (the scan only WRITES survivors).
+template <bool CLEAR>
 __global__ void __launch_bounds__(TPB)
 topk_merge_kernel(const u64* __restrict__ in, int64_t in_stride, int64_t n_in, int k,
                   u64* __restrict__ out, int64_t out_stride) {
@@ -162,12 +165,49 @@ topk_merge_kernel(const u64* __restrict__ in, int64_t in_stride, int64_t n_in, i
   const int tid = threadIdx.x;
   const int64_t q = blockIdx.x, chunk = blockIdx.y;
   u64 keys[KPT];
+  int nz = 0;
 #pragma unroll
   for (int i = 0; i < KPT; ++i) {
     const int64_t idx = chunk * R + tid + i * TPB;
     keys[i] = idx < n_in ? in[q * in_stride + idx] : 0ull;
+    if (keys[i] != 0ull) {
+      ++nz;
+      if (CLEAR) const_cast<u64*>(in)[q * in_stride + idx] = 0ull;
+    }
   }
-  select_topk(keys, k, s_hist, s_ctl, s_out);
+  // few survivors (the common case behind a threshold): no radix passes, just gather and sort them
+  const int total = __syncthreads_count(nz > 0) == 0 ? 0 : -1;
+  if (total == 0) {
+    if (tid < k) out[q * out_stride + chunk * k + tid] = 0ull;
+    return;
+  }
+  if (tid == 0) s_ctl[3] = 0;
+  __syncthreads();
+  if (nz) atomicAdd(&s_ctl[3], static_cast<unsigned>(nz));
+  __syncthreads();
+  if (s_ctl[3] <= static_cast<unsigned>(k)) {
+    if (tid < KMAX) s_out[tid] = 0;
+    if (tid == 0) s_ctl[2] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < KPT; ++i)
+      if (keys[i] != 0ull) s_out[atomicAdd(&s_ctl[2], 1u)] = keys[i];
+    __syncthreads();
+    for (int size = 2; size <= KMAX; size <<= 1) {
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        if (tid < KMAX / 2) {
+          const int lo = (tid / stride) * stride * 2 + (tid % stride);
+          const int hi = lo + stride;
+          const bool desc = ((lo & size) == 0);
+          const u64 a = s_out[lo], b = s_out[hi];
+          if ((a < b) == desc) { s_out[lo] = b; s_out[hi] = a; }
+        }
+        __syncthreads();
+      }
+    }
+  } else {
+    select_topk(keys, k, s_hist, s_ctl, s_out);
+  }
   if (tid < k) out[q * out_stride + chunk * k + tid] = s_out[tid];
 }
 
@@ -202,7 +242,7 @@ int run_merge_levels(u64* buf[2], int src, int64_t nQ, int64_t n_in, int k, cuda
     const int64_t n_chunks = ceil_div64(n_in, R);
     const int dst = src ^ 1;
     dim3 grid(static_cast<unsigned>(nQ), static_cast<unsigned>(n_chunks));
-    topk_merge_kernel<<<grid, TPB, 0, st>>>(buf[src], n_in, n_in, k, buf[dst], n_chunks * k);
+    topk_merge_kernel<false><<<grid, TPB, 0, st>>>(buf[src], n_in, n_in, k, buf[dst], n_chunks * k);
     ++g_clsm_launches;
     src = dst;
     n_in = n_chunks * k;
@@ -273,6 +313,135 @@ int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_
   const int64_t n = nQ * k;
   topk_decode_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(buf[src], n, 0, out_score, out_id);
   CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// ---- bf16 corpus: tensor-core scoring (topk_tc.cu) + the same exact selection --------------------------
+// The corpus is processed in segments of SEG rows.  For each 128-query block and segment: score_tc writes the
+// (128, SEG) key matrix (only keys >= the k-th best key found in earlier segments survive, the rest are 0),
+// one selection level reduces every 2048-key chunk to its k best, and a second level merges those lists with
+// the running best-k list of the block; its k-th key is the threshold for the next segment.
+constexpr int64_t SEG = 65536;
+
+__global__ void kth_key_kernel(const u64* __restrict__ best, int64_t nq, int k, u64* __restrict__ thr) {
+  const int64_t q = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (q < nq) thr[q] = best[q * k + (k - 1)];          // 0 while fewer than k candidates exist
+}
+// level-2 input row of query q: [lists of this segment (n_lists*k) | running best (k)]
+__global__ void append_best_kernel(u64* __restrict__ lists, int64_t stride, int64_t off, const u64* __restrict__ best, int64_t nq, int k) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= nq * k) return;
+  const int64_t q = i / k;
+  lists[q * stride + off + (i - q * k)] = best[i];
+}
+__global__ void normalize_rows_bf16_kernel(const float* __restrict__ sem, int64_t N, int H, __nv_bfloat16* __restrict__ vec) {
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int64_t r = static_cast<int64_t>(blockIdx.x) * (blockDim.x / 32) + warp;
+  if (r >= N) return;
+  float s = 0.0f;
+  for (int h = lane; h < H; h += 32) { const float x = sem[r * H + h]; s = fmaf(x, x, s); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float n = sqrtf(fmaxf(s, FLT_MIN));
+  for (int h = lane; h < H; h += 32) vec[r * H + h] = __float2bfloat16_rn(sem[r * H + h] / n);
+}
+
+struct TcPlan { size_t off_keys, off_l1, off_l2, off_best, off_thr, total; int64_t l1_lists; };
+TcPlan tc_plan(int k) {
+  TcPlan p{};
+  size_t o = 0;
+  auto take = [&](size_t b) { size_t r = o; o += align_up(b, 256); return r; };
+  p.l1_lists = SEG / R;                                           // 32 chunks of 2048 keys
+  p.off_keys = take(static_cast<size_t>(128) * SEG * 8);
+  p.off_l1 = take(static_cast<size_t>(128) * (p.l1_lists + 1) * k * 8);   // + running best appended
+  p.off_l2 = take(static_cast<size_t>(128) * 4 * k * 8);
+  p.off_best = take(static_cast<size_t>(128) * k * 8);
+  p.off_thr = take(128 * 8);
+  p.total = o;
+  return p;
+}
+
+}  // namespace
+
+int clsm_score_keys_tc(const void* Qn, int64_t nQ, int64_t q_begin, const void* Cn, int64_t N, int H,
+                       int64_t row_begin, int64_t row_end, unsigned long long* keys, int64_t seg_cap,
+                       const unsigned long long* thr, cudaStream_t st);     // topk_tc.cu
+
+extern "C" {
+
+int clsm_normalize_rows_bf16(const float* sem, int64_t N, int H, void* vec, void* stream) {
+  CLSM_REQUIRE(N >= 0 && H > 0, "normalize_rows_bf16: bad sizes");
+  if (N == 0) return CLSM_OK;
+  normalize_rows_bf16_kernel<<<static_cast<unsigned>(ceil_div64(N, 8)), 256, 0, as_stream(stream)>>>(sem, N, H, static_cast<__nv_bfloat16*>(vec));
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+size_t clsm_cos_topk_bf16_workspace_bytes(int64_t nQ, int64_t N, int k) { (void)nQ; (void)N; return tc_plan(k).total; }
+
+int clsm_cos_topk_bf16(const void* Qn, int64_t nQ, const void* Cn, int64_t N, int H, int k,
+                       int64_t id_base, float* out_score, int64_t* out_id,
+                       void* ws, size_t ws_bytes, void* stream) {
+  CLSM_REQUIRE(nQ > 0 && N > 0 && N < (1ll << 31), "cos_topk_bf16: bad sizes");
+  CLSM_REQUIRE(k >= 1 && k <= KMAX, "cos_topk_bf16: k must be in [1, %d]", KMAX);
+  const TcPlan p = tc_plan(k);
+  if (ws_bytes < p.total) { clsm_set_error("cos_topk_bf16: workspace too small (%zu < %zu)", ws_bytes, p.total); return CLSM_EWORKSPACE; }
+  cudaStream_t st = as_stream(stream);
+  char* w = static_cast<char*>(ws);
+  u64* keys = reinterpret_cast<u64*>(w + p.off_keys);
+  u64* l1 = reinterpret_cast<u64*>(w + p.off_l1);
+  u64* l2 = reinterpret_cast<u64*>(w + p.off_l2);
+  u64* best = reinterpret_cast<u64*>(w + p.off_best);
+  u64* thr = reinterpret_cast<u64*>(w + p.off_thr);
+  const int64_t l1_stride = (p.l1_lists + 1) * k;
+  // the scan writes survivors only and the level-1 select zeroes what it reads, so the key matrix is
+  // all-empty between segments; it has to start that way
+  CLSM_CUDA(cudaMemsetAsync(keys, 0, static_cast<size_t>(128) * SEG * 8, st));
+  for (int64_t qb = 0; qb < nQ; qb += 128) {
+    const int64_t nq = (nQ - qb < 128) ? nQ - qb : 128;
+    CLSM_CUDA(cudaMemsetAsync(best, 0, static_cast<size_t>(nq) * k * 8, st));
+    bool have_thr = false;
+    for (int64_t r0 = 0; r0 < N; r0 += SEG) {
+      const int64_t r1 = (r0 + SEG < N) ? r0 + SEG : N;
+      const int64_t rows = r1 - r0;
+      int rc = clsm_score_keys_tc(Qn, nQ, qb, Cn, N, H, r0, r1, keys, SEG, have_thr ? thr : nullptr, st);
+      if (rc != CLSM_OK) return rc;
+      // level 1: every 2048-key chunk of the segment -> its k best
+      const int64_t n_chunks = ceil_div64(rows, R);
+      {
+        dim3 grid(static_cast<unsigned>(nq), static_cast<unsigned>(n_chunks));
+        topk_merge_kernel<true><<<grid, TPB, 0, st>>>(keys, SEG, ((rows + 1) / 2) * 2, k, l1, l1_stride);
+        CLSM_LAUNCH_CHECK();
+      }
+      // level 2: those lists + the running best list -> new running best
+      append_best_kernel<<<static_cast<unsigned>(ceil_div64(nq * k, 256)), 256, 0, st>>>(l1, l1_stride, n_chunks * k, best, nq, k);
+      CLSM_LAUNCH_CHECK();
+      u64* bufs[2] = {l1, l2};
+      int64_t n_in = (n_chunks + 1) * k;
+      int src = 0;
+      int64_t stride = l1_stride;
+      while (true) {                                   // (n_chunks+1)*k <= 33*128 keys: at most two more levels
+        const int64_t nc = ceil_div64(n_in, R);
+        const int dst = src ^ 1;
+        u64* out = (nc == 1) ? best : bufs[dst];
+        dim3 grid(static_cast<unsigned>(nq), static_cast<unsigned>(nc));
+        topk_merge_kernel<false><<<grid, TPB, 0, st>>>(bufs[src], stride, n_in, k, out, nc * k);
+        CLSM_LAUNCH_CHECK();
+        if (nc == 1) break;
+        n_in = nc * k; stride = nc * k; src = dst;
+      }
+      kth_key_kernel<<<1, 128, 0, st>>>(best, nq, k, thr);
+      CLSM_LAUNCH_CHECK();
+      have_thr = true;
+    }
+    const int64_t n = nq * k;
+    topk_decode_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(best, n, id_base, out_score + qb * k, out_id + qb * k);
+    CLSM_LAUNCH_CHECK();
+  }
   return CLSM_OK;
 }
 

@@ -1,0 +1,230 @@
+// Cosine scoring of a bf16 page-vector corpus on the tensor cores, feeding the exact top-k selection of
+// topk.cu.  (No retrieval code exists in the reference; the score is RTF's cosine, cnn_dssm_tf.py:63-77,
+// on L2-normalised vectors.)
+//
+//   scores[q, row] = Qn[q, :] . Cn[row, :]          Qn (nQ, H), Cn (N, H) bf16, H a multiple of 64
+//
+// One CTA per SM, persistent over 256-row corpus tiles.  A operand = a block of 128 queries, resident in
+// shared memory for the whole launch; B operand = the corpus tile, streamed by TMA (all H/64 K-chunks of a
+// tile form one pipeline stage); D = 128 queries (TMEM lanes) x 256 rows (TMEM columns), double buffered so
+// the epilogue of tile i overlaps the MMAs of tile i+1.  The epilogue turns every score into the 64-bit key
+// (ordered(score) << 32) | ~row of topk.cu and writes it to keys[q, row - seg_begin]; with a threshold array
+// it writes only keys >= thr[q] (the matrix is all-empty on entry and the selection zeroes what it reads), which
+// is how later corpus segments are pruned by the k-th best key found so far.  The corpus is read exactly once per 128-query block: HBM-bound.
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+using namespace tcptx;
+
+namespace {
+
+constexpr int QB = 128;                       // queries per block (UMMA M)
+constexpr int NT = 256;                       // corpus rows per tile (UMMA N)
+constexpr int KCHUNK = 64;
+constexpr int NUM_EPI_WARPS = 4;
+constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
+constexpr int SMEM_LIMIT = 227 * 1024;
+
+typedef unsigned long long u64;
+
+struct ScoreParams {
+  int64_t row_begin, row_end;   // corpus rows of this segment
+  int64_t q_begin;              // first query of this block
+  int64_t nQ;
+  int hchunks;                  // H / 64
+  int n_tiles;
+  u64* keys;                    // (QB, seg_cap): keys[(q - q_begin) * seg_cap + (row - row_begin)]
+  int64_t seg_cap;
+  const u64* thr;               // (nQ) or nullptr: only keys >= thr[q] are kept
+  int stages;
+};
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmC, const ScoreParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t q_bytes = static_cast<uint32_t>(p.hchunks) * QB * 128u;          // resident query block
+  const uint32_t stage_bytes = static_cast<uint32_t>(p.hchunks) * NT * 128u;      // one corpus tile, all K chunks
+  const uint32_t stage0 = base + q_bytes;
+  const uint32_t bars = stage0 + static_cast<uint32_t>(p.stages) * stage_bytes;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (p.stages + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * p.stages + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * p.stages + 2 + a); };
+  const uint32_t q_bar = bars + 8u * (2 * p.stages + 4);
+  const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 5);
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), NUM_EPI_WARPS); }
+    mbar_init(q_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmQ) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmC) : "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // the query block, once
+      mbar_expect_tx(q_bar, q_bytes);
+      for (int hc = 0; hc < p.hchunks; ++hc)
+        tma_load_2d(base + static_cast<uint32_t>(hc) * QB * 128u, &tmQ, hc * KCHUNK, static_cast<int>(p.q_begin), q_bar);
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        const int64_t r0 = p.row_begin + static_cast<int64_t>(tile) * NT;
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        mbar_expect_tx(full_bar(stage), stage_bytes);
+        for (int hc = 0; hc < p.hchunks; ++hc)
+          tma_load_2d(stage0 + stage * stage_bytes + static_cast<uint32_t>(hc) * NT * 128u, &tmC, hc * KCHUNK, static_cast<int>(r0), full_bar(stage));
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(NT);
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0;
+      mbar_wait(q_bar, 0);
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t b_src = stage0 + stage * stage_bytes;
+        for (int hc = 0; hc < p.hchunks; ++hc) {
+#pragma unroll
+          for (int ks = 0; ks < KCHUNK / 16; ++ks)
+            tc_mma_bf16(tmem_base + static_cast<uint32_t>(acc * NT),
+                        make_sw128_desc(base + static_cast<uint32_t>(hc) * QB * 128u + ks * 32),
+                        make_sw128_desc(b_src + static_cast<uint32_t>(hc) * NT * 128u + ks * 32), idesc, (hc | ks) != 0 ? 1u : 0u);
+        }
+        tc_commit(empty_bar(stage));
+        tc_commit(tfull_bar(acc));
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    const int lq = warp & 3;
+    const int ql = lq * 32 + lane;                              // query inside the block = TMEM lane
+    const int64_t q = p.q_begin + ql;
+    const bool qok = q < p.nQ;
+    const u64 thr = (p.thr != nullptr && qok) ? p.thr[q] : 0ull;
+    u64* krow = p.keys + static_cast<int64_t>(ql) * p.seg_cap;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      const int64_t r0 = p.row_begin + static_cast<int64_t>(tile) * NT;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(acc * NT);
+#pragma unroll 1
+      for (int cb = 0; cb < NT; cb += 64) {
+        uint32_t v[4][16];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tc_ld16_async(taddr + cb + c * 16, v[c]);
+        tc_wait_ld();
+        if (cb + 64 >= NT) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(acc)); }
+        if (qok) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 2) {
+              const int64_t row = r0 + cb + c * 16 + i;
+              u64 k0 = 0ull, k1 = 0ull;
+              if (row < p.row_end) {
+                k0 = (static_cast<u64>(f32_to_ordered(__uint_as_float(v[c][i]) + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row));
+                if (k0 < thr) k0 = 0ull;
+              }
+              if (row + 1 < p.row_end) {
+                k1 = (static_cast<u64>(f32_to_ordered(__uint_as_float(v[c][i + 1]) + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row + 1));
+                if (k1 < thr) k1 = 0ull;
+              }
+              if ((k0 | k1) != 0ull)       // survivors only: the matrix is all-empty on entry (topk.cu clears what it reads)
+                *reinterpret_cast<ulonglong2*>(krow + (row - p.row_begin)) = make_ulonglong2(k0, k1);
+            }
+          }
+        }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+bool make_map(CUtensorMap* map, const void* ptr, uint64_t cols, uint64_t rows, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {KCHUNK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace
+
+// Scores queries [q_begin, q_begin+128) against corpus rows [row_begin, row_end) into keys (128, seg_cap).
+int clsm_score_keys_tc(const void* Qn, int64_t nQ, int64_t q_begin, const void* Cn, int64_t N, int H,
+                       int64_t row_begin, int64_t row_end, unsigned long long* keys, int64_t seg_cap,
+                       const unsigned long long* thr, cudaStream_t st) {
+  CLSM_REQUIRE(H == 64 || H == 128, "cos_topk(bf16): the tensor-core scan takes H = 64 or 128 (use clsm_cos_topk otherwise)");
+  CLSM_REQUIRE(N < (1ll << 31) && seg_cap % 2 == 0, "cos_topk(bf16): corpus shard too large or odd segment");
+  ScoreParams p{};
+  p.row_begin = row_begin; p.row_end = row_end; p.q_begin = q_begin; p.nQ = nQ;
+  p.hchunks = H / 64;
+  p.n_tiles = static_cast<int>(ceil_div64(row_end - row_begin, NT));
+  p.keys = keys; p.seg_cap = seg_cap; p.thr = thr;
+  const int q_bytes = p.hchunks * QB * 128;
+  const int stage_bytes = p.hchunks * NT * 128;
+  int stages = (SMEM_LIMIT - 2048 - q_bytes) / stage_bytes;
+  if (stages > 4) stages = 4;
+  CLSM_REQUIRE(stages >= 2, "cos_topk(bf16): H too large for a 2-stage pipeline");
+  p.stages = stages;
+  const int smem_bytes = q_bytes + stages * stage_bytes + 1024 + 8 * (2 * stages + 6);
+  CUtensorMap tmQ, tmC;
+  if (!make_map(&tmQ, Qn, static_cast<uint64_t>(H), static_cast<uint64_t>(nQ), QB) ||
+      !make_map(&tmC, Cn, static_cast<uint64_t>(H), static_cast<uint64_t>(N), NT)) {
+    clsm_set_error("cos_topk(bf16): cuTensorMapEncodeTiled failed");
+    return CLSM_ECUDA;
+  }
+  CLSM_CUDA(cudaFuncSetAttribute(score_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  int grid = clsm_sm_count();
+  if (grid > p.n_tiles) grid = p.n_tiles;
+  if (grid < 1) return CLSM_OK;
+  score_tc_kernel<<<grid, NUM_THREADS, smem_bytes, st>>>(tmQ, tmC, p);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}

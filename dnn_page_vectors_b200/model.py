@@ -446,19 +446,20 @@ class CLSM(object):
         return hist
 
     # ---- page vectors and retrieval (absent in the reference; composition of model() and RTF)
-    def encode_pages(self, tokens, batch_size=8192, out=None, normalise=True):
-        """tokens (N, Ld) host ints -> device tensor (N, H) fp32 of L2-normalised page vectors."""
+    def encode_pages(self, tokens, batch_size=8192, out=None, normalise=True, dtype=torch.float32):
+        """tokens (N, Ld) host ints -> device tensor (N, H) of L2-normalised page vectors.
+        dtype=torch.bfloat16 gives the compact corpus format the tensor-core retrieval path scans."""
         tokens = np.ascontiguousarray(tokens, dtype=np.int32)
-        return self._encode(self.doc_model, tokens, batch_size, out, normalise)
+        return self._encode(self.doc_model, tokens, batch_size, out, normalise, dtype)
 
-    def encode_queries(self, tokens, batch_size=8192, normalise=True):
+    def encode_queries(self, tokens, batch_size=8192, normalise=True, dtype=torch.float32):
         tokens = np.ascontiguousarray(tokens, dtype=np.int32)
-        return self._encode(self.query_model, tokens, batch_size, None, normalise)
+        return self._encode(self.query_model, tokens, batch_size, None, normalise, dtype)
 
-    def _encode(self, tower, tokens, batch_size, out, normalise):
+    def _encode(self, tower, tokens, batch_size, out, normalise, dtype=torch.float32):
         N = tokens.shape[0]
         if out is None:
-            out = torch.empty((N, tower.H), dtype=torch.float32, device=self.device)
+            out = torch.empty((N, tower.H), dtype=dtype, device=self.device)
         for s in range(0, N, batch_size):
             chunk = tokens[s:s + batch_size]
             b = tower.buffers(chunk.shape[0], False)
@@ -468,10 +469,12 @@ class CLSM(object):
 
     def encode_resident(self, tower, b, out, normalise=True):
         sem = tower.forward(b, False)
-        if normalise:
-            call("clsm_normalize_rows", _ptr(sem), b["S"], tower.H, _ptr(out), _stream())
-        else:
+        if not normalise:
             out.copy_(sem)
+        elif out.dtype == torch.bfloat16:
+            call("clsm_normalize_rows_bf16", _ptr(sem), b["S"], tower.H, _ptr(out), _stream())
+        else:
+            call("clsm_normalize_rows", _ptr(sem), b["S"], tower.H, _ptr(out), _stream())
         return out
 
     def topk(self, query_vecs, corpus_vecs, k=100, id_base=0):
@@ -480,6 +483,17 @@ class CLSM(object):
         Q, H = query_vecs.shape
         N = corpus_vecs.shape[0]
         k = int(k)
+        if corpus_vecs.dtype == torch.bfloat16:
+            # tensor-core scan of a bf16 corpus (queries are rounded to bf16 too)
+            qv = query_vecs if query_vecs.dtype == torch.bfloat16 else query_vecs.to(torch.bfloat16)
+            qv = qv.contiguous()
+            ws_bytes = lib.clsm_cos_topk_bf16_workspace_bytes(Q, N, k)
+            ws = self._scratch("topk_tc", ws_bytes)
+            sc = torch.empty((Q, k), dtype=torch.float32, device=self.device)
+            ids = torch.empty((Q, k), dtype=torch.int64, device=self.device)
+            call("clsm_cos_topk_bf16", _ptr(qv), Q, _ptr(corpus_vecs), N, H, k, int(id_base), _ptr(sc), _ptr(ids),
+                 _ptr(ws), ws_bytes, _stream())
+            return sc, ids
         ws_bytes = lib.clsm_cos_topk_workspace_bytes(Q, N, k)
         ws = self._scratch("topk", ws_bytes)
         sc = torch.empty((Q, k), dtype=torch.float32, device=self.device)

@@ -166,6 +166,16 @@ size_t clsm_topk_merge_workspace_bytes(int n_parts, int64_t nQ, int k);
 int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_t nQ, int k,
                     float* out_score, int64_t* out_id, void* ws, size_t ws_bytes, void* stream);
 
+/* bf16 corpus, tensor-core scoring (the production retrieval path): Qn (nQ, H) and Cn (N, H) are
+ * L2-normalised bf16 (clsm_normalize_rows_bf16), H = 64 or 128 (other widths: clsm_cos_topk).  The corpus is read once per block of
+ * 128 queries by a tcgen05 kernel; selection is the same exact radix select, so the order and the
+ * independence from sharding are those of clsm_cos_topk. */
+int clsm_normalize_rows_bf16(const float* sem, int64_t N, int H, void* vec, void* stream);
+size_t clsm_cos_topk_bf16_workspace_bytes(int64_t nQ, int64_t N, int k);
+int clsm_cos_topk_bf16(const void* Qn, int64_t nQ, const void* Cn, int64_t N, int H, int k,
+                       int64_t id_base, float* out_score, int64_t* out_id,
+                       void* ws, size_t ws_bytes, void* stream);
+
 /* clsm_topk_merge_static: clsm_topk_merge without a workspace argument and without any allocation.
  * (No counterpart in the reference, which has no retrieval code at all.)
  * Who needs it: a caller that is not allowed to obtain device memory at the moment it has to merge --

@@ -452,3 +452,37 @@ def test_normalize_rows():
     call("clsm_normalize_rows", P(z_d), 100, 128, P(out), ST())
     np.testing.assert_allclose(out.cpu().numpy(), O.normalise_rows(z.astype(np.float64)), rtol=1e-5, atol=1e-7)
     assert (out[3] == 0).all()
+
+
+# ------------------------------------------------------------------ top-k, bf16 corpus on the tensor cores
+@pytest.mark.parametrize("Q,N,H,k", [(3, 50, 64, 10), (9, 5000, 128, 100), (130, 70000, 128, 100), (200, 300000, 128, 100),
+                                     (2, 65537, 64, 128), (1, 7, 64, 10)])
+def test_cos_topk_bf16_matches_oracle(Q, N, H, k):
+    rng = np.random.RandomState(13)
+    c = bf16_round(O.normalise_rows(rng.randn(N, H)))
+    q = bf16_round(O.normalise_rows(rng.randn(Q, H)))
+    if N > 40:
+        c[17] = c[5]; c[N - 1] = c[5]; q[0] = c[5]            # exact ties across segments -> lowest id first
+    cd, qd = dev(c).to(torch.bfloat16), dev(q).to(torch.bfloat16)
+    ws_bytes = lib.clsm_cos_topk_bf16_workspace_bytes(Q, N, k)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    sc = torch.empty((Q, k), dtype=torch.float32, device=DEV)
+    ids = torch.empty((Q, k), dtype=torch.int64, device=DEV)
+    call("clsm_cos_topk_bf16", P(qd), Q, P(cd), N, H, k, 1000, P(sc), P(ids), P(ws), ws_bytes, ST())
+    osc, oid = O.cos_topk(q.astype(np.float64), c.astype(np.float64), k, id_base=1000)   # same bf16-rounded inputs
+    kk = min(k, N)
+    got_s, got_i = sc.cpu().numpy(), ids.cpu().numpy()
+    np.testing.assert_allclose(got_s[:, :kk], osc, rtol=2e-5, atol=2e-6)       # exact bf16 products, fp32 accumulate
+    if kk < k:
+        assert (got_i[:, kk:] == -1).all()
+    mism = got_i[:, :kk] != oid
+    assert mism.mean() < 0.02
+    for r, j in np.argwhere(mism):
+        assert abs(got_s[r, j] - osc[r, j]) < 1e-5
+    if N > 40:
+        assert list(got_i[0, :3]) == [1005, 1017, 1000 + N - 1]
+    assert (np.diff(got_s[:, :kk], axis=1) <= 0).all()
+    # second call straight after (workspace reuse): identical answer
+    sc2 = torch.empty_like(sc); ids2 = torch.empty_like(ids)
+    call("clsm_cos_topk_bf16", P(qd), Q, P(cd), N, H, k, 1000, P(sc2), P(ids2), P(ws), ws_bytes, ST())
+    assert torch.equal(ids2, ids) and torch.equal(sc2, sc)
