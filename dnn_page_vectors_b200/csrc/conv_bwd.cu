@@ -17,6 +17,8 @@ size_t clsm_conv_bwd_dx_fast_bytes(int64_t S, int L, int F);
 int clsm_conv_bwd_dx_fast(const void* Wt, int dtype, int k, int Dpad, int L, int64_t S, const float* G, const int32_t* A,
                           int ldp, int col0, int F, float* dX, int accumulate, void* scratch, cudaStream_t st);
 
+int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, int max_splits, const float* G,
+                        const int32_t* A, int ldp, int col0, int F, int k, float* part, cudaStream_t st);          // conv_bwd_tc.cu
 size_t clsm_conv_bwd_dx_tc_bytes(int k, int Dpad, int F);                                               // conv_bwd_tc.cu
 int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64_t S, const float* G, const int32_t* A,
                         int ldp, int col0, int F, float* dX, int accumulate, void* scratch, cudaStream_t st);
@@ -247,7 +249,11 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
   w += align_up(static_cast<size_t>(kColsumChunks) * F * 4, 256);
   void* sort_scratch = w;
 
-  int rc = clsm_conv_bwd_dw_fast(X, dtype, L, Dpad, S, n_groups, G, argmax, ldp, col0, F, k, part, st);
+  // dW: tensor cores (bf16 mode) -> shared-memory staged CUDA cores -> generic
+  int n_parts = n_groups;
+  int rc = clsm_conv_bwd_dw_tc(X, dtype, L, Dpad, S, n_groups, G, argmax, ldp, col0, F, k, part, st);
+  if (rc > 0) { n_parts = rc; rc = CLSM_OK; }
+  else if (rc == CLSM_EUNSUPPORTED) rc = clsm_conv_bwd_dw_fast(X, dtype, L, Dpad, S, n_groups, G, argmax, ldp, col0, F, k, part, st);
   if (rc == CLSM_EUNSUPPORTED) {            // shape outside the shared-memory plan: generic kernel
     dim3 grid(n_groups, Dpad / 64, (F + FT - 1) / FT);
     rc = dtype == CLSM_BF16
@@ -259,7 +265,7 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
     return rc;
   }
   const int64_t ne = static_cast<int64_t>(k) * D * F;
-  conv_bwd_dw_reduce_kernel<<<static_cast<unsigned>(ceil_div64(ne, 256)), 256, 0, st>>>(part, n_groups, k, D, Dpad, F, dW_ref);
+  conv_bwd_dw_reduce_kernel<<<static_cast<unsigned>(ceil_div64(ne, 256)), 256, 0, st>>>(part, n_parts, k, D, Dpad, F, dW_ref);
   CLSM_LAUNCH_CHECK();
   if (clsm_colsum(G, S, ldp, col0, F, db, cs, kColsumChunks, st) != CLSM_OK) { clsm_set_error("conv_pool_bwd: colsum launch failed"); return CLSM_ECUDA; }
 

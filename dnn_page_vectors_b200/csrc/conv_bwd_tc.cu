@@ -217,6 +217,235 @@ dx_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const DxParams p) {
   }
 }
 
+// =====================================================================================================
+// dW on the tensor cores:  dWt[f, (j,c)] = sum_r dY[r, f] * X[r + j, c]   (r = flat token row; dY[r, f] =
+// G[s,f] at the arg-max row of (s,f), zero elsewhere).  The reduction runs over TOKENS, so
+//   A operand = dY^T tile (128 filters x 64 tokens per M tile, K-major), built in swizzled shared memory by
+//               the builder warps exactly like the Gt tile above (one non-zero per (sequence, filter));
+//   B operand = the token tile itself, X[r0+j .. r0+j+63, c0 .. c0+127], whose K dimension (tokens) is the
+//               SLOW dimension of X: an MN-major operand.  A TMA box of 64 token rows x 64 columns with the
+//               128-byte swizzle is precisely the canonical MN-major SW128 layout (8-row K atoms 1024 B apart
+//               = SBO, 64-column blocks one box apart = LBO), so the rows of X feed the tensor core untouched;
+//               the window offset j is again just the TMA row coordinate.
+// Each CTA owns one (j, 128-column range) slice of dW for all filters (3 M tiles x 128 TMEM columns) and one
+// split of the token range; partial sums go to the same part[split][f][j][c] buffer the CUDA-core kernels use
+// and are reduced in fixed order by conv_bwd_dw_reduce_kernel.
+struct DwParams {
+  int64_t n_rows;
+  int L, k, F, Dpad;
+  int n_mt;                    // filter M tiles
+  int n_cr;                    // 128-column ranges of Dpad
+  int n_slices;                // k * n_cr
+  int64_t chunks_total, chunks_per_split;
+  const float* G; const int32_t* A; int ldp, col0;
+  float* part;
+  int stages;
+};
+
+__device__ __forceinline__ uint64_t make_sw128_mn_desc(uint32_t saddr, uint32_t lbo_bytes) {
+  return static_cast<uint64_t>((saddr & 0x3FFFFu) >> 4) | (static_cast<uint64_t>(lbo_bytes >> 4) << 16) |
+         (static_cast<uint64_t>(1024 >> 4) << 32) | (static_cast<uint64_t>(1) << 46) | (static_cast<uint64_t>(2) << 61);
+}
+
+constexpr int DW_NT = 128;          // (j, c) columns per CTA = UMMA N
+constexpr int DW_KT = 64;           // tokens per chunk
+constexpr int DW_BLD_WARPS = 8;     // warps 2..9: builders during the main loop, epilogue at the end
+constexpr int DW_THREADS = 64 + DW_BLD_WARPS * 32;
+
+template <int MAXSEQ>          // sequences a 64-token chunk can touch: 2 when L >= 64, else up to 5 (L >= 16)
+__global__ void __launch_bounds__(DW_THREADS, 1)
+dw_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t a_bytes = static_cast<uint32_t>(p.n_mt) * MT_BYTES;        // dY^T: n_mt x (128 f x 64 tokens)
+  const uint32_t b_bytes = 2u * DW_KT * 128u;                               // X: two boxes of 64 tokens x 64 columns
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t bars = base + static_cast<uint32_t>(p.stages) * stage_bytes;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (p.stages + s); };
+  const uint32_t tfull_bar = bars + 8u * (2 * p.stages);
+  const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 1);
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int split = blockIdx.x / p.n_slices;
+  const int slice = blockIdx.x - split * p.n_slices;
+  const int j = slice / p.n_cr, c0 = (slice - j * p.n_cr) * DW_NT;
+  const int64_t ch_begin = static_cast<int64_t>(split) * p.chunks_per_split;
+  const int64_t ch_end = (ch_begin + p.chunks_per_split < p.chunks_total) ? ch_begin + p.chunks_per_split : p.chunks_total;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1 + DW_BLD_WARPS); mbar_init(empty_bar(s), 1); }
+    mbar_init(tfull_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmX) : "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int64_t ch = ch_begin; ch < ch_end; ++ch) {
+        const int r0 = static_cast<int>(ch * DW_KT);
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        mbar_expect_tx(full_bar(stage), b_bytes);
+        const uint32_t b_dst = base + stage * stage_bytes + a_bytes;
+        tma_load_2d(b_dst, &tmX, c0, r0 + j, full_bar(stage));
+        tma_load_2d(b_dst + DW_KT * 128u, &tmX, c0 + 64, r0 + j, full_bar(stage));
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(DW_NT) | (1u << 16);                 // B operand MN-major
+      int stage = 0; uint32_t phase = 0;
+      bool first = true;
+      for (int64_t ch = ch_begin; ch < ch_end; ++ch) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t a_src = base + stage * stage_bytes;
+        const uint32_t b_src = a_src + a_bytes;
+#pragma unroll
+        for (int ks = 0; ks < DW_KT / 16; ++ks) {
+          const uint32_t accum = (first && ks == 0) ? 0u : 1u;
+          const uint64_t bdesc = make_sw128_mn_desc(b_src + ks * 2048u, DW_KT * 128u);   // 16 tokens = two 8-row K atoms
+          for (int m = 0; m < p.n_mt; ++m)
+            tc_mma_bf16(tmem_base + static_cast<uint32_t>(m * DW_NT), make_sw128_desc(a_src + m * MT_BYTES + ks * 32), bdesc, idesc, accum);
+        }
+        first = false;
+        tc_commit(empty_bar(stage));
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+      tc_commit(tfull_bar);
+    }
+  } else {
+    // ---- builders: dY^T tile of every chunk.  The (G, arg-max) pairs a thread needs for chunk ch+1 are
+    // fetched into registers while it scatters chunk ch, so no global-load latency sits on the critical path.
+    const int bt = threadIdx.x - 64;
+    constexpr int NB = DW_BLD_WARPS * 32;
+    constexpr int MAXFI = 2;                           // F <= 512
+    uint32_t phase = 0;
+    const uint32_t zero_chunks = a_bytes / 16;
+    float g_nxt[MAXSEQ * MAXFI]; int a_nxt[MAXSEQ * MAXFI];
+    // (first sequence, offset of the chunk's first token inside it) of the chunk being PREFETCHED and of the
+    // chunk being BUILT, advanced by 64 tokens per chunk -- no division on the per-chunk path
+    int64_t ps = (ch_begin * DW_KT) / p.L;
+    int pt = static_cast<int>(ch_begin * DW_KT - ps * p.L);
+    int64_t cs = ps; int ct = pt;
+    const int64_t S_total = p.n_rows / p.L;
+    auto prefetch = [&](int64_t ch) {
+      // sequences touched: tokens [pt, pt+63] of sequence ps onward
+      const int nseq = (pt + DW_KT - 1) / p.L + 1;
+      const float* gp = p.G + ps * p.ldp + p.col0 + bt;
+      const int32_t* ap = p.A + ps * p.ldp + p.col0 + bt;
+#pragma unroll
+      for (int sq = 0; sq < MAXSEQ; ++sq)
+#pragma unroll
+        for (int fi = 0; fi < MAXFI; ++fi) {
+          const bool ok = ch < ch_end && sq < nseq && ps + sq < S_total && bt + fi * NB < p.F;
+          g_nxt[sq * MAXFI + fi] = ok ? __ldg(gp + static_cast<int64_t>(sq) * p.ldp + fi * NB) : 0.0f;
+          a_nxt[sq * MAXFI + fi] = ok ? __ldg(ap + static_cast<int64_t>(sq) * p.ldp + fi * NB) : 0;
+        }
+      pt += DW_KT;
+      while (pt >= p.L) { pt -= p.L; ++ps; }
+    };
+    // The tiles start all-zero and every thread un-writes exactly what IT wrote the last time the stage was
+    // used (its candidates never collide with another thread's), so no 48 KB re-zeroing and no barrier per chunk.
+    for (int st = 0; st < p.stages; ++st) {
+      uint8_t* atile = base_ptr + st * stage_bytes;
+      for (uint32_t i = bt; i < zero_chunks; i += NB) reinterpret_cast<uint4*>(atile)[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(NB) : "memory");
+    constexpr uint32_t NONE = 0xFFFFFFFFu;
+    uint32_t wrote[3][MAXSEQ * MAXFI];                 // byte offsets written per stage (p.stages == 3)
+#pragma unroll
+    for (int st = 0; st < 3; ++st)
+#pragma unroll
+      for (int i = 0; i < MAXSEQ * MAXFI; ++i) wrote[st][i] = NONE;
+    prefetch(ch_begin);
+    for (int64_t chb = ch_begin; chb < ch_end; chb += 3) {
+#pragma unroll
+      for (int st = 0; st < 3; ++st) {
+        const int64_t ch = chb + st;
+        if (ch < ch_end) {
+          float g_cur[MAXSEQ * MAXFI]; int a_cur[MAXSEQ * MAXFI];
+#pragma unroll
+          for (int i = 0; i < MAXSEQ * MAXFI; ++i) { g_cur[i] = g_nxt[i]; a_cur[i] = a_nxt[i]; }
+          prefetch(ch + 1);
+          mbar_wait(empty_bar(st), phase ^ 1u);
+          uint8_t* atile = base_ptr + st * stage_bytes;
+#pragma unroll
+          for (int i = 0; i < MAXSEQ * MAXFI; ++i)
+            if (wrote[st][i] != NONE) *reinterpret_cast<uint16_t*>(atile + wrote[st][i]) = 0;
+#pragma unroll
+          for (int sq = 0; sq < MAXSEQ; ++sq)
+#pragma unroll
+            for (int fi = 0; fi < MAXFI; ++fi) {
+              const float g = g_cur[sq * MAXFI + fi];
+              const int f = bt + fi * NB;
+              const int n = sq * p.L + a_cur[sq * MAXFI + fi] - ct;          // token column inside the chunk
+              uint32_t off = NONE;
+              if (g != 0.0f && n >= 0 && n < DW_KT) {
+                const uint32_t fl = static_cast<uint32_t>(f) & 127u;
+                off = static_cast<uint32_t>(f >> 7) * MT_BYTES + fl * 128u +
+                      (((static_cast<uint32_t>(n) >> 3) ^ (fl & 7u)) << 4) + (static_cast<uint32_t>(n) & 7u) * 2u;
+                *reinterpret_cast<__nv_bfloat16*>(atile + off) = __float2bfloat16_rn(g);
+              }
+              wrote[st][sq * MAXFI + fi] = off;
+            }
+          ct += DW_KT;
+          while (ct >= p.L) { ct -= p.L; ++cs; }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(full_bar(st));
+        }
+      }
+      phase ^= 1u;
+    }
+    // ---- epilogue (same warps): D[f, n] -> part[split][f][j][c0 + n]
+    const int lq = warp & 3;
+    const int half = (warp - 2) >> 2;                      // 64 of the 128 columns each
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    for (int m = 0; m < p.n_mt; ++m) {
+      const int f = m * MT + lq * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(m * DW_NT + half * 64);
+      uint32_t v[4][16];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) tc_ld16_async(taddr + q * 16, v[q]);
+      tc_wait_ld();
+      if (f < p.F) {
+        float* dst = p.part + ((static_cast<int64_t>(split) * p.F + f) * p.k + j) * p.Dpad + c0 + half * 64;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+#pragma unroll
+          for (int i = 0; i < 16; i += 4) {
+            const int n = q * 16 + i;
+            if (c0 + half * 64 + n < p.Dpad)
+              *reinterpret_cast<float4*>(dst + n) = make_float4(__uint_as_float(v[q][i]), __uint_as_float(v[q][i + 1]),
+                                                                 __uint_as_float(v[q][i + 2]), __uint_as_float(v[q][i + 3]));
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -292,4 +521,52 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
 #undef DX_LAUNCH
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
+}
+
+// dW on the tensor cores.  Returns the number of token splits written to `part` (>= 1), or a negative code.
+int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, int max_splits, const float* G,
+                        const int32_t* A, int ldp, int col0, int F, int k, float* part, cudaStream_t st) {
+  if (dtype != CLSM_BF16) return CLSM_EUNSUPPORTED;
+  const char* env = getenv("CLSM_CONV_BWD_DW");
+  if (env != nullptr && env[0] == 's') return CLSM_EUNSUPPORTED;       // force the CUDA-core path
+  DwParams p{};
+  p.n_rows = S * L; p.L = L; p.k = k; p.F = F; p.Dpad = Dpad;
+  p.n_mt = (F + MT - 1) / MT;
+  p.n_cr = (Dpad + DW_NT - 1) / DW_NT;
+  p.n_slices = k * p.n_cr;
+  if (p.n_mt * DW_NT > 512 || p.n_rows + 512 >= (1ll << 31) || L < 16 || F > 512) return CLSM_EUNSUPPORTED;
+  int splits = clsm_sm_count() / p.n_slices;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) return CLSM_EUNSUPPORTED;
+  p.chunks_total = ceil_div64(p.n_rows, DW_KT);
+  if (splits > p.chunks_total) splits = static_cast<int>(p.chunks_total);
+  p.chunks_per_split = ceil_div64(p.chunks_total, splits);
+  p.G = G; p.A = A; p.ldp = ldp; p.col0 = col0; p.part = part;
+  const int stage_bytes = p.n_mt * MT_BYTES + 2 * DW_KT * 128;
+  int stages = (SMEM_LIMIT - 2048) / stage_bytes;
+  if (stages < 3) return CLSM_EUNSUPPORTED;
+  stages = 3;                                   // the builders' un-write bookkeeping is unrolled for 3 stages
+  p.stages = stages;
+  const int smem_bytes = stages * stage_bytes + 1024 + 8 * (2 * stages + 3);
+  EncodeTiledFn enc = get_encode();
+  if (!enc) { clsm_set_error("conv_pool_bwd(tcgen05): cuTensorMapEncodeTiled unavailable"); return CLSM_ECUDA; }
+  CUtensorMap tmX;
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(Dpad), static_cast<cuuint64_t>(p.n_rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(Dpad) * 2};
+  cuuint32_t box[2] = {64, DW_KT};
+  cuuint32_t estr[2] = {1, 1};
+  if (enc(&tmX, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(X), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+    clsm_set_error("conv_pool_bwd(tcgen05): cuTensorMapEncodeTiled failed");
+    return CLSM_ECUDA;
+  }
+  if (L >= DW_KT) {
+    CLSM_CUDA(cudaFuncSetAttribute(dw_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    dw_tc_kernel<2><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
+  } else {
+    CLSM_CUDA(cudaFuncSetAttribute(dw_tc_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    dw_tc_kernel<5><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
+  }
+  CLSM_LAUNCH_CHECK();
+  return splits;
 }
