@@ -54,7 +54,7 @@ __global__ void pack_wb_kernel(const __nv_bfloat16* __restrict__ Wt, int k, int 
   Wb[i] = f < F ? Wt[static_cast<int64_t>(f) * k * Dpad + static_cast<int64_t>(j) * Dpad + c] : __float2bfloat16_rn(0.0f);
 }
 
-template <int NCH>
+template <int NCH, int MAXC>      // MAXC = candidate slots per builder thread per chunk: ceil(sequences per tile * 64 / 128)
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 dx_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const DxParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -99,7 +99,8 @@ dx_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const DxParams p) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           mbar_expect_tx(full_bar(stage), a_bytes);
           const uint32_t a_dst = base + stage * stage_bytes;
-          for (int m = 0; m < p.n_mt; ++m) tma_load_2d(a_dst + m * MT_BYTES, &tmWb, kc * KCHUNK, m * MT, full_bar(stage));
+          const int fbq = kc / p.k, jq = kc - fbq * p.k;               // chunk order: filter block outer, window offset inner
+          for (int m = 0; m < p.n_mt; ++m) tma_load_2d(a_dst + m * MT_BYTES, &tmWb, (jq * p.fblocks + fbq) * KCHUNK, m * MT, full_bar(stage));
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
       }
@@ -167,44 +168,89 @@ dx_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const DxParams p) {
       acc_phase ^= 1u;
     }
   } else {
-    // ---- Gt builders: 4 warps fill the B tile of every stage
+    // ---- Gt builders: 4 warps fill the B tile of every stage.  Chunks run filter-block outer / window offset
+    // inner, so a thread's (G, arg-max) candidates are fetched once per filter block (prefetched one block
+    // ahead, in registers) and reused for the k offsets; tiles start all-zero and each thread un-writes what it
+    // wrote the last time the stage was used.
     const int bt = threadIdx.x - (2 + NUM_EPI_WARPS) * 32;        // 0..127
     constexpr int NB = NUM_BLD_WARPS * 32;
-    int stage = 0; uint32_t phase = 0;
-    const uint32_t zero_chunks = b_bytes / 16;                     // 16-byte chunks of the tile
-    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+    constexpr uint32_t NONE = 0xFFFFFFFFu;
+    const uint32_t zero_chunks = (stage_bytes - a_bytes) / 16;
+    for (int st = 0; st < p.stages; ++st) {
+      uint8_t* btile = base_ptr + st * stage_bytes + a_bytes;
+      for (uint32_t i = bt; i < zero_chunks; i += NB) reinterpret_cast<uint4*>(btile)[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(NB) : "memory");
+    uint32_t wrote[3][MAXC];
+#pragma unroll
+    for (int st = 0; st < 3; ++st)
+#pragma unroll
+      for (int c = 0; c < MAXC; ++c) wrote[st][c] = NONE;
+    float g_nxt[MAXC]; int a_nxt[MAXC];
+    // state of the block being prefetched: (tile, fb); of the block being built: tile geometry
+    int ptile = blockIdx.x, pfb = 0;
+    auto tile_geom = [&](int tile, int64_t& s_first, int& t0, int& nseq) {
       const int64_t r0 = static_cast<int64_t>(tile) * p.NT;
       const int64_t r_last = (r0 + p.NT < p.n_rows ? r0 + p.NT : p.n_rows) - 1;
-      const int64_t s_first = r0 / p.L;
-      const int nseq = r_last >= r0 ? static_cast<int>(r_last / p.L - s_first) + 1 : 0;
-      for (int kc = 0; kc < nk; ++kc) {
-        const int j = kc / p.fblocks, fb = kc - j * p.fblocks;
-        mbar_wait(empty_bar(stage), phase ^ 1u);
-        uint8_t* btile = base_ptr + stage * stage_bytes + a_bytes;
-        for (uint32_t i = bt; i < zero_chunks; i += NB) reinterpret_cast<uint4*>(btile)[i] = make_uint4(0u, 0u, 0u, 0u);
-        asm volatile("bar.sync 1, %0;" ::"n"(NB) : "memory");        // zeros land before anyone scatters
-        // candidates: (sequence in tile, filter in this 64-block)
-        for (int cidx = bt; cidx < nseq * 64; cidx += NB) {
-          const int sq = cidx >> 6, fl = cidx & 63;
-          const int f = fb * 64 + fl;
-          if (f < p.F) {
-            const int64_t s = s_first + sq;
-            const float g = __ldg(p.G + s * p.ldp + p.col0 + f);
-            if (g != 0.0f) {
-              const int a = __ldg(p.A + s * p.ldp + p.col0 + f);
-              const int64_t n = s * p.L + a + j - r0;                  // token column of this hit inside the tile
-              if (n >= 0 && n < p.NT) {
-                const uint32_t off = static_cast<uint32_t>(n) * 128u + ((static_cast<uint32_t>(fl >> 3) ^ (static_cast<uint32_t>(n) & 7u)) << 4) +
-                                     static_cast<uint32_t>(fl & 7) * 2u;
-                *reinterpret_cast<__nv_bfloat16*>(btile + off) = __float2bfloat16_rn(g);
-              }
+      s_first = r0 / p.L;
+      t0 = static_cast<int>(r0 - s_first * p.L);
+      nseq = r_last >= r0 ? static_cast<int>(r_last / p.L - s_first) + 1 : 0;
+    };
+    int64_t ps_first = 0; int pt0 = 0, pnseq = 0;
+    if (ptile < p.n_tiles) tile_geom(ptile, ps_first, pt0, pnseq);
+    auto prefetch = [&]() {
+#pragma unroll
+      for (int c = 0; c < MAXC; ++c) {
+        const int cidx = bt + c * NB;
+        const int sq = cidx >> 6, f = pfb * 64 + (cidx & 63);
+        const bool ok = ptile < p.n_tiles && sq < pnseq && f < p.F;
+        g_nxt[c] = ok ? __ldg(p.G + (ps_first + sq) * p.ldp + p.col0 + f) : 0.0f;
+        a_nxt[c] = ok ? __ldg(p.A + (ps_first + sq) * p.ldp + p.col0 + f) : 0;
+      }
+      if (++pfb == p.fblocks) {
+        pfb = 0;
+        ptile += gridDim.x;
+        if (ptile < p.n_tiles) tile_geom(ptile, ps_first, pt0, pnseq);
+      }
+    };
+    prefetch();
+    int st = 0; uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      int64_t s_first; int t0, nseq;
+      tile_geom(tile, s_first, t0, nseq);
+      for (int fb = 0; fb < p.fblocks; ++fb) {
+        float g_cur[MAXC]; int a_cur[MAXC];
+#pragma unroll
+        for (int c = 0; c < MAXC; ++c) { g_cur[c] = g_nxt[c]; a_cur[c] = a_nxt[c]; }
+        prefetch();
+        for (int j = 0; j < p.k; ++j) {
+          mbar_wait(empty_bar(st), phase ^ 1u);
+          uint8_t* btile = base_ptr + st * stage_bytes + a_bytes;
+          // the stage index is a runtime value: select the bookkeeping row with predicated copies
+          uint32_t w_old[MAXC];
+#pragma unroll
+          for (int c = 0; c < MAXC; ++c) w_old[c] = st == 0 ? wrote[0][c] : st == 1 ? wrote[1][c] : wrote[2][c];
+#pragma unroll
+          for (int c = 0; c < MAXC; ++c)
+            if (w_old[c] != NONE) *reinterpret_cast<uint16_t*>(btile + w_old[c]) = 0;
+#pragma unroll
+          for (int c = 0; c < MAXC; ++c) {
+            const int cidx = bt + c * NB;
+            const int sq = cidx >> 6, fl = cidx & 63;
+            const int n = sq * p.L + a_cur[c] + j - t0;               // token column of this hit inside the tile
+            uint32_t off = NONE;
+            if (g_cur[c] != 0.0f && n >= 0 && n < p.NT) {
+              off = static_cast<uint32_t>(n) * 128u + ((static_cast<uint32_t>(fl >> 3) ^ (static_cast<uint32_t>(n) & 7u)) << 4) +
+                    static_cast<uint32_t>(fl & 7) * 2u;
+              *reinterpret_cast<__nv_bfloat16*>(btile + off) = __float2bfloat16_rn(g_cur[c]);
             }
+            if (st == 0) wrote[0][c] = off; else if (st == 1) wrote[1][c] = off; else wrote[2][c] = off;
           }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(full_bar(st));
+          if (++st == p.stages) { st = 0; phase ^= 1u; }
         }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA's async reads
-        __syncwarp();
-        if (lane == 0) mbar_arrive(full_bar(stage));
-        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
     }
   }
@@ -487,10 +533,14 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
   const int a_rows = p.n_mt * MT;
   const int stage_bytes = a_rows * 128 + ((p.NT * 128 + 1023) / 1024) * 1024;
   int stages = (SMEM_LIMIT - 2048) / stage_bytes;
-  if (stages > 6) stages = 6;
-  if (stages < 2) return CLSM_EUNSUPPORTED;
+  if (stages < 3) return CLSM_EUNSUPPORTED;
+  stages = 3;                                   // the builders' un-write bookkeeping is laid out for 3 stages
   p.stages = stages;
   const int smem_bytes = stages * stage_bytes + 1024 + 8 * (2 * stages + 4);
+  // sequences one tile can touch -> candidate slots per builder thread (128 threads, 64 filters per block)
+  const int max_seq = (p.NT + L - 1) / L + 1;
+  const int maxc = (max_seq * 64 + 127) / 128;
+  if (maxc > 5) return CLSM_EUNSUPPORTED;
 
   __nv_bfloat16* Wb = static_cast<__nv_bfloat16*>(scratch);
   const int64_t n_wb = static_cast<int64_t>(Dpad) * k * Fk;
@@ -512,12 +562,13 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
   int grid = clsm_sm_count();
   if (grid > p.n_tiles) grid = p.n_tiles;
   const int nch = p.NT / 32;
-#define DX_LAUNCH(N)                                                                                          \
-  do {                                                                                                        \
-    CLSM_CUDA(cudaFuncSetAttribute(dx_tc_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)); \
-    dx_tc_kernel<N><<<grid, NUM_THREADS, smem_bytes, st>>>(tmWb, p);                                          \
+#define DX_LAUNCH(N, C)                                                                                          \
+  do {                                                                                                           \
+    CLSM_CUDA(cudaFuncSetAttribute(dx_tc_kernel<N, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)); \
+    dx_tc_kernel<N, C><<<grid, NUM_THREADS, smem_bytes, st>>>(tmWb, p);                                          \
   } while (0)
-  if (nch == 4) DX_LAUNCH(4); else if (nch == 5) DX_LAUNCH(5); else DX_LAUNCH(8);
+  if (maxc <= 2) { if (nch == 4) DX_LAUNCH(4, 2); else if (nch == 5) DX_LAUNCH(5, 2); else DX_LAUNCH(8, 2); }
+  else           { if (nch == 4) DX_LAUNCH(4, 5); else if (nch == 5) DX_LAUNCH(5, 5); else DX_LAUNCH(8, 5); }
 #undef DX_LAUNCH
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
