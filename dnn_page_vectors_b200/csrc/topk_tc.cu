@@ -35,7 +35,7 @@ struct ScoreParams {
   int n_tiles;
   u64* keys;                    // (QB, seg_cap): keys[(q - q_begin) * seg_cap + (row - row_begin)]
   int64_t seg_cap;
-  const u64* thr;               // (nQ) or nullptr: only keys >= thr[q] are kept
+  const u64* thr;               // (128) or nullptr: only keys >= thr[q - q_begin] are kept
   int stages;
 };
 
@@ -120,7 +120,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int ql = lq * 32 + lane;                              // query inside the block = TMEM lane
     const int64_t q = p.q_begin + ql;
     const bool qok = q < p.nQ;
-    const u64 thr = (p.thr != nullptr && qok) ? p.thr[q] : 0ull;
+    const u64 thr = (p.thr != nullptr && qok) ? p.thr[ql] : 0ull;      // thresholds are indexed inside the query block
     u64* krow = p.keys + static_cast<int64_t>(ql) * p.seg_cap;
     int acc = 0; uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {

@@ -251,7 +251,7 @@ def test_conv_pool_bwd(bf16, shape):
     A[0, col0:col0 + F] = 0; A[1, col0:col0 + F] = L - k                  # edges
     Xd, Wt = make_X(X, Dpad, bf16), pack_w(W, Dpad, Fpad, bf16)
     ws_bytes = lib.clsm_conv_bwd_workspace_bytes(S, L, k, D, F)
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    ws = torch.full((ws_bytes,), 0xA5, dtype=torch.uint8, device=DEV)       # poisoned workspace
     dW = torch.empty((k, D, F), dtype=torch.float32, device=DEV)
     db = torch.empty(F, dtype=torch.float32, device=DEV)
     dX = torch.full((S * L, Dpad), 3.0, dtype=torch.float32, device=DEV)
@@ -297,7 +297,7 @@ def test_conv_pool_bwd(bf16, shape):
 def run_scatter(tok, dX, D, V1, keep=1.0, seed=0):
     n_tok, Dpad = dX.shape
     ws_bytes = lib.clsm_emb_scatter_workspace_bytes(n_tok, D)
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    ws = torch.full((ws_bytes,), 0xA5, dtype=torch.uint8, device=DEV)       # poisoned workspace
     uniq = torch.full((n_tok,), -7, dtype=torch.int32, device=DEV)
     nu = torch.zeros(1, dtype=torch.int32, device=DEV)
     rows = torch.full((min(n_tok, V1), Dpad), 9.0, dtype=torch.float32, device=DEV)
@@ -401,7 +401,7 @@ def test_cos_topk_matches_oracle(Q, N, H, k):
         c[17] = c[5]; c[N - 1] = c[5]; q[0] = c[5]            # exact ties -> lowest id first
     cd, qd = dev(c), dev(q)
     ws_bytes = lib.clsm_cos_topk_workspace_bytes(Q, N, k)
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    ws = torch.full((ws_bytes,), 0xA5, dtype=torch.uint8, device=DEV)       # poisoned workspace
     sc = torch.empty((Q, k), dtype=torch.float32, device=DEV)
     ids = torch.empty((Q, k), dtype=torch.int64, device=DEV)
     call("clsm_cos_topk", P(qd), Q, P(cd), N, H, k, 1000, P(sc), P(ids), P(ws), ws_bytes, ST())
@@ -471,7 +471,7 @@ def test_cos_topk_bf16_matches_oracle(Q, N, H, k):
         c[17] = c[5]; c[N - 1] = c[5]; q[0] = c[5]            # exact ties across segments -> lowest id first
     cd, qd = dev(c).to(torch.bfloat16), dev(q).to(torch.bfloat16)
     ws_bytes = lib.clsm_cos_topk_bf16_workspace_bytes(Q, N, k)
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    ws = torch.full((ws_bytes,), 0xA5, dtype=torch.uint8, device=DEV)       # poisoned: nothing may be read before written
     sc = torch.empty((Q, k), dtype=torch.float32, device=DEV)
     ids = torch.empty((Q, k), dtype=torch.int64, device=DEV)
     call("clsm_cos_topk_bf16", P(qd), Q, P(cd), N, H, k, 1000, P(sc), P(ids), P(ws), ws_bytes, ST())
