@@ -43,10 +43,14 @@ struct TcParams {
   unsigned long long* keys;
   int wbox, n_wbox;      // TMA box rows for W and how many boxes per stage
   int stages;
-  int shift_mode;        // 0: one X box per (j, c) chunk.  >0: one X box (NT + halo rows) per c chunk, reused for all j
-                         //    through a B descriptor whose start is advanced by j rows (1/2/3 = base_offset 0 / j / 8-j)
-  int xrows;             // rows of the X box in shift mode (NT + k - 1 rounded up to 8)
-  int xstages, wstages;
+  int shift_mode;        // 0: K-outer loop, one X box per (j, c) chunk, all M tiles per stage, one accumulator barrier.
+                         // 1: M-tile-outer loop over a RESIDENT token tile: one X box (NT + halo rows) per c chunk stays in
+                         //    shared memory for the whole tile and serves every window offset j through a B descriptor whose
+                         //    start is advanced by j rows (the UMMA swizzle works on absolute address bits, base_offset 0);
+                         //    weights stream one (M tile, j, c) chunk per slot; each M tile's TMEM region has its own
+                         //    full/empty barrier, so the epilogue of region m overlaps the MMAs of region m+1.
+  int xrows;             // rows of the X box in mode 1 (NT + k - 1 rounded up to 8)
+  int xstages, wstages;  // mode 1: xstages = cpj token slots, wstages weight slots of one M tile chunk (16 KB)
 };
 
 using namespace tcptx;
@@ -61,21 +65,20 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   const uint32_t stage_bytes = a_bytes + ((b_bytes + 1023u) & ~1023u);
   const uint32_t data_bytes = p.shift_mode == 0
       ? static_cast<uint32_t>(p.stages) * stage_bytes
-      : static_cast<uint32_t>(p.wstages) * a_bytes + static_cast<uint32_t>(p.xstages) * (((static_cast<uint32_t>(p.xrows) * 128u) + 1023u) & ~1023u);
+      : static_cast<uint32_t>(p.wstages) * MT_BYTES + static_cast<uint32_t>(p.xstages) * (((static_cast<uint32_t>(p.xrows) * 128u) + 1023u) & ~1023u);
   const uint32_t bars = base + data_bytes;
-  // barrier layout: full[stages] | empty[stages] | tfull | tempty | tmem ptr
+  // barrier layout: full[stages] | empty[stages] | tfull[4] | tempty[4] | tmem ptr   (mode 0 uses tfull[0]/tempty[0])
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (p.stages + s); };
-  const uint32_t tfull_bar = bars + 8u * (2 * p.stages);
-  const uint32_t tempty_bar = bars + 8u * (2 * p.stages + 1);
-  const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 2);
+  auto tfull_bar = [&](int m) { return bars + 8u * (2 * p.stages + m); };
+  auto tempty_bar = [&](int m) { return bars + 8u * (2 * p.stages + 4 + m); };
+  const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 8);
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), CLUSTER ? 2 : 1); }
-    mbar_init(tfull_bar, 1);
-    mbar_init(tempty_bar, NUM_EPI_WARPS);
+    for (int m = 0; m < 4; ++m) { mbar_init(tfull_bar(m), 1); mbar_init(tempty_bar(m), NUM_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -103,8 +106,8 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
 
   // ---- shift mode: separate rings for weights (one (j, c) chunk per slot) and tokens (one c chunk per slot)
   const uint32_t x_slot_bytes = ((static_cast<uint32_t>(p.xrows) * 128u) + 1023u) & ~1023u;
-  const uint32_t w_ring = base;                                             // wstages * a_bytes
-  const uint32_t x_ring = base + static_cast<uint32_t>(p.wstages) * a_bytes;   // xstages * x_slot_bytes
+  const uint32_t w_ring = base;                                             // wstages * MT_BYTES
+  const uint32_t x_ring = base + static_cast<uint32_t>(p.wstages) * MT_BYTES;  // xstages * x_slot_bytes
   // barriers in shift mode reuse the same array: full[i]/empty[i] for i < wstages are the weight ring,
   // i in [wstages, wstages + xstages) the token ring (p.stages == wstages + xstages)
 
@@ -131,23 +134,25 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
         }
       }
     } else if (lane == 0) {
-      int ws = 0, xs = 0; uint32_t wphase = 0, xphase = 0;
+      int ws = 0; uint32_t wphase = 0, xphase = 0;
       for (int tile = tile_first; tile < tile_end; tile += tile_step) {
         const int r0 = tile * p.NT;
-        for (int cc = 0; cc < p.cpj; ++cc) {
-          mbar_wait(empty_bar(p.wstages + xs), xphase ^ 1u);
-          mbar_expect_tx(full_bar(p.wstages + xs), static_cast<uint32_t>(p.xrows) * 128u);
-          tma_load_2d(x_ring + xs * x_slot_bytes, &tmX, cc * KCHUNK, r0, full_bar(p.wstages + xs));
-          if (++xs == p.xstages) { xs = 0; xphase ^= 1u; }
-          for (int j = 0; j < p.k; ++j) {
-            const int kc = j * p.cpj + cc;
-            mbar_wait(empty_bar(ws), wphase ^ 1u);
-            mbar_expect_tx(full_bar(ws), a_bytes);
-            for (int b = 0; b < p.n_wbox; ++b)
-              tma_load_2d(w_ring + ws * a_bytes + static_cast<uint32_t>(b * p.wbox) * 128u, &tmW, kc * KCHUNK, b * p.wbox, full_bar(ws));
-            if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
+        for (int m = 0; m < p.n_mt; ++m) {
+          for (int cc = 0; cc < p.cpj; ++cc) {
+            if (m == 0) {                            // the token tile: one slot per c chunk, loaded once per tile
+              mbar_wait(empty_bar(p.wstages + cc), xphase ^ 1u);
+              mbar_expect_tx(full_bar(p.wstages + cc), static_cast<uint32_t>(p.xrows) * 128u);
+              tma_load_2d(x_ring + cc * x_slot_bytes, &tmX, cc * KCHUNK, r0, full_bar(p.wstages + cc));
+            }
+            for (int j = 0; j < p.k; ++j) {
+              mbar_wait(empty_bar(ws), wphase ^ 1u);
+              mbar_expect_tx(full_bar(ws), MT_BYTES);
+              tma_load_2d(w_ring + ws * MT_BYTES, &tmW, (j * p.cpj + cc) * KCHUNK, m * MT, full_bar(ws));
+              if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
+            }
           }
         }
+        xphase ^= 1u;
       }
     }
   } else if (warp == 1) {
@@ -156,7 +161,7 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       int stage = 0; uint32_t phase = 0;
       uint32_t acc_phase = 0;
       for (int tile = tile_first; tile < tile_end; tile += tile_step) {
-        mbar_wait(tempty_bar, acc_phase ^ 1u);
+        mbar_wait(tempty_bar(0), acc_phase ^ 1u);
         tc_fence_after();
         for (int kc = 0; kc < nk; ++kc) {
           mbar_wait(full_bar(stage), phase);
@@ -174,40 +179,36 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
           else tc_commit(empty_bar(stage));            // smem slot free once these MMAs retire
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
-        tc_commit(tfull_bar);                          // accumulators complete
+        tc_commit(tfull_bar(0));                       // accumulators complete
         acc_phase ^= 1u;
       }
     } else if (lane == 0) {
       const uint32_t idesc = make_idesc(p.NT);
-      int ws = 0, xs = 0; uint32_t wphase = 0, xphase = 0;
-      uint32_t acc_phase = 0;
+      int ws = 0; uint32_t wphase = 0, xphase = 0, acc_phase = 0;
       for (int tile = tile_first; tile < tile_end; tile += tile_step) {
-        mbar_wait(tempty_bar, acc_phase ^ 1u);
-        tc_fence_after();
-        for (int cc = 0; cc < p.cpj; ++cc) {
-          mbar_wait(full_bar(p.wstages + xs), xphase);
-          const uint32_t x_src = x_ring + xs * x_slot_bytes;
-          for (int j = 0; j < p.k; ++j) {
-            mbar_wait(full_bar(ws), wphase);
-            tc_fence_after();
-            const uint32_t a_src = w_ring + ws * a_bytes;
-            const uint32_t bo = p.shift_mode == 2 ? static_cast<uint32_t>(j) : (p.shift_mode == 3 ? static_cast<uint32_t>(8 - j) : 0u);
+        for (int m = 0; m < p.n_mt; ++m) {
+          mbar_wait(tempty_bar(m), acc_phase ^ 1u);    // region m drained by the epilogue of the previous tile
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(m * p.NT);
+          for (int cc = 0; cc < p.cpj; ++cc) {
+            if (m == 0) mbar_wait(full_bar(p.wstages + cc), xphase);
+            const uint32_t x_src = x_ring + cc * x_slot_bytes;
+            for (int j = 0; j < p.k; ++j) {
+              mbar_wait(full_bar(ws), wphase);
+              tc_fence_after();
+              const uint32_t a_src = w_ring + ws * MT_BYTES;
 #pragma unroll
-            for (int ks = 0; ks < KCHUNK / 16; ++ks) {
-              const uint32_t accum = (cc | j | ks) != 0 ? 1u : 0u;
-              // token rows j .. j+NT-1 of the resident box: start address advanced by j rows of 128 B
-              const uint64_t bdesc = make_sw128_desc_bo(x_src + static_cast<uint32_t>(j) * 128u + ks * 32, bo);
-              for (int m = 0; m < p.n_mt; ++m)
-                tc_mma_bf16(tmem_base + static_cast<uint32_t>(m * p.NT), make_sw128_desc(a_src + m * MT_BYTES + ks * 32), bdesc, idesc, accum);
+              for (int ks = 0; ks < KCHUNK / 16; ++ks)   // token rows j .. j+NT-1 of the resident box
+                tc_mma_bf16(d_tmem, make_sw128_desc(a_src + ks * 32), make_sw128_desc(x_src + static_cast<uint32_t>(j) * 128u + ks * 32),
+                            idesc, (cc | j | ks) != 0 ? 1u : 0u);
+              tc_commit(empty_bar(ws));
+              if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
             }
-            tc_commit(empty_bar(ws));
-            if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
+            if (m == p.n_mt - 1) tc_commit(empty_bar(p.wstages + cc));   // last M tile is done with this token slot
           }
-          tc_commit(empty_bar(p.wstages + xs));        // token box free once all k offsets have used it
-          if (++xs == p.xstages) { xs = 0; xphase ^= 1u; }
+          tc_commit(tfull_bar(m));                     // region m complete: its epilogue overlaps region m+1's MMAs
         }
-        tc_commit(tfull_bar);
-        acc_phase ^= 1u;
+        xphase ^= 1u; acc_phase ^= 1u;
       }
     }
   } else {
@@ -218,9 +219,9 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     uint32_t acc_phase = 0;
     for (int tile = tile_first; tile < tile_end; tile += tile_step) {
       const int64_t rbeg = static_cast<int64_t>(tile) * p.NT + half * ncol;       // flat row of my first column
-      mbar_wait(tfull_bar, acc_phase);
-      tc_fence_after();
+      if (p.shift_mode == 0) { mbar_wait(tfull_bar(0), acc_phase); tc_fence_after(); }
       for (int m = 0; m < p.n_mt; ++m) {
+        if (p.shift_mode != 0) { mbar_wait(tfull_bar(m), acc_phase); tc_fence_after(); }
         const int f = m * MT + lq * 32 + lane;
         unsigned long long* kcol = p.keys + p.col0 + f;
         // running (max, first arg-max) of the current sequence piece
@@ -294,7 +295,8 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
 #pragma unroll
         for (int c = 0; c < NCH; ++c) tc_ld16_async(taddr + c * 16, v[c]);
         tc_wait_ld();
-        if (m == p.n_mt - 1) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar); }    // last read: release TMEM
+        if (p.shift_mode != 0) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(m)); }         // region m is in registers
+        else if (m == p.n_mt - 1) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(0)); }    // last read: release TMEM
 #pragma unroll
         for (int c = 0; c < NCH; ++c) process(v[c], c * 16);
         flush(s * p.L + (bt >= 0 ? bt : 0));
@@ -365,19 +367,22 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
   const int a_rows = p.n_mt * MT;
   if (cluster) { p.wbox = a_rows / 2; p.n_wbox = 2; }
   else { p.wbox = MT; p.n_wbox = p.n_mt; }
-  { const char* e = getenv("CLSM_CONV_TC_SHIFT"); p.shift_mode = (e != nullptr && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 0; }
+  // mode 0 (default).  CLSM_CONV_TC_SHIFT=1 selects the M-tile-outer / resident-token-tile variant: its epilogue
+  // overlap works, but with one 16 KB weight chunk (4 MMAs) per barrier round trip the MMA warp becomes the
+  // bottleneck -- measured 1.60 ms against 1.47 ms on cfg2 -- so it is kept as a switch, not the default.
+  { const char* e = getenv("CLSM_CONV_TC_SHIFT"); p.shift_mode = (e != nullptr && e[0] == '1') ? 1 : 0; }
   if (cluster) p.shift_mode = 0;
   int smem_bytes = 0;
   p.xrows = (p.NT + k - 1 + 7) / 8 * 8;
   if (p.shift_mode != 0 && p.xrows <= 256) {
     const int x_slot = (p.xrows * 128 + 1023) / 1024 * 1024;
-    p.xstages = 2;
-    p.wstages = (SMEM_LIMIT - 2048 - p.xstages * x_slot) / (a_rows * 128);
-    if (p.wstages > 6) p.wstages = 6;
-    if (p.wstages < 2) p.shift_mode = 0;
+    p.xstages = p.cpj;
+    p.wstages = (SMEM_LIMIT - 2048 - p.xstages * x_slot) / MT_BYTES;
+    if (p.wstages > 8) p.wstages = 8;
+    if (p.wstages < 3) p.shift_mode = 0;
     else {
       p.stages = p.wstages + p.xstages;
-      smem_bytes = p.wstages * a_rows * 128 + p.xstages * x_slot + 1024 + 8 * (2 * p.stages + 4);
+      smem_bytes = p.wstages * MT_BYTES + p.xstages * x_slot + 1024 + 8 * (2 * p.stages + 9);
     }
   } else {
     p.shift_mode = 0;
@@ -388,14 +393,15 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
     if (stages > 8) stages = 8;
     CLSM_REQUIRE(stages >= 2, "conv_pool_fwd(tcgen05): tile too large for a 2-stage pipeline");
     p.stages = stages;
-    smem_bytes = stages * stage_bytes + 1024 /*alignment slack*/ + 8 * (2 * stages + 4);
+    smem_bytes = stages * stage_bytes + 1024 /*alignment slack*/ + 8 * (2 * stages + 9);
   }
 
   CUtensorMap tmX, tmW;
   // rows of Wt past Fpad (the last M tile is usually partial) are zero-filled by TMA
   if (!make_map_2d(&tmX, X, static_cast<uint64_t>(Dpad), static_cast<uint64_t>(n_rows), KCHUNK,
                    static_cast<uint32_t>(p.shift_mode ? p.xrows : p.NT)) ||
-      !make_map_2d(&tmW, Wt, static_cast<uint64_t>(k) * Dpad, static_cast<uint64_t>(Fpad), KCHUNK, static_cast<uint32_t>(p.wbox))) {
+      !make_map_2d(&tmW, Wt, static_cast<uint64_t>(k) * Dpad, static_cast<uint64_t>(Fpad), KCHUNK,
+                   static_cast<uint32_t>(p.shift_mode ? MT : p.wbox))) {
     clsm_set_error("conv_pool_fwd(tcgen05): cuTensorMapEncodeTiled failed");
     return CLSM_ECUDA;
   }
