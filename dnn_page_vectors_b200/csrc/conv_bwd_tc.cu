@@ -592,6 +592,8 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
   p.chunks_total = ceil_div64(p.n_rows, DW_KT);
   if (splits > p.chunks_total) splits = static_cast<int>(p.chunks_total);
   p.chunks_per_split = ceil_div64(p.chunks_total, splits);
+  // no empty split: a CTA without chunks would issue no MMA and flush an unwritten accumulator
+  splits = static_cast<int>(ceil_div64(p.chunks_total, p.chunks_per_split));
   p.G = G; p.A = A; p.ldp = ldp; p.col0 = col0; p.part = part;
   const int stage_bytes = p.n_mt * MT_BYTES + 2 * DW_KT * 128;
   int stages = (SMEM_LIMIT - 2048) / stage_bytes;

@@ -236,7 +236,10 @@ def test_sim_loss_fwd_bwd(B, J, H):
 # ------------------------------------------------------------------ conv backward
 @pytest.mark.parametrize("bf16", [False, True])
 @pytest.mark.parametrize("shape", [(5, 20, 100, 3, 150), (9, 12, 64, 2, 20), (3, 100, 300, 3, 300), (4, 30, 100, 5, 130),
-                                   (6, 9, 40, 1, 17), (2, 1100, 64, 3, 40), (3, 500, 100, 4, 150), (70, 100, 300, 3, 300)])
+                                   (6, 9, 40, 1, 17), (2, 1100, 64, 3, 40), (3, 500, 100, 4, 150), (70, 100, 300, 3, 300),
+                                   # token-chunk counts that do not divide over the dW token splits (48 chunks / 37 CTAs,
+                                   # 14 / 49): the split count must shrink so that no CTA is left without work
+                                   (128, 24, 100, 4, 150), (37, 24, 100, 3, 150), (11, 200, 100, 6, 64)])
 def test_conv_pool_bwd(bf16, shape):
     S, L, D, k, F = shape
     rng = np.random.RandomState(6)
