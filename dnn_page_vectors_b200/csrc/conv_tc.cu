@@ -44,16 +44,20 @@ struct TcParams {
   int wbox, n_wbox;      // TMA box rows for W and how many boxes per stage
   int stages;
   int shift_mode;        // 0: K-outer loop, one X box per (j, c) chunk, all M tiles per stage, one accumulator barrier.
-                         // 1: M-tile-outer loop over a RESIDENT token tile: one X box (NT + halo rows) per c chunk stays in
+                         // 1 (default): M-tile-outer loop over a RESIDENT token tile: one X box (NT + halo rows) per c chunk stays in
                          //    shared memory for the whole tile and serves every window offset j through a B descriptor whose
                          //    start is advanced by j rows (the UMMA swizzle works on absolute address bits, base_offset 0);
                          //    weights stream one (M tile, j, c) chunk per slot; each M tile's TMEM region has its own
                          //    full/empty barrier, so the epilogue of region m overlaps the MMAs of region m+1.
   int xrows;             // rows of the X box in mode 1 (NT + k - 1 rounded up to 8)
   int xstages, wstages;  // mode 1: xstages = cpj token slots, wstages weight slots of one M tile chunk (16 KB)
+  int nreg;              // mode 1: TMEM accumulator regions of NT columns used round-robin by the (tile, M tile) units
+  long long* prof;       // optional cycle counters (CLSM_CONV_TC_PROF=1), else nullptr
 };
 
 using namespace tcptx;
+
+__device__ long long g_conv_tc_prof[8];      // CLSM_CONV_TC_PROF=1 diagnostics
 
 template <bool CLUSTER, int NCH>     // NCH = 16-column chunks per epilogue warp (NT / 32)
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -160,11 +164,17 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       const uint32_t idesc = make_idesc(p.NT);
       int stage = 0; uint32_t phase = 0;
       uint32_t acc_phase = 0;
+      long long w_tmem = 0, w_feed = 0;
+      const long long t_begin = clock64();
       for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+        long long c0 = clock64();
         mbar_wait(tempty_bar(0), acc_phase ^ 1u);
+        w_tmem += clock64() - c0;
         tc_fence_after();
         for (int kc = 0; kc < nk; ++kc) {
+          c0 = clock64();
           mbar_wait(full_bar(stage), phase);
+          w_feed += clock64() - c0;
           tc_fence_after();
           const uint32_t a_src = base + stage * stage_bytes;
           const uint32_t b_src = a_src + a_bytes;
@@ -182,19 +192,31 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
         tc_commit(tfull_bar(0));                       // accumulators complete
         acc_phase ^= 1u;
       }
+      if (p.prof != nullptr) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 0), static_cast<unsigned long long>(clock64() - t_begin));
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 1), static_cast<unsigned long long>(w_tmem));
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 2), static_cast<unsigned long long>(w_feed));
+      }
     } else if (lane == 0) {
       const uint32_t idesc = make_idesc(p.NT);
-      int ws = 0; uint32_t wphase = 0, xphase = 0, acc_phase = 0;
+      int ws = 0; uint32_t wphase = 0, xphase = 0;
+      int reg = 0; uint32_t rphase = 0;                // accumulator region of the current unit, and its use parity
+      long long w_tmem = 0, w_feed = 0;
+      const long long t_begin = clock64();
       for (int tile = tile_first; tile < tile_end; tile += tile_step) {
         for (int m = 0; m < p.n_mt; ++m) {
-          mbar_wait(tempty_bar(m), acc_phase ^ 1u);    // region m drained by the epilogue of the previous tile
+          long long c0 = clock64();
+          mbar_wait(tempty_bar(reg), rphase ^ 1u);     // region drained by the epilogue of the unit that used it last
+          w_tmem += clock64() - c0;
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(m * p.NT);
+          const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(reg * p.NT);
           for (int cc = 0; cc < p.cpj; ++cc) {
-            if (m == 0) mbar_wait(full_bar(p.wstages + cc), xphase);
+            if (m == 0) { c0 = clock64(); mbar_wait(full_bar(p.wstages + cc), xphase); w_feed += clock64() - c0; }
             const uint32_t x_src = x_ring + cc * x_slot_bytes;
             for (int j = 0; j < p.k; ++j) {
+              c0 = clock64();
               mbar_wait(full_bar(ws), wphase);
+              w_feed += clock64() - c0;
               tc_fence_after();
               const uint32_t a_src = w_ring + ws * MT_BYTES;
 #pragma unroll
@@ -206,9 +228,15 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
             }
             if (m == p.n_mt - 1) tc_commit(empty_bar(p.wstages + cc));   // last M tile is done with this token slot
           }
-          tc_commit(tfull_bar(m));                     // region m complete: its epilogue overlaps region m+1's MMAs
+          tc_commit(tfull_bar(reg));                   // unit complete: its epilogue overlaps the next unit's MMAs
+          if (++reg == p.nreg) { reg = 0; rphase ^= 1u; }
         }
-        xphase ^= 1u; acc_phase ^= 1u;
+        xphase ^= 1u;
+      }
+      if (p.prof != nullptr) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 0), static_cast<unsigned long long>(clock64() - t_begin));
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 1), static_cast<unsigned long long>(w_tmem));
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 2), static_cast<unsigned long long>(w_feed));
       }
     }
   } else {
@@ -217,11 +245,21 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
     const int Tn = p.L - p.k + 1;
     const int ncol = p.NT / 2;                         // columns this warp walks, multiple of 16
     uint32_t acc_phase = 0;
+    int reg = 0; uint32_t rphase = 0;                  // mode 1: accumulator region of the current unit
+    long long w_full = 0, w_work = 0;
     for (int tile = tile_first; tile < tile_end; tile += tile_step) {
       const int64_t rbeg = static_cast<int64_t>(tile) * p.NT + half * ncol;       // flat row of my first column
-      if (p.shift_mode == 0) { mbar_wait(tfull_bar(0), acc_phase); tc_fence_after(); }
+      if (p.shift_mode == 0) {
+        const long long c0 = clock64();
+        mbar_wait(tfull_bar(0), acc_phase);
+        tc_fence_after();
+        w_full += clock64() - c0;
+      }
       for (int m = 0; m < p.n_mt; ++m) {
-        if (p.shift_mode != 0) { mbar_wait(tfull_bar(m), acc_phase); tc_fence_after(); }
+        const long long c0 = clock64();
+        if (p.shift_mode != 0) { mbar_wait(tfull_bar(reg), rphase); tc_fence_after(); }
+        const long long c1 = clock64();
+        w_full += c1 - c0;
         const int f = m * MT + lq * 32 + lane;
         unsigned long long* kcol = p.keys + p.col0 + f;
         // running (max, first arg-max) of the current sequence piece
@@ -289,19 +327,29 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
             }
           }
         };
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(m * p.NT + half * ncol);
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) +
+                               static_cast<uint32_t>((p.shift_mode != 0 ? reg : m) * p.NT + half * ncol);
         // all of this warp's columns of region m in one go: up to 8 x16 loads in flight, one wait
         uint32_t v[NCH][16];
 #pragma unroll
         for (int c = 0; c < NCH; ++c) tc_ld16_async(taddr + c * 16, v[c]);
         tc_wait_ld();
-        if (p.shift_mode != 0) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(m)); }         // region m is in registers
+        if (p.shift_mode != 0) {                                                                        // the unit is in registers
+          tc_fence_before();
+          if (lane == 0) mbar_arrive(tempty_bar(reg));
+          if (++reg == p.nreg) { reg = 0; rphase ^= 1u; }
+        }
         else if (m == p.n_mt - 1) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(0)); }    // last read: release TMEM
 #pragma unroll
         for (int c = 0; c < NCH; ++c) process(v[c], c * 16);
         flush(s * p.L + (bt >= 0 ? bt : 0));
+        w_work += clock64() - c1;
       }
       acc_phase ^= 1u;
+    }
+    if (p.prof != nullptr && warp == 2 && lane == 0) {
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 3), static_cast<unsigned long long>(w_full));
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 4), static_cast<unsigned long long>(w_work));
     }
   }
 
@@ -367,12 +415,27 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
   const int a_rows = p.n_mt * MT;
   if (cluster) { p.wbox = a_rows / 2; p.n_wbox = 2; }
   else { p.wbox = MT; p.n_wbox = p.n_mt; }
-  // mode 0 (default).  CLSM_CONV_TC_SHIFT=1 selects the M-tile-outer / resident-token-tile variant: its epilogue
-  // overlap works, but with one 16 KB weight chunk (4 MMAs) per barrier round trip the MMA warp becomes the
-  // bottleneck -- measured 1.60 ms against 1.47 ms on cfg2 -- so it is kept as a switch, not the default.
-  { const char* e = getenv("CLSM_CONV_TC_SHIFT"); p.shift_mode = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  // mode 1 (default) = M-tile-outer loop over a resident token tile; CLSM_CONV_TC_SHIFT=0 selects mode 0 (K-outer,
+  // all M tiles per stage).  Measured on cfg2 documents (cycles per CTA, CLSM_CONV_TC_PROF=1): mode 0 spends 21 % of
+  // the MMA thread's time waiting for the epilogue to drain TMEM (n_mt * NT = 480 columns leave no second
+  // accumulator set) and runs at 112 cycles per MMA against a floor of 80, which is the shared-memory bound
+  // (4 KB weights written + 4 KB read + 5 KB tokens read + 1.7 KB tokens written per MMA at 128 B/clk).  Mode 1
+  // with 224-token tiles needs 37 % fewer bytes per flop, never waits for TMEM, and is 14 % faster end to end.
+  { const char* e = getenv("CLSM_CONV_TC_SHIFT"); p.shift_mode = (e != nullptr && e[0] == '0') ? 0 : 1; }
   if (cluster) p.shift_mode = 0;
   int smem_bytes = 0;
+  if (p.shift_mode != 0) {
+    // mode 1 is not tied to n_mt * NT <= 512: the (tile, M tile) units rotate through 512 / NT regions.
+    // NT = 224: the widest tile whose NT + k - 1 token rows still fit one TMA box (256 rows) and whose UMMA
+    // floor (N / 2 = 112 cycles) covers the ~105-cycle latency of back-to-back MMAs into one accumulator.
+    int nt = 224;
+    { const char* e = getenv("CLSM_CONV_TC_NT"); if (e != nullptr && atoi(e) >= 64 && atoi(e) <= 256 && atoi(e) % 32 == 0) nt = atoi(e); }
+    while (nt > 64 && nt + k - 1 > 256) nt -= 32;
+    p.NT = nt;
+    p.n_tiles = static_cast<int>(ceil_div64(n_rows, p.NT));
+    p.nreg = 512 / p.NT;
+    if (p.nreg > 4) p.nreg = 4;
+  }
   p.xrows = (p.NT + k - 1 + 7) / 8 * 8;
   if (p.shift_mode != 0 && p.xrows <= 256) {
     const int x_slot = (p.xrows * 128 + 1023) / 1024 * 1024;
@@ -388,6 +451,9 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
     p.shift_mode = 0;
   }
   if (p.shift_mode == 0) {
+    p.NT = (512 / p.n_mt) / 32 * 32;           // (a fallback from mode 1 returns to the n_mt-region tile)
+    if (p.NT > 256) p.NT = 256;
+    p.n_tiles = static_cast<int>(ceil_div64(n_rows, p.NT));
     const int stage_bytes = a_rows * 128 + ((p.NT * 128 + 1023) / 1024) * 1024;
     int stages = (SMEM_LIMIT - 2048) / stage_bytes;
     if (stages > 8) stages = 8;
@@ -404,6 +470,14 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
                    static_cast<uint32_t>(p.shift_mode ? MT : p.wbox))) {
     clsm_set_error("conv_pool_fwd(tcgen05): cuTensorMapEncodeTiled failed");
     return CLSM_ECUDA;
+  }
+  static int prof_on = -1;
+  if (prof_on < 0) { const char* e = getenv("CLSM_CONV_TC_PROF"); prof_on = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  if (prof_on) {
+    void* sym = nullptr;
+    CLSM_CUDA(cudaGetSymbolAddress(&sym, g_conv_tc_prof));
+    p.prof = static_cast<long long*>(sym);
+    CLSM_CUDA(cudaMemsetAsync(sym, 0, sizeof(long long) * 8, st));
   }
   int grid = clsm_sm_count();
   cudaLaunchConfig_t cfg = {};
@@ -429,8 +503,27 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
   } while (0)
   const int nch = p.NT / 32;
   if (cluster) { if (nch == 4) TC_LAUNCH(true, 4); else if (nch == 5) TC_LAUNCH(true, 5); else TC_LAUNCH(true, 8); }
-  else { if (nch == 4) TC_LAUNCH(false, 4); else if (nch == 5) TC_LAUNCH(false, 5); else TC_LAUNCH(false, 8); }
+  else {
+    switch (nch) {
+      case 2: TC_LAUNCH(false, 2); break;
+      case 3: TC_LAUNCH(false, 3); break;
+      case 4: TC_LAUNCH(false, 4); break;
+      case 5: TC_LAUNCH(false, 5); break;
+      case 6: TC_LAUNCH(false, 6); break;
+      case 7: TC_LAUNCH(false, 7); break;
+      default: TC_LAUNCH(false, 8); break;
+    }
+  }
 #undef TC_LAUNCH
   CLSM_LAUNCH_CHECK();
+  if (prof_on) {           // diagnostics only: synchronises and prints average cycles per CTA
+    long long h[8];
+    CLSM_CUDA(cudaStreamSynchronize(st));
+    CLSM_CUDA(cudaMemcpy(h, p.prof, sizeof(h), cudaMemcpyDeviceToHost));
+    const double g = static_cast<double>(grid);
+    fprintf(stderr, "[conv_tc prof] mode %d NT %d tiles %d grid %d | MMA thread: total %.0f, wait TMEM %.0f, wait feed %.0f | "
+            "epilogue warp: wait accumulator %.0f, work %.0f (cycles per CTA)\n", p.shift_mode, p.NT, p.n_tiles, grid,
+            h[0] / g, h[1] / g, h[2] / g, h[3] / g, h[4] / g);
+  }
   return CLSM_OK;
 }

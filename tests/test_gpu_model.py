@@ -121,6 +121,58 @@ def test_fp32_training_trajectory_matches_oracle(cfg, act):
             assert err.max() < 7e-3 and (err > 2e-5).mean() < 2e-2, (tag, err.max(), (err > 2e-5).mean())
 
 
+# BASELINE.json configs 3 and 4 at their own sequence / window / negative counts, batch cut so that the oracle
+# finishes in seconds: cfg3 = 50 negatives of 1000 tokens (the long-sequence time tiling, 51 documents per pair),
+# cfg4 = four window sizes (1, 2, 3, 5) x 300 filters (1200-wide pooled vector).
+CFG_THREE = dict(B=2, J=50, Lq=20, Ld=1000, V=3000, D=300, windows=(3,), F=300, H=128)
+CFG_FOUR = dict(B=8, J=4, Lq=20, Ld=100, V=1000, D=300, windows=(1, 2, 3, 5), F=300, H=128)
+
+
+@pytest.mark.parametrize("cfg", [CFG_THREE, CFG_FOUR], ids=["cfg3", "cfg4"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_config_shapes_first_step_matches_oracle(cfg, precision):
+    """Loss, accuracy and every gradient tensor of the first training step against the oracle.
+    fp32 mode: CUDA-core kernels, 1e-4 of each tensor's scale.  bf16 mode: the tcgen05 forward and backward
+    kernels (bf16 operands and bf16 pooled-gradient entries, fp32 accumulation): 2e-2 of the scale."""
+    fp32 = precision == "fp32"
+    net, pq, pd_ = build(precision, "relu", conv_impl="simt" if fp32 else "auto", **cfg)
+    if not fp32:
+        # the library computes on bf16-rounded tables and conv weights: give the oracle the same operands
+        for p in (pq, pd_):
+            p["E"] = bf16_round(p["E"]).astype(np.float64)
+            p["convW"] = [bf16_round(W).astype(np.float64) for W in p["convW"]]
+    x = synth(5, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"])
+    q64, d64 = x[0].astype(np.int64), np.stack(x[1:], axis=1).astype(np.int64)
+    head, ogq, ogd, _, _ = O.model_loss_and_grads(q64, d64, pq, pd_, act="relu")
+    tol_loss, tol_g, frac = (2e-5, 1e-4, 0.01) if fp32 else (5e-3, 2e-2, 0.03)
+    l0, a0 = net.test_on_batch(x)
+    assert abs(l0 - head["loss"]) <= tol_loss * max(1.0, abs(head["loss"]))
+    l, a = net.train_on_batch(x)
+    assert abs(l - head["loss"]) <= tol_loss * max(1.0, abs(head["loss"]))
+    for tower, og in ((net.query_model, ogq), (net.doc_model, ogd)):
+        def close(got, want):
+            got, want = np.asarray(got, dtype=np.float64), np.asarray(want)
+            assert got.shape == want.shape
+            scale = np.abs(want).max() + 1e-30
+            bad = np.abs(got - want) > tol_g * scale
+            per_filter = bad.reshape(-1, bad.shape[-1]).any(axis=0) if bad.ndim > 1 else bad
+            assert per_filter.mean() <= frac, (per_filter.mean(), np.abs(got - want).max() / scale)
+        close(tower.g_Wd.cpu().numpy(), og["Wd"])
+        close(tower.g_bd.cpu().numpy(), og["bd"])
+        for i in range(len(tower.windows)):
+            close(tower.g_convW[i].cpu().numpy(), og["convW"][i])
+            close(tower.g_convb[i * tower.F:(i + 1) * tower.F].cpu().numpy(), og["convb"][i])
+        S = cfg["B"] if tower is net.query_model else cfg["B"] * (1 + cfg["J"])
+        b = tower.buffers(S, True)
+        n_u = int(b["n_uniq"].item())
+        ids = b["uniq"][:n_u].cpu().numpy()
+        rows = b["dE_rows"][:n_u, :tower.D].cpu().numpy().astype(np.float64)
+        want = og["E"][ids]
+        scale = np.abs(want).max()
+        assert (np.abs(rows - want) > tol_g * scale).any(axis=1).mean() <= 2 * frac
+        assert np.abs(np.delete(og["E"], ids, axis=0)).max() == 0.0
+
+
 def test_bf16_forward_and_loss_within_tolerance():
     cfg = CFG_ONE
     net, pq, pd_ = build("bf16", "relu", conv_impl="simt", **cfg)
