@@ -40,7 +40,10 @@ struct DxParams {
   const float* G; const int32_t* A; int ldp, col0;
   float* dX; int accumulate;
   int stages;
+  long long* prof;             // optional cycle counters (CLSM_CONV_BWD_PROF=1), else nullptr
 };
+
+__device__ long long g_conv_bwd_prof[8];
 
 // Wb[c, j*Fk + f] = Wt[f, j*Dpad + c]   (Fk = fblocks*64, zero padded)
 __global__ void pack_wb_kernel(const __nv_bfloat16* __restrict__ Wt, int k, int Dpad, int F, int Fk,
@@ -70,7 +73,7 @@ dx_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const DxParams p) {
   const uint32_t tempty_bar = bars + 8u * (2 * p.stages + 1);
   const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 2);
 
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int warp = warp_id_uniform(), lane = threadIdx.x % 32;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1 + NUM_BLD_WARPS); mbar_init(empty_bar(s), 1); }
@@ -106,29 +109,41 @@ dx_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const DxParams p) {
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // whole warp, warp-uniform issue loop (tc_ptx.cuh)
+    {
       const uint32_t idesc = make_idesc(p.NT);
       int stage = 0; uint32_t phase = 0, acc_phase = 0;
+      long long w_tmem = 0, w_full = 0;
+      const long long t_begin = clock64();
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        long long c0 = clock64();
         mbar_wait(tempty_bar, acc_phase ^ 1u);
+        w_tmem += clock64() - c0;
         tc_fence_after();
         for (int kc = 0; kc < nk; ++kc) {
+          c0 = clock64();
           mbar_wait(full_bar(stage), phase);
+          w_full += clock64() - c0;
           tc_fence_after();
-          const uint32_t a_src = base + stage * stage_bytes;
-          const uint32_t b_src = a_src + a_bytes;
+          const uint32_t a_lo = sw128_desc_lo(base + stage * stage_bytes);
+          const uint32_t b_lo = sw128_desc_lo(base + stage * stage_bytes + a_bytes);
 #pragma unroll
           for (int ks = 0; ks < KCHUNK / 16; ++ks) {
             const uint32_t accum = (kc | ks) != 0 ? 1u : 0u;
-            const uint64_t bdesc = make_sw128_desc(b_src + ks * 32);
             for (int m = 0; m < p.n_mt; ++m)
-              tc_mma_bf16(tmem_base + static_cast<uint32_t>(m * p.NT), make_sw128_desc(a_src + m * MT_BYTES + ks * 32), bdesc, idesc, accum);
+              tc_mma_bf16_u(tmem_base + static_cast<uint32_t>(m * p.NT), a_lo + static_cast<uint32_t>(m * (MT_BYTES / 16) + ks * 2),
+                            b_lo + ks * 2, idesc, accum);
           }
-          tc_commit(empty_bar(stage));
+          tc_commit_u(empty_bar(stage));
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
-        tc_commit(tfull_bar);
+        tc_commit_u(tfull_bar);
         acc_phase ^= 1u;
+      }
+      if (p.prof != nullptr && lane == 0) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 4), static_cast<unsigned long long>(clock64() - t_begin));
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 5), static_cast<unsigned long long>(w_tmem));
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 6), static_cast<unsigned long long>(w_full));
       }
     }
   } else if (warp < 2 + NUM_EPI_WARPS) {
@@ -286,12 +301,10 @@ struct DwParams {
   const float* G; const int32_t* A; int ldp, col0;
   float* part;
   int stages;
+  long long* prof;             // optional cycle counters (CLSM_CONV_BWD_PROF=1), else nullptr
 };
 
-__device__ __forceinline__ uint64_t make_sw128_mn_desc(uint32_t saddr, uint32_t lbo_bytes) {
-  return static_cast<uint64_t>((saddr & 0x3FFFFu) >> 4) | (static_cast<uint64_t>(lbo_bytes >> 4) << 16) |
-         (static_cast<uint64_t>(1024 >> 4) << 32) | (static_cast<uint64_t>(1) << 46) | (static_cast<uint64_t>(2) << 61);
-}
+
 
 constexpr int DW_NT = 128;          // (j, c) columns per CTA = UMMA N
 constexpr int DW_KT = 64;           // tokens per chunk
@@ -313,7 +326,7 @@ dw_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
   const uint32_t tfull_bar = bars + 8u * (2 * p.stages);
   const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 1);
 
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int warp = warp_id_uniform(), lane = threadIdx.x % 32;
   const int split = blockIdx.x / p.n_slices;
   const int slice = blockIdx.x - split * p.n_slices;
   const int j = slice / p.n_cr, c0 = (slice - j * p.n_cr) * DW_NT;
@@ -350,27 +363,27 @@ dw_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       const uint32_t idesc = make_idesc(DW_NT) | (1u << 16);                 // B operand MN-major
       int stage = 0; uint32_t phase = 0;
       bool first = true;
       for (int64_t ch = ch_begin; ch < ch_end; ++ch) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
-        const uint32_t a_src = base + stage * stage_bytes;
-        const uint32_t b_src = a_src + a_bytes;
+        const uint32_t a_lo = sw128_desc_lo(base + stage * stage_bytes);
+        const uint32_t b_lo = sw128_mn_desc_lo(base + stage * stage_bytes + a_bytes, DW_KT * 128u);
 #pragma unroll
         for (int ks = 0; ks < DW_KT / 16; ++ks) {
-          const uint32_t accum = (first && ks == 0) ? 0u : 1u;
-          const uint64_t bdesc = make_sw128_mn_desc(b_src + ks * 2048u, DW_KT * 128u);   // 16 tokens = two 8-row K atoms
+          const uint32_t accum = (first && ks == 0) ? 0u : 1u;            // 16 tokens = two 8-row K atoms = 2048 B
           for (int m = 0; m < p.n_mt; ++m)
-            tc_mma_bf16(tmem_base + static_cast<uint32_t>(m * DW_NT), make_sw128_desc(a_src + m * MT_BYTES + ks * 32), bdesc, idesc, accum);
+            tc_mma_bf16_u(tmem_base + static_cast<uint32_t>(m * DW_NT), a_lo + static_cast<uint32_t>(m * (MT_BYTES / 16) + ks * 2),
+                          b_lo + ks * 128, idesc, accum);
         }
         first = false;
-        tc_commit(empty_bar(stage));
+        tc_commit_u(empty_bar(stage));
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
-      tc_commit(tfull_bar);
+      tc_commit_u(tfull_bar);
     }
   } else {
     // ---- builders: dY^T tile of every chunk.  The (G, arg-max) pairs a thread needs for chunk ch+1 are
@@ -492,6 +505,219 @@ dw_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
   }
 }
 
+// ---- dW, second tiling (k * 128 <= 512 accumulator columns, i.e. k <= 4): a CTA owns ONE filter M tile and one
+// 128-column slice of the token rows for ALL k window offsets.  The k accumulators D_j[f, c] share the dY^T tile
+// (built once per chunk, for 128 filters only -- a third of the builder work of the per-offset tiling above, and
+// each CTA's builders touch only their own filters) and the token box: 64 + 8 rows are loaded once and offset j
+// is the same MN-major descriptor advanced by j rows (the swizzle is a function of absolute address bits).
+// The k accumulators are independent, so consecutive MMAs never wait on each other's result.
+constexpr int DW2_XROWS = DW_KT + 8;                        // token rows per box: the chunk plus the window halo
+constexpr uint32_t DW2_BOX_BYTES = DW2_XROWS * 128u;        // 9216 = 9 swizzle atoms
+
+template <int MAXSEQ>
+__global__ void __launch_bounds__(DW_THREADS, 1)
+dw2_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t a_bytes = MT_BYTES;                                          // dY^T: 128 f x 64 tokens
+  const uint32_t b_bytes = 2u * DW2_BOX_BYTES;                                // X: two boxes of 72 tokens x 64 columns
+  const uint32_t stage_bytes = a_bytes + ((b_bytes + 1023u) & ~1023u);
+  const uint32_t bars = base + static_cast<uint32_t>(p.stages) * stage_bytes;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (p.stages + s); };
+  const uint32_t tfull_bar = bars + 8u * (2 * p.stages);
+  const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 1);
+
+  const int warp = warp_id_uniform(), lane = threadIdx.x % 32;
+  const int split = blockIdx.x / p.n_slices;
+  const int slice = blockIdx.x - split * p.n_slices;
+  const int mt = slice / p.n_cr, c0 = (slice - mt * p.n_cr) * DW_NT;           // filter M tile, column slice
+  const int64_t ch_begin = static_cast<int64_t>(split) * p.chunks_per_split;
+  const int64_t ch_end = (ch_begin + p.chunks_per_split < p.chunks_total) ? ch_begin + p.chunks_per_split : p.chunks_total;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1 + DW_BLD_WARPS / 2); mbar_init(empty_bar(s), 1); }
+    mbar_init(tfull_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmX) : "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int64_t ch = ch_begin; ch < ch_end; ++ch) {
+        const int r0 = static_cast<int>(ch * DW_KT);
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        mbar_expect_tx(full_bar(stage), b_bytes);
+        const uint32_t b_dst = base + stage * stage_bytes + a_bytes;
+        tma_load_2d(b_dst, &tmX, c0, r0, full_bar(stage));
+        tma_load_2d(b_dst + DW2_BOX_BYTES, &tmX, c0 + 64, r0, full_bar(stage));
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    {
+      const uint32_t idesc = make_idesc(DW_NT) | (1u << 16);                 // B operand MN-major
+      int stage = 0; uint32_t phase = 0;
+      bool first = true;
+      long long w_full = 0;
+      const long long t_begin = clock64();
+      for (int64_t ch = ch_begin; ch < ch_end; ++ch) {
+        const long long c0 = clock64();
+        mbar_wait(full_bar(stage), phase);
+        w_full += clock64() - c0;
+        tc_fence_after();
+        const uint32_t a_lo = sw128_desc_lo(base + stage * stage_bytes);
+        const uint32_t b_lo = sw128_mn_desc_lo(base + stage * stage_bytes + a_bytes, DW2_BOX_BYTES);
+#pragma unroll
+        for (int ks = 0; ks < DW_KT / 16; ++ks) {
+          const uint32_t accum = (first && ks == 0) ? 0u : 1u;
+          for (int j = 0; j < p.k; ++j)                                        // token rows 16 ks + j .. of the box
+            tc_mma_bf16_u(tmem_base + static_cast<uint32_t>(j * DW_NT), a_lo + ks * 2, b_lo + ks * 128 + static_cast<uint32_t>(j) * 8u, idesc, accum);
+        }
+        first = false;
+        tc_commit_u(empty_bar(stage));
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+      tc_commit_u(tfull_bar);
+      if (p.prof != nullptr && lane == 0) {
+        mbar_wait(tfull_bar, 0);
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 0), static_cast<unsigned long long>(clock64() - t_begin));
+        atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 1), static_cast<unsigned long long>(w_full));
+      }
+    }
+  } else {
+    // ---- builders: dY^T of the CTA's 128 filters.  The eight warps form two groups of 128 threads (thread =
+    // filter); group g builds the chunks of parity g, so a group has two MMA periods per tile.  With FOUR stages
+    // group g only ever touches stages g and g + 2: a thread owns the locations it writes and "un-write what I
+    // wrote the last time this stage was used, then write" needs no barrier between builder threads.
+    const int bt = threadIdx.x - 64;
+    const int fl = bt & 127, grp = bt >> 7;
+    const int f = mt * MT + fl;
+    constexpr int NS = MAXSEQ;
+    const uint32_t zero_chunks = a_bytes / 16;
+    constexpr int NB = DW_BLD_WARPS * 32;
+    float g_nxt[NS]; int a_nxt[NS];
+    const int64_t tok0 = (ch_begin + grp) * DW_KT;            // first token of this group's first chunk
+    int64_t ps = tok0 / p.L;
+    int pt = static_cast<int>(tok0 - ps * p.L);
+    int ct = pt;
+    const int64_t S_total = p.n_rows / p.L;
+    auto prefetch = [&](int64_t ch) {
+      const int nseq = (pt + DW_KT - 1) / p.L + 1;
+      const float* gp = p.G + ps * p.ldp + p.col0 + f;
+      const int32_t* ap = p.A + ps * p.ldp + p.col0 + f;
+#pragma unroll
+      for (int sq = 0; sq < NS; ++sq) {
+        const bool ok = ch < ch_end && sq < nseq && ps + sq < S_total && f < p.F;
+        g_nxt[sq] = ok ? __ldg(gp + static_cast<int64_t>(sq) * p.ldp) : 0.0f;
+        a_nxt[sq] = ok ? __ldg(ap + static_cast<int64_t>(sq) * p.ldp) : 0;
+      }
+      pt += 2 * DW_KT;
+      while (pt >= p.L) { pt -= p.L; ++ps; }
+    };
+    for (int st = 0; st < p.stages; ++st) {
+      uint8_t* atile = base_ptr + st * stage_bytes;
+      for (uint32_t i = bt; i < zero_chunks; i += NB) reinterpret_cast<uint4*>(atile)[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(NB) : "memory");
+    constexpr uint32_t NONE = 0xFFFFFFFFu;
+    uint32_t wrote[2][NS];                               // per owned stage (g, g + 2): byte offsets written last time
+#pragma unroll
+    for (int sl = 0; sl < 2; ++sl)
+#pragma unroll
+      for (int i = 0; i < NS; ++i) wrote[sl][i] = NONE;
+    prefetch(ch_begin + grp);
+    long long w_empty = 0;
+    const long long tb_begin = clock64();
+    uint32_t phase = 0;
+    for (int64_t chb = ch_begin + grp; chb < ch_end; chb += 4) {
+#pragma unroll
+      for (int sl = 0; sl < 2; ++sl) {
+        const int64_t ch = chb + 2 * sl;
+        const int st = grp + 2 * sl;
+        if (ch < ch_end) {
+          float g_cur[NS]; int a_cur[NS];
+#pragma unroll
+          for (int i = 0; i < NS; ++i) { g_cur[i] = g_nxt[i]; a_cur[i] = a_nxt[i]; }
+          prefetch(ch + 2);
+          const long long c0 = clock64();
+          mbar_wait(empty_bar(st), phase ^ 1u);
+          w_empty += clock64() - c0;
+          uint8_t* atile = base_ptr + st * stage_bytes;
+#pragma unroll
+          for (int i = 0; i < NS; ++i)
+            if (wrote[sl][i] != NONE) *reinterpret_cast<uint16_t*>(atile + wrote[sl][i]) = 0;
+#pragma unroll
+          for (int sq = 0; sq < NS; ++sq) {
+            const int n = sq * p.L + a_cur[sq] - ct;                         // token column inside the chunk
+            uint32_t off = NONE;
+            if (g_cur[sq] != 0.0f && n >= 0 && n < DW_KT) {
+              off = static_cast<uint32_t>(fl) * 128u + (((static_cast<uint32_t>(n) >> 3) ^ (static_cast<uint32_t>(fl) & 7u)) << 4) +
+                    (static_cast<uint32_t>(n) & 7u) * 2u;
+              *reinterpret_cast<__nv_bfloat16*>(atile + off) = __float2bfloat16_rn(g_cur[sq]);
+            }
+            wrote[sl][sq] = off;
+          }
+          ct += 2 * DW_KT;
+          while (ct >= p.L) ct -= p.L;
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(full_bar(st));
+        }
+      }
+      phase ^= 1u;
+    }
+    if (p.prof != nullptr && bt == 0) {
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 2), static_cast<unsigned long long>(clock64() - tb_begin));
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 3), static_cast<unsigned long long>(w_empty));
+    }
+    // ---- epilogue (same warps): D_j[f, n] -> part[split][f][j][c0 + n]
+    const int lq = warp & 3;
+    const int half = (warp - 2) >> 2;                      // 64 of the 128 columns each
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    const int fo = mt * MT + lq * 32 + lane;
+    for (int j = 0; j < p.k; ++j) {
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(j * DW_NT + half * 64);
+      uint32_t v[4][16];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) tc_ld16_async(taddr + q * 16, v[q]);
+      tc_wait_ld();
+      if (fo < p.F) {
+        float* dst = p.part + ((static_cast<int64_t>(split) * p.F + fo) * p.k + j) * p.Dpad + c0 + half * 64;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+#pragma unroll
+          for (int i = 0; i < 16; i += 4) {
+            const int n = q * 16 + i;
+            if (c0 + half * 64 + n < p.Dpad)
+              *reinterpret_cast<float4*>(dst + n) = make_float4(__uint_as_float(v[q][i]), __uint_as_float(v[q][i + 1]),
+                                                                 __uint_as_float(v[q][i + 2]), __uint_as_float(v[q][i + 3]));
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -561,6 +787,14 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
   }
   int grid = clsm_sm_count();
   if (grid > p.n_tiles) grid = p.n_tiles;
+  static int prof_on = -1;
+  if (prof_on < 0) { const char* e = getenv("CLSM_CONV_BWD_PROF"); prof_on = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  if (prof_on) {
+    void* sym = nullptr;
+    CLSM_CUDA(cudaGetSymbolAddress(&sym, g_conv_bwd_prof));
+    p.prof = static_cast<long long*>(sym);
+    CLSM_CUDA(cudaMemsetAsync(sym, 0, sizeof(long long) * 8, st));
+  }
   const int nch = p.NT / 32;
 #define DX_LAUNCH(N, C)                                                                                          \
   do {                                                                                                           \
@@ -571,6 +805,13 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
   else           { if (nch == 4) DX_LAUNCH(4, 5); else if (nch == 5) DX_LAUNCH(5, 5); else DX_LAUNCH(8, 5); }
 #undef DX_LAUNCH
   CLSM_LAUNCH_CHECK();
+  if (prof_on) {           // diagnostics only: synchronises and prints average cycles per CTA
+    long long h[8];
+    CLSM_CUDA(cudaStreamSynchronize(st));
+    CLSM_CUDA(cudaMemcpy(h, p.prof, sizeof(h), cudaMemcpyDeviceToHost));
+    fprintf(stderr, "[dx_tc prof] NT %d tiles %d grid %d maxc %d | MMA thread: total %.0f, wait TMEM %.0f, wait operands %.0f (cycles per CTA)\n",
+            p.NT, p.n_tiles, grid, maxc, h[4] / static_cast<double>(grid), h[5] / static_cast<double>(grid), h[6] / static_cast<double>(grid));
+  }
   return CLSM_OK;
 }
 
@@ -584,8 +825,11 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
   p.n_rows = S * L; p.L = L; p.k = k; p.F = F; p.Dpad = Dpad;
   p.n_mt = (F + MT - 1) / MT;
   p.n_cr = (Dpad + DW_NT - 1) / DW_NT;
-  p.n_slices = k * p.n_cr;
-  if (p.n_mt * DW_NT > 512 || p.n_rows + 512 >= (1ll << 31) || L < 16 || F > 512) return CLSM_EUNSUPPORTED;
+  // tiling 2 (CTA = filter M tile x column slice, all window offsets) when the k accumulators fit TMEM; else
+  // tiling 1 (CTA = window offset x column slice, all filters).  CLSM_CONV_BWD_DW=1 forces tiling 1.
+  const bool tiling2 = k * DW_NT <= 512 && !(env != nullptr && env[0] == '1');
+  p.n_slices = (tiling2 ? p.n_mt : k) * p.n_cr;
+  if ((!tiling2 && p.n_mt * DW_NT > 512) || p.n_rows + 512 >= (1ll << 31) || L < 16 || F > 512) return CLSM_EUNSUPPORTED;
   int splits = clsm_sm_count() / p.n_slices;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) return CLSM_EUNSUPPORTED;
@@ -595,10 +839,11 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
   // no empty split: a CTA without chunks would issue no MMA and flush an unwritten accumulator
   splits = static_cast<int>(ceil_div64(p.chunks_total, p.chunks_per_split));
   p.G = G; p.A = A; p.ldp = ldp; p.col0 = col0; p.part = part;
-  const int stage_bytes = p.n_mt * MT_BYTES + 2 * DW_KT * 128;
+  const int stage_bytes = tiling2 ? MT_BYTES + ((2 * static_cast<int>(DW2_BOX_BYTES) + 1023) / 1024) * 1024
+                                  : p.n_mt * MT_BYTES + 2 * DW_KT * 128;
   int stages = (SMEM_LIMIT - 2048) / stage_bytes;
-  if (stages < 3) return CLSM_EUNSUPPORTED;
-  stages = 3;                                   // the builders' un-write bookkeeping is unrolled for 3 stages
+  if (stages < (tiling2 ? 4 : 3)) return CLSM_EUNSUPPORTED;
+  stages = tiling2 ? 4 : 3;                     // the builders' un-write bookkeeping is laid out for exactly this many
   p.stages = stages;
   const int smem_bytes = stages * stage_bytes + 1024 + 8 * (2 * stages + 3);
   EncodeTiledFn enc = get_encode();
@@ -606,14 +851,28 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
   CUtensorMap tmX;
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(Dpad), static_cast<cuuint64_t>(p.n_rows)};
   cuuint64_t strides[1] = {static_cast<cuuint64_t>(Dpad) * 2};
-  cuuint32_t box[2] = {64, DW_KT};
+  cuuint32_t box[2] = {64, static_cast<cuuint32_t>(tiling2 ? DW2_XROWS : DW_KT)};
   cuuint32_t estr[2] = {1, 1};
   if (enc(&tmX, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(X), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
     clsm_set_error("conv_pool_bwd(tcgen05): cuTensorMapEncodeTiled failed");
     return CLSM_ECUDA;
   }
-  if (L >= DW_KT) {
+  static int prof_on = -1;
+  if (prof_on < 0) { const char* e = getenv("CLSM_CONV_BWD_PROF"); prof_on = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  if (prof_on) {
+    void* sym = nullptr;
+    CLSM_CUDA(cudaGetSymbolAddress(&sym, g_conv_bwd_prof));
+    p.prof = static_cast<long long*>(sym);
+    CLSM_CUDA(cudaMemsetAsync(sym, 0, sizeof(long long) * 8, st));
+  }
+  if (tiling2 && L >= DW_KT) {
+    CLSM_CUDA(cudaFuncSetAttribute(dw2_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    dw2_tc_kernel<2><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
+  } else if (tiling2) {
+    CLSM_CUDA(cudaFuncSetAttribute(dw2_tc_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    dw2_tc_kernel<5><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
+  } else if (L >= DW_KT) {
     CLSM_CUDA(cudaFuncSetAttribute(dw_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     dw_tc_kernel<2><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
   } else {
@@ -621,5 +880,14 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
     dw_tc_kernel<5><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
   }
   CLSM_LAUNCH_CHECK();
+  if (prof_on && tiling2) {           // diagnostics only: synchronises and prints average cycles per CTA
+    long long h[8];
+    CLSM_CUDA(cudaStreamSynchronize(st));
+    CLSM_CUDA(cudaMemcpy(h, p.prof, sizeof(h), cudaMemcpyDeviceToHost));
+    const double g = static_cast<double>(splits) * p.n_slices;
+    fprintf(stderr, "[dw_tc prof] chunks/CTA %lld grid %d | MMA thread: total %.0f, wait operands %.0f | builder: total %.0f, "
+            "wait free stage %.0f (cycles per CTA)\n", static_cast<long long>(p.chunks_per_split), splits * p.n_slices,
+            h[0] / g, h[1] / g, h[2] / g, h[3] / g);
+  }
   return splits;
 }

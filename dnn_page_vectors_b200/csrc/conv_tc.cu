@@ -78,7 +78,7 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   auto tempty_bar = [&](int m) { return bars + 8u * (2 * p.stages + 4 + m); };
   const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 8);
 
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int warp = warp_id_uniform(), lane = threadIdx.x % 32;   // warp index as a provably warp-uniform value
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), CLUSTER ? 2 : 1); }
@@ -160,7 +160,8 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && p.shift_mode == 0) {
+    // the whole warp runs the issue loop (uniform addresses -> uniform registers); see tc_ptx.cuh
+    if (p.shift_mode == 0) {
       const uint32_t idesc = make_idesc(p.NT);
       int stage = 0; uint32_t phase = 0;
       uint32_t acc_phase = 0;
@@ -176,28 +177,28 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
           mbar_wait(full_bar(stage), phase);
           w_feed += clock64() - c0;
           tc_fence_after();
-          const uint32_t a_src = base + stage * stage_bytes;
-          const uint32_t b_src = a_src + a_bytes;
+          const uint32_t a_lo = sw128_desc_lo(base + stage * stage_bytes);
+          const uint32_t b_lo = sw128_desc_lo(base + stage * stage_bytes + a_bytes);
 #pragma unroll
           for (int ks = 0; ks < KCHUNK / 16; ++ks) {
             const uint32_t accum = (kc | ks) != 0 ? 1u : 0u;
-            const uint64_t bdesc = make_sw128_desc(b_src + ks * 32);
             for (int m = 0; m < p.n_mt; ++m)
-              tc_mma_bf16(tmem_base + static_cast<uint32_t>(m * p.NT), make_sw128_desc(a_src + m * MT_BYTES + ks * 32), bdesc, idesc, accum);
+              tc_mma_bf16_u(tmem_base + static_cast<uint32_t>(m * p.NT), a_lo + static_cast<uint32_t>(m * (MT_BYTES / 16) + ks * 2),
+                            b_lo + ks * 2, idesc, accum);
           }
-          if (CLUSTER) tc_commit_mc(empty_bar(stage), static_cast<uint16_t>(3));   // frees the slot in BOTH CTAs
-          else tc_commit(empty_bar(stage));            // smem slot free once these MMAs retire
+          if (CLUSTER) { if (elect_one()) tc_commit_mc(empty_bar(stage), static_cast<uint16_t>(3)); }   // frees the slot in BOTH CTAs
+          else tc_commit_u(empty_bar(stage));          // smem slot free once these MMAs retire
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
-        tc_commit(tfull_bar(0));                       // accumulators complete
+        tc_commit_u(tfull_bar(0));                     // accumulators complete
         acc_phase ^= 1u;
       }
-      if (p.prof != nullptr) {
+      if (p.prof != nullptr && lane == 0) {
         atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 0), static_cast<unsigned long long>(clock64() - t_begin));
         atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 1), static_cast<unsigned long long>(w_tmem));
         atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 2), static_cast<unsigned long long>(w_feed));
       }
-    } else if (lane == 0) {
+    } else {
       const uint32_t idesc = make_idesc(p.NT);
       int ws = 0; uint32_t wphase = 0, xphase = 0;
       int reg = 0; uint32_t rphase = 0;                // accumulator region of the current unit, and its use parity
@@ -212,28 +213,27 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
           const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(reg * p.NT);
           for (int cc = 0; cc < p.cpj; ++cc) {
             if (m == 0) { c0 = clock64(); mbar_wait(full_bar(p.wstages + cc), xphase); w_feed += clock64() - c0; }
-            const uint32_t x_src = x_ring + cc * x_slot_bytes;
+            const uint32_t x_lo = sw128_desc_lo(x_ring + cc * x_slot_bytes);
             for (int j = 0; j < p.k; ++j) {
               c0 = clock64();
               mbar_wait(full_bar(ws), wphase);
               w_feed += clock64() - c0;
               tc_fence_after();
-              const uint32_t a_src = w_ring + ws * MT_BYTES;
+              const uint32_t a_lo = sw128_desc_lo(w_ring + ws * MT_BYTES);
 #pragma unroll
-              for (int ks = 0; ks < KCHUNK / 16; ++ks)   // token rows j .. j+NT-1 of the resident box
-                tc_mma_bf16(d_tmem, make_sw128_desc(a_src + ks * 32), make_sw128_desc(x_src + static_cast<uint32_t>(j) * 128u + ks * 32),
-                            idesc, (cc | j | ks) != 0 ? 1u : 0u);
-              tc_commit(empty_bar(ws));
+              for (int ks = 0; ks < KCHUNK / 16; ++ks)   // token rows j .. j+NT-1 of the resident box (128 B = 8 units per row)
+                tc_mma_bf16_u(d_tmem, a_lo + ks * 2, x_lo + static_cast<uint32_t>(j) * 8u + ks * 2, idesc, (cc | j | ks) != 0 ? 1u : 0u);
+              tc_commit_u(empty_bar(ws));
               if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
             }
-            if (m == p.n_mt - 1) tc_commit(empty_bar(p.wstages + cc));   // last M tile is done with this token slot
+            if (m == p.n_mt - 1) tc_commit_u(empty_bar(p.wstages + cc));   // last M tile is done with this token slot
           }
-          tc_commit(tfull_bar(reg));                   // unit complete: its epilogue overlaps the next unit's MMAs
+          tc_commit_u(tfull_bar(reg));                 // unit complete: its epilogue overlaps the next unit's MMAs
           if (++reg == p.nreg) { reg = 0; rphase ^= 1u; }
         }
         xphase ^= 1u;
       }
-      if (p.prof != nullptr) {
+      if (p.prof != nullptr && lane == 0) {
         atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 0), static_cast<unsigned long long>(clock64() - t_begin));
         atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 1), static_cast<unsigned long long>(w_tmem));
         atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 2), static_cast<unsigned long long>(w_feed));

@@ -107,6 +107,41 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
 __device__ __forceinline__ uint64_t make_sw128_desc_bo(uint32_t saddr, uint32_t base_offset) {
   return make_sw128_desc(saddr) | (static_cast<uint64_t>(base_offset & 7u) << 49);
 }
+// ---------------------------------------------------------------- warp-uniform MMA issue
+// tcgen05.mma (SASS UTCHMMA) takes its descriptors from UNIFORM registers.  Issued from inside an
+// `if (lane == 0)` region, every operand is computed in vector registers and moved over with an
+// ELECT / R2UR.BROADCAST / BRA.U.ANY sequence -- about 23 instructions and 70-160 cycles per MMA, more than the
+// tensor pipe needs for the MMA itself (measured with scripts/mma_bench.cu: 71.5 cycles per 128x128x16 MMA that
+// way, 64.0 = the pipe's floor this way).  So the whole MMA warp runs the issue loop with warp-uniform control
+// flow and addresses, descriptors are a 32-bit running address word plus a constant high word, and only the
+// instruction itself sits under elect.sync (which elects the same lane every time for a full mask).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ int warp_id_uniform() { return __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0); }
+// high word of every 128-byte-swizzle descriptor used here: SBO = 1024 B, descriptor version 1, layout SWIZZLE_128B
+constexpr uint32_t SW128_DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+// low word: start address >> 4 (14 bits) | LBO >> 4 at bit 16.  K-major operands use LBO = 1 (ignored by the
+// hardware for swizzled K-major layouts); MN-major operands pass the byte distance between 64-element blocks.
+__device__ __forceinline__ uint32_t sw128_desc_lo(uint32_t saddr) { return ((saddr & 0x3FFFFu) >> 4) | (1u << 16); }
+__device__ __forceinline__ uint32_t sw128_mn_desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((saddr & 0x3FFFFu) >> 4) | ((lbo_bytes >> 4) << 16);
+}
+// Call from ALL lanes of a converged warp; the elected lane issues D[tmem] (+)= A[smem] * B[smem].
+__device__ __forceinline__ void tc_mma_bf16_u(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+  if (elect_one()) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %5, 0;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(SW128_DESC_HI), "r"(idesc), "r"(accumulate) : "memory");
+  }
+}
+__device__ __forceinline__ void tc_commit_u(uint32_t bar) {
+  if (elect_one()) tc_commit(bar);
+}
+
 // kind::f16, A/B = bf16 (1), D = fp32 (1), both K-major, M = 128
 __device__ __forceinline__ uint32_t make_idesc(int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) |

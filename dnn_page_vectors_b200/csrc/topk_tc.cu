@@ -54,7 +54,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const uint32_t q_bar = bars + 8u * (2 * p.stages + 4);
   const uint32_t tmem_slot = bars + 8u * (2 * p.stages + 5);
 
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int warp = warp_id_uniform(), lane = threadIdx.x % 32;
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), NUM_EPI_WARPS); }
@@ -92,25 +92,26 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // whole warp, warp-uniform issue loop (tc_ptx.cuh)
+    {
       const uint32_t idesc = make_idesc(NT);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       mbar_wait(q_bar, 0);
+      const uint32_t q_lo = sw128_desc_lo(base);
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
-        const uint32_t b_src = stage0 + stage * stage_bytes;
+        const uint32_t b_lo = sw128_desc_lo(stage0 + stage * stage_bytes);
         for (int hc = 0; hc < p.hchunks; ++hc) {
 #pragma unroll
           for (int ks = 0; ks < KCHUNK / 16; ++ks)
-            tc_mma_bf16(tmem_base + static_cast<uint32_t>(acc * NT),
-                        make_sw128_desc(base + static_cast<uint32_t>(hc) * QB * 128u + ks * 32),
-                        make_sw128_desc(b_src + static_cast<uint32_t>(hc) * NT * 128u + ks * 32), idesc, (hc | ks) != 0 ? 1u : 0u);
+            tc_mma_bf16_u(tmem_base + static_cast<uint32_t>(acc * NT), q_lo + static_cast<uint32_t>(hc) * (QB * 128u / 16u) + ks * 2,
+                          b_lo + static_cast<uint32_t>(hc) * (NT * 128u / 16u) + ks * 2, idesc, (hc | ks) != 0 ? 1u : 0u);
         }
-        tc_commit(empty_bar(stage));
-        tc_commit(tfull_bar(acc));
+        tc_commit_u(empty_bar(stage));
+        tc_commit_u(tfull_bar(acc));
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
