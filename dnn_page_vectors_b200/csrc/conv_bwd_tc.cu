@@ -279,6 +279,217 @@ dx_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const DxParams p) {
 }
 
 // =====================================================================================================
+// dX, second tiling (the default when it fits shared memory): the structure of the forward kernel's resident-tile
+// mode.  dX[r, c] = sum_j sum_f dY[r - j, f] * W[j, c, f] with dY[(s,t), f] = G[s,f] at the arg-max row of (s,f):
+// the one-hot dY tile (NT + k - 1 token rows x F filters, 64 filters per shared-memory slot) is built ONCE per
+// tile and serves every window offset j through a B descriptor whose start is advanced by (k-1-j) rows, so the
+// builders do a k-th of the work of the per-(j, filter block) tiling above.  Weights Wb stream one (M tile, j,
+// filter block) chunk of 16 KB per slot; the (tile, M tile) units rotate through 512 / NT accumulator regions
+// so that the store epilogue of one unit overlaps the MMAs of the next.
+struct Dx2Params {
+  int64_t n_rows;
+  int L, k, F, Dpad;
+  int n_mt, NT, n_tiles, fblocks;
+  const float* G; const int32_t* A; int ldp, col0;
+  float* dX; int accumulate;
+  int wstages, xrows, nreg;
+  long long* prof;
+};
+
+template <int NCH>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+dx2_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const Dx2Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t x_slot_bytes = ((static_cast<uint32_t>(p.xrows) * 128u) + 1023u) & ~1023u;
+  const uint32_t w_ring = base;
+  const uint32_t x_ring = base + static_cast<uint32_t>(p.wstages) * MT_BYTES;
+  const int stages = p.wstages + p.fblocks;                   // barrier pairs: weight slots, then dY slots
+  const uint32_t bars = x_ring + static_cast<uint32_t>(p.fblocks) * x_slot_bytes;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (stages + s); };
+  auto tfull_bar = [&](int r) { return bars + 8u * (2 * stages + r); };
+  auto tempty_bar = [&](int r) { return bars + 8u * (2 * stages + 4 + r); };
+  const uint32_t tmem_slot = bars + 8u * (2 * stages + 8);
+
+  const int warp = warp_id_uniform(), lane = threadIdx.x % 32;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) { mbar_init(full_bar(s), s < p.wstages ? 1 : NUM_BLD_WARPS); mbar_init(empty_bar(s), 1); }
+    for (int r = 0; r < 4; ++r) { mbar_init(tfull_bar(r), 1); mbar_init(tempty_bar(r), NUM_EPI_WARPS); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmWb) : "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    // ---- weights: one (M tile, filter block, window offset) chunk per slot, warp-uniform loop
+    int ws = 0; uint32_t wphase = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      for (int m = 0; m < p.n_mt; ++m)
+        for (int fb = 0; fb < p.fblocks; ++fb)
+          for (int j = 0; j < p.k; ++j) {
+            mbar_wait(empty_bar(ws), wphase ^ 1u);
+            if (elect_one()) {
+              mbar_expect_tx(full_bar(ws), MT_BYTES);
+              tma_load_2d(w_ring + ws * MT_BYTES, &tmWb, (j * p.fblocks + fb) * KCHUNK, m * MT, full_bar(ws));
+            }
+            if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
+          }
+    }
+  } else if (warp == 1) {
+    // ---- MMA issue, warp-uniform loop (tc_ptx.cuh)
+    const uint32_t idesc = make_idesc(p.NT);
+    int ws = 0; uint32_t wphase = 0, xphase = 0;
+    int reg = 0; uint32_t rphase = 0;
+    long long w_tmem = 0, w_full = 0;
+    const long long t_begin = clock64();
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      for (int m = 0; m < p.n_mt; ++m) {
+        long long c0 = clock64();
+        mbar_wait(tempty_bar(reg), rphase ^ 1u);
+        w_tmem += clock64() - c0;
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(reg * p.NT);
+        for (int fb = 0; fb < p.fblocks; ++fb) {
+          if (m == 0) { c0 = clock64(); mbar_wait(full_bar(p.wstages + fb), xphase); w_full += clock64() - c0; }
+          const uint32_t x_lo = sw128_desc_lo(x_ring + fb * x_slot_bytes);
+          for (int j = 0; j < p.k; ++j) {
+            c0 = clock64();
+            mbar_wait(full_bar(ws), wphase);
+            w_full += clock64() - c0;
+            tc_fence_after();
+            const uint32_t a_lo = sw128_desc_lo(w_ring + ws * MT_BYTES);
+#pragma unroll
+            for (int ks = 0; ks < KCHUNK / 16; ++ks)      // output token n reads tile row n + (k-1-j): 8 units of 16 B per row
+              tc_mma_bf16_u(d_tmem, a_lo + ks * 2, x_lo + static_cast<uint32_t>(p.k - 1 - j) * 8u + ks * 2, idesc, (fb | j | ks) != 0 ? 1u : 0u);
+            tc_commit_u(empty_bar(ws));
+            if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
+          }
+          if (m == p.n_mt - 1) tc_commit_u(empty_bar(p.wstages + fb));     // the builders may rebuild this slot
+        }
+        tc_commit_u(tfull_bar(reg));
+        if (++reg == p.nreg) { reg = 0; rphase ^= 1u; }
+      }
+      xphase ^= 1u;
+    }
+    if (p.prof != nullptr && lane == 0) {
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 4), static_cast<unsigned long long>(clock64() - t_begin));
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 5), static_cast<unsigned long long>(w_tmem));
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 6), static_cast<unsigned long long>(w_full));
+    }
+  } else if (warp < 2 + NUM_EPI_WARPS) {
+    // ---- epilogue: D[c, token] -> dX[token, c]; a warp's 32 lanes are 32 consecutive c of one token row
+    const int lq = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int ncol = p.NT / 2;
+    int reg = 0; uint32_t rphase = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      const int64_t rbeg = static_cast<int64_t>(tile) * p.NT + half * ncol;
+      for (int m = 0; m < p.n_mt; ++m) {
+        mbar_wait(tfull_bar(reg), rphase);
+        tc_fence_after();
+        const int c = m * MT + lq * 32 + lane;
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(reg * p.NT + half * ncol);
+        uint32_t v[NCH][16];
+#pragma unroll
+        for (int q = 0; q < NCH; ++q) tc_ld16_async(taddr + q * 16, v[q]);
+        tc_wait_ld();
+        tc_fence_before();
+        if (lane == 0) mbar_arrive(tempty_bar(reg));
+        if (++reg == p.nreg) { reg = 0; rphase ^= 1u; }
+        if (c < p.Dpad) {
+          float* dst = p.dX + rbeg * p.Dpad + c;
+#pragma unroll
+          for (int q = 0; q < NCH; ++q) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int n = q * 16 + i;
+              if (rbeg + n < p.n_rows) {
+                float x = __uint_as_float(v[q][i]);
+                if (p.accumulate) x += dst[static_cast<int64_t>(n) * p.Dpad];
+                dst[static_cast<int64_t>(n) * p.Dpad] = x;
+              }
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ---- dY builders: 4 warps, thread = (filter of the block, parity of the sequence slot).  Each slot starts
+    // all-zero; before a tile's hits are written, the previous tile's hits are cleared by recomputing their
+    // positions from (G, arg-max) (L2-resident), so nothing is remembered in registers and the sequence count
+    // per tile is unbounded.  A named barrier separates clearing from writing: a thread's new hit may land
+    // where another thread's old hit was.
+    const int bt = threadIdx.x - (2 + NUM_EPI_WARPS) * 32;        // 0..127
+    constexpr int NB = NUM_BLD_WARPS * 32;
+    const int fl = bt & 63, par = bt >> 6;
+    const uint32_t zero_chunks = static_cast<uint32_t>(p.fblocks) * x_slot_bytes / 16;
+    uint8_t* xbase = base_ptr + (x_ring - base);
+    for (uint32_t i = bt; i < zero_chunks; i += NB) reinterpret_cast<uint4*>(xbase)[i] = make_uint4(0u, 0u, 0u, 0u);
+    asm volatile("bar.sync 1, %0;" ::"n"(NB) : "memory");
+    const int rows_used = p.NT + p.k - 1;
+    auto tile_geom = [&](int tile, int64_t& r_lo, int64_t& s_first, int& nseq) {
+      r_lo = static_cast<int64_t>(tile) * p.NT - (p.k - 1);                 // token row of slot row 0 (may be < 0)
+      const int64_t r_first = r_lo < 0 ? 0 : r_lo;
+      int64_t r_last = static_cast<int64_t>(tile) * p.NT + p.NT - 1;
+      if (r_last > p.n_rows - 1) r_last = p.n_rows - 1;
+      s_first = r_first / p.L;
+      nseq = static_cast<int>(r_last / p.L - s_first) + 1;
+    };
+    auto scatter = [&](uint8_t* slot, int f, int64_t r_lo, int64_t s_first, int nseq, bool clear) {
+      for (int sq = par; sq < nseq; sq += 2) {
+        const int64_t sidx = s_first + sq;
+        const float g = __ldg(p.G + sidx * p.ldp + p.col0 + f);
+        const int a = __ldg(p.A + sidx * p.ldp + p.col0 + f);
+        const int64_t row = sidx * p.L + a - r_lo;
+        if (g != 0.0f && row >= 0 && row < rows_used) {
+          const uint32_t r = static_cast<uint32_t>(row);
+          const uint32_t off = r * 128u + ((static_cast<uint32_t>(fl >> 3) ^ (r & 7u)) << 4) + static_cast<uint32_t>(fl & 7) * 2u;
+          *reinterpret_cast<__nv_bfloat16*>(slot + off) = clear ? __float2bfloat16_rn(0.0f) : __float2bfloat16_rn(g);
+        }
+      }
+    };
+    uint32_t xphase = 0;
+    bool has_prev = false;
+    int64_t pr_lo = 0, ps_first = 0; int pnseq = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      int64_t r_lo, s_first; int nseq;
+      tile_geom(tile, r_lo, s_first, nseq);
+      for (int fb = 0; fb < p.fblocks; ++fb) {
+        const int f = fb * 64 + fl;
+        uint8_t* slot = xbase + static_cast<size_t>(fb) * x_slot_bytes;
+        mbar_wait(empty_bar(p.wstages + fb), xphase ^ 1u);
+        if (has_prev && f < p.F) scatter(slot, f, pr_lo, ps_first, pnseq, true);
+        asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
+        if (f < p.F) scatter(slot, f, r_lo, s_first, nseq, false);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(full_bar(p.wstages + fb));
+      }
+      xphase ^= 1u;
+      has_prev = true; pr_lo = r_lo; ps_first = s_first; pnseq = nseq;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
+  }
+}
+
+// =====================================================================================================
 // dW on the tensor cores:  dWt[f, (j,c)] = sum_r dY[r, f] * X[r + j, c]   (r = flat token row; dY[r, f] =
 // G[s,f] at the arg-max row of (s,f), zero elsewhere).  The reduction runs over TOKENS, so
 //   A operand = dY^T tile (128 filters x 64 tokens per M tile, K-major), built in swizzled shared memory by
@@ -766,7 +977,24 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
   // sequences one tile can touch -> candidate slots per builder thread (128 threads, 64 filters per block)
   const int max_seq = (p.NT + L - 1) / L + 1;
   const int maxc = (max_seq * 64 + 127) / 128;
-  if (maxc > 5) return CLSM_EUNSUPPORTED;
+
+  // tiling 2 (resident dY tile) when its shared-memory plan fits; CLSM_CONV_BWD_DX=1 forces tiling 1
+  Dx2Params q{};
+  bool tiling2 = !(env != nullptr && env[0] == '1');
+  if (tiling2) {
+    int nt = 224;
+    while (nt > 64 && nt + k - 1 > 256) nt -= 32;
+    q.n_rows = p.n_rows; q.L = L; q.k = k; q.F = F; q.Dpad = Dpad; q.n_mt = p.n_mt; q.NT = nt; q.fblocks = p.fblocks;
+    q.n_tiles = static_cast<int>(ceil_div64(p.n_rows, nt));
+    q.G = G; q.A = A; q.ldp = ldp; q.col0 = col0; q.dX = dX; q.accumulate = accumulate;
+    q.xrows = (nt + k - 1 + 7) / 8 * 8;
+    q.nreg = 512 / nt; if (q.nreg > 4) q.nreg = 4;
+    const int x_slot = (q.xrows * 128 + 1023) / 1024 * 1024;
+    q.wstages = (SMEM_LIMIT - 2048 - q.fblocks * x_slot) / MT_BYTES;
+    if (q.wstages > 8) q.wstages = 8;
+    if (q.wstages < 3) tiling2 = false;
+  }
+  if (!tiling2 && maxc > 5) return CLSM_EUNSUPPORTED;
 
   __nv_bfloat16* Wb = static_cast<__nv_bfloat16*>(scratch);
   const int64_t n_wb = static_cast<int64_t>(Dpad) * k * Fk;
@@ -786,7 +1014,7 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
     return CLSM_ECUDA;
   }
   int grid = clsm_sm_count();
-  if (grid > p.n_tiles) grid = p.n_tiles;
+  if (grid > (tiling2 ? q.n_tiles : p.n_tiles)) grid = tiling2 ? q.n_tiles : p.n_tiles;
   static int prof_on = -1;
   if (prof_on < 0) { const char* e = getenv("CLSM_CONV_BWD_PROF"); prof_on = (e != nullptr && e[0] == '1') ? 1 : 0; }
   if (prof_on) {
@@ -794,6 +1022,35 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
     CLSM_CUDA(cudaGetSymbolAddress(&sym, g_conv_bwd_prof));
     p.prof = static_cast<long long*>(sym);
     CLSM_CUDA(cudaMemsetAsync(sym, 0, sizeof(long long) * 8, st));
+  }
+  if (tiling2) {
+    q.prof = p.prof;
+    const int x_slot = (q.xrows * 128 + 1023) / 1024 * 1024;
+    const int stages2 = q.wstages + q.fblocks;
+    const int smem2 = q.wstages * MT_BYTES + q.fblocks * x_slot + 1024 + 8 * (2 * stages2 + 9);
+#define DX2_LAUNCH(N)                                                                                            \
+  do {                                                                                                           \
+    CLSM_CUDA(cudaFuncSetAttribute(dx2_tc_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));  \
+    dx2_tc_kernel<N><<<grid, NUM_THREADS, smem2, st>>>(tmWb, q);                                                 \
+  } while (0)
+    switch (q.NT / 32) {
+      case 2: DX2_LAUNCH(2); break;
+      case 3: DX2_LAUNCH(3); break;
+      case 4: DX2_LAUNCH(4); break;
+      case 5: DX2_LAUNCH(5); break;
+      case 6: DX2_LAUNCH(6); break;
+      default: DX2_LAUNCH(7); break;
+    }
+#undef DX2_LAUNCH
+    CLSM_LAUNCH_CHECK();
+    if (prof_on) {
+      long long h[8];
+      CLSM_CUDA(cudaStreamSynchronize(st));
+      CLSM_CUDA(cudaMemcpy(h, q.prof, sizeof(h), cudaMemcpyDeviceToHost));
+      fprintf(stderr, "[dx_tc prof] tiling 2 NT %d tiles %d grid %d wstages %d | MMA thread: total %.0f, wait TMEM %.0f, wait operands %.0f (cycles per CTA)\n",
+              q.NT, q.n_tiles, grid, q.wstages, h[4] / static_cast<double>(grid), h[5] / static_cast<double>(grid), h[6] / static_cast<double>(grid));
+    }
+    return CLSM_OK;
   }
   const int nch = p.NT / 32;
 #define DX_LAUNCH(N, C)                                                                                          \

@@ -137,7 +137,8 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
       }
-    } else if (lane == 0) {
+    } else if (p.shift_mode != 0) {
+      // whole warp, warp-uniform loop: TMA descriptors, coordinates and barrier addresses live in uniform registers
       int ws = 0; uint32_t wphase = 0, xphase = 0;
       for (int tile = tile_first; tile < tile_end; tile += tile_step) {
         const int r0 = tile * p.NT;
@@ -145,13 +146,17 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
           for (int cc = 0; cc < p.cpj; ++cc) {
             if (m == 0) {                            // the token tile: one slot per c chunk, loaded once per tile
               mbar_wait(empty_bar(p.wstages + cc), xphase ^ 1u);
-              mbar_expect_tx(full_bar(p.wstages + cc), static_cast<uint32_t>(p.xrows) * 128u);
-              tma_load_2d(x_ring + cc * x_slot_bytes, &tmX, cc * KCHUNK, r0, full_bar(p.wstages + cc));
+              if (elect_one()) {
+                mbar_expect_tx(full_bar(p.wstages + cc), static_cast<uint32_t>(p.xrows) * 128u);
+                tma_load_2d(x_ring + cc * x_slot_bytes, &tmX, cc * KCHUNK, r0, full_bar(p.wstages + cc));
+              }
             }
             for (int j = 0; j < p.k; ++j) {
               mbar_wait(empty_bar(ws), wphase ^ 1u);
-              mbar_expect_tx(full_bar(ws), MT_BYTES);
-              tma_load_2d(w_ring + ws * MT_BYTES, &tmW, (j * p.cpj + cc) * KCHUNK, m * MT, full_bar(ws));
+              if (elect_one()) {
+                mbar_expect_tx(full_bar(ws), MT_BYTES);
+                tma_load_2d(w_ring + ws * MT_BYTES, &tmW, (j * p.cpj + cc) * KCHUNK, m * MT, full_bar(ws));
+              }
               if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
             }
           }
