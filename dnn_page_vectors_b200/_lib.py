@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libclsm_b200.so")
 OK, EINVAL, ECUDA, EWORKSPACE, EUNSUPPORTED = 0, -1, -2, -3, -4
 F32, BF16 = 0, 1
 ACT = {"linear": 0, "relu": 1, "tanh": 2}
+MATH_TF32 = 0x100          # OR into the act argument of clsm_dense_fwd / clsm_dense_bwd (include/clsm_b200.h)
 IMPL = {"auto": 0, "simt": 1, "tcgen05": 2}
 
 i32, i64, u64, f32, vp, sz = C.c_int, C.c_int64, C.c_uint64, C.c_float, C.c_void_p, C.c_size_t

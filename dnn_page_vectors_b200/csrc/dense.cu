@@ -86,6 +86,130 @@ __global__ void __launch_bounds__(256) gemm_f32_kernel(GemmP p) {
   }
 }
 
+// ---- the same GEMM on the tensor cores with TF32 operands (act | CLSM_MATH_TF32; the bf16-precision mode of the
+// host model passes it).  128 x 64 x 32 tiles, 8 warps of 32 x 32, mma.sync m16n8k8, fp32 accumulation.  Operands
+// are rounded to TF32 (10-bit mantissa, cvt.rna) when they are staged; both tiles sit in shared memory as
+// [row][k] with a row pitch of 36 floats, which makes every fragment load conflict-free.  This projection is
+// 0.2 % of the step's flops: the legacy warp-level MMA is ample, no TMEM pipeline needed.
+constexpr int GM = 128, GN = 64, GK = 32, GP = GK + 4;
+
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+
+__global__ void __launch_bounds__(256) gemm_tf32_kernel(GemmP p) {
+  __shared__ uint32_t As[GM][GP];
+  __shared__ uint32_t Bs[GN][GP];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
+  const int g = lane >> 2, t = lane & 3;
+  const int64_t m0 = static_cast<int64_t>(blockIdx.x) * GM;
+  const int n0 = blockIdx.y * GN;
+  const int64_t kbeg = static_cast<int64_t>(blockIdx.z) * p.k_per_split;
+  const int64_t kend = (kbeg + p.k_per_split < p.K) ? kbeg + p.k_per_split : p.K;
+  float acc[2][4][4];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[i][j][c] = 0.0f;
+  const bool a_kfast = (p.sak == 1);
+  const bool b_kfast = (p.sbk == 1);
+  float ra[16], rb[8];
+  auto load_tiles = [&](int64_t kk) {
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      int m, q;
+      if (a_kfast) { q = tid & 31; m = (tid >> 5) + e * 8; }
+      else         { m = tid & 127; q = (tid >> 7) + e * 2; }
+      const int64_t gm = m0 + m, gk = kk + q;
+      ra[e] = (gm < p.M && gk < kend) ? __ldg(p.A + gm * p.sam + gk * p.sak) : 0.0f;
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      int n, q;
+      if (b_kfast) { q = tid & 31; n = (tid >> 5) + e * 8; }
+      else         { n = tid & 63; q = (tid >> 6) + e * 4; }
+      const int gn = n0 + n; const int64_t gk = kk + q;
+      rb[e] = (gn < p.N && gk < kend) ? __ldg(p.B + gk * p.sbk + gn * p.sbn) : 0.0f;
+    }
+  };
+  auto store_tiles = [&]() {
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      int m, q;
+      if (a_kfast) { q = tid & 31; m = (tid >> 5) + e * 8; }
+      else         { m = tid & 127; q = (tid >> 7) + e * 2; }
+      As[m][q] = to_tf32(ra[e]);
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      int n, q;
+      if (b_kfast) { q = tid & 31; n = (tid >> 5) + e * 8; }
+      else         { n = tid & 63; q = (tid >> 6) + e * 4; }
+      Bs[n][q] = to_tf32(rb[e]);
+    }
+  };
+  if (kbeg < kend) load_tiles(kbeg);
+  for (int64_t kk = kbeg; kk < kend; kk += GK) {
+    store_tiles();
+    __syncthreads();
+    if (kk + GK < kend) load_tiles(kk + GK);          // next tile's global loads fly during the MMAs
+#pragma unroll
+    for (int ks = 0; ks < GK; ks += 8) {
+      uint32_t a[2][4], b[4][2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        a[i][0] = As[wm + i * 16 + g][ks + t];
+        a[i][1] = As[wm + i * 16 + g + 8][ks + t];
+        a[i][2] = As[wm + i * 16 + g][ks + t + 4];
+        a[i][3] = As[wm + i * 16 + g + 8][ks + t + 4];
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        b[j][0] = Bs[wn + j * 8 + g][ks + t];
+        b[j][1] = Bs[wn + j * 8 + g][ks + t + 4];
+      }
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                       : "+f"(acc[i][j][0]), "+f"(acc[i][j][1]), "+f"(acc[i][j][2]), "+f"(acc[i][j][3])
+                       : "r"(a[i][0]), "r"(a[i][1]), "r"(a[i][2]), "r"(a[i][3]), "r"(b[j][0]), "r"(b[j][1]));
+    }
+    __syncthreads();
+  }
+  float* C = p.C + static_cast<int64_t>(blockIdx.z) * p.M * p.ldc;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int64_t m = m0 + wm + i * 16 + g + (c >> 1) * 8;
+        const int n = n0 + wn + j * 8 + 2 * t + (c & 1);
+        if (m >= p.M || n >= p.N) continue;
+        float v = acc[i][j][c];
+        if (p.epi == EPI_BIAS_ACT) v = act_apply(v + p.bias[n], p.act);
+        else if (p.epi == EPI_MUL_ACTGRAD) v *= act_grad_out(p.aux[m * p.ldaux + n], p.act);
+        C[m * p.ldc + n] = v;
+      }
+}
+
+void launch_gemm(const GemmP& p, int splits, bool tf32, cudaStream_t st) {
+  if (tf32) {
+    dim3 grid(static_cast<unsigned>(ceil_div64(p.M, GM)), (p.N + GN - 1) / GN, splits);
+    gemm_tf32_kernel<<<grid, 256, 0, st>>>(p);
+  } else {
+    dim3 grid(static_cast<unsigned>(ceil_div64(p.M, TM)), (p.N + TN - 1) / TN, splits);
+    gemm_f32_kernel<<<grid, 256, 0, st>>>(p);
+  }
+}
+
 // out[i] = sum_z part[z*stride + i], z ascending (deterministic)
 __global__ void reduce_splits_kernel(const float* __restrict__ part, int n_splits, int64_t stride,
                                      int64_t n, float* __restrict__ out) {
@@ -142,13 +266,14 @@ int clsm_dense_fwd(const float* pooled, int64_t S, int P, int ldp, const float* 
                    int H, int act, float* sem, void* stream) {
   CLSM_REQUIRE(S >= 0 && P > 0 && H > 0 && ldp >= P, "dense_fwd: bad sizes");
   if (S == 0) return CLSM_OK;
+  const bool tf32 = (act & CLSM_MATH_TF32) != 0;
+  act &= ~CLSM_MATH_TF32;
   GemmP p{};
   p.A = pooled; p.sam = ldp; p.sak = 1;
   p.B = Wd; p.sbk = H; p.sbn = 1;
   p.C = sem; p.ldc = H; p.M = S; p.N = H; p.K = P; p.k_per_split = P;
   p.epi = EPI_BIAS_ACT; p.act = act; p.bias = bd;
-  dim3 grid(static_cast<unsigned>(ceil_div64(S, TM)), (H + TN - 1) / TN, 1);
-  gemm_f32_kernel<<<grid, 256, 0, as_stream(stream)>>>(p);
+  launch_gemm(p, 1, tf32, as_stream(stream));
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
 }
@@ -164,6 +289,8 @@ int clsm_dense_bwd(const float* pooled, const float* sem, const float* dsem, int
                    const float* Wd, int H, int act, float* dWd, float* dbd, float* G,
                    void* ws, size_t ws_bytes, void* stream) {
   CLSM_REQUIRE(S > 0 && P > 0 && H > 0 && ldp >= P, "dense_bwd: bad sizes");
+  const bool tf32 = (act & CLSM_MATH_TF32) != 0;
+  act &= ~CLSM_MATH_TF32;
   if (ws_bytes < clsm_dense_bwd_workspace_bytes(S, P, H)) {
     clsm_set_error("dense_bwd: workspace too small (%zu < %zu)", ws_bytes, clsm_dense_bwd_workspace_bytes(S, P, H));
     return CLSM_EWORKSPACE;
@@ -188,10 +315,9 @@ int clsm_dense_bwd(const float* pooled, const float* sem, const float* dsem, int
     p.A = pooled; p.sam = 1; p.sak = ldp;
     p.B = dpre; p.sbk = H; p.sbn = 1;
     p.C = (splits > 1) ? parts : dWd; p.ldc = H; p.M = P; p.N = H; p.K = S;
-    p.k_per_split = ceil_div64(ceil_div64(S, splits), TK) * TK;
+    p.k_per_split = ceil_div64(ceil_div64(S, splits), GK) * GK;      // a multiple of both kernels' K tiles
     p.epi = EPI_NONE;
-    dim3 grid((P + TM - 1) / TM, (H + TN - 1) / TN, splits);
-    gemm_f32_kernel<<<grid, 256, 0, st>>>(p);
+    launch_gemm(p, splits, tf32, st);
     CLSM_LAUNCH_CHECK();
     if (splits > 1) {
       const int64_t ne = static_cast<int64_t>(P) * H;
@@ -206,8 +332,7 @@ int clsm_dense_bwd(const float* pooled, const float* sem, const float* dsem, int
     p.B = Wd; p.sbk = 1; p.sbn = H;
     p.C = G; p.ldc = ldp; p.M = S; p.N = P; p.K = H; p.k_per_split = H;
     p.epi = EPI_MUL_ACTGRAD; p.act = act; p.aux = pooled; p.ldaux = ldp;
-    dim3 grid(static_cast<unsigned>(ceil_div64(S, TM)), (P + TN - 1) / TN, 1);
-    gemm_f32_kernel<<<grid, 256, 0, st>>>(p);
+    launch_gemm(p, 1, tf32, st);
     CLSM_LAUNCH_CHECK();
   }
   return CLSM_OK;

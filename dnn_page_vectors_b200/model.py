@@ -24,7 +24,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import ACT, BF16, F32, IMPL, call, lib
+from ._lib import ACT, BF16, F32, IMPL, MATH_TF32, call, lib
 from .config import ModelParams
 
 
@@ -195,7 +195,7 @@ class Tower(object):
         call("clsm_pool_finalize", _ptr(b["keys"]), S, self.P, self.P, _ptr(self.convb), ACT[net.params.activation],
              _ptr(b["pooled"]), _ptr(b["argmax"]), self.P, st)
         call("clsm_dense_fwd", _ptr(b["pooled"]), S, self.P, self.P, _ptr(self.Wd), _ptr(self.bd), self.H,
-             ACT[net.params.activation], _ptr(b["sem"]), st)
+             ACT[net.params.activation] | (MATH_TF32 if self.bf16 else 0), _ptr(b["sem"]), st)
         b["keep"], b["seed"] = keep, seed
         return b["sem"]
 
@@ -206,7 +206,8 @@ class Tower(object):
         S, n_tok = b["S"], b["n_tok"]
         act = ACT[net.params.activation]
         call("clsm_dense_bwd", _ptr(b["pooled"]), _ptr(b["sem"]), _ptr(b["dsem"]), S, self.P, self.P, _ptr(self.Wd),
-             self.H, act, _ptr(self.g_Wd), _ptr(self.g_bd), _ptr(b["G"]), _ptr(b["ws"]), b["ws_bytes"], st)
+             self.H, act | (MATH_TF32 if self.bf16 else 0), _ptr(self.g_Wd), _ptr(self.g_bd), _ptr(b["G"]),
+             _ptr(b["ws"]), b["ws_bytes"], st)
         for i, k in enumerate(self.windows):
             gb = self.g_convb[i * self.F:(i + 1) * self.F]
             call("clsm_conv_pool_bwd", _ptr(b["X"]), self.dtype_code, S, self.L, self.D, self.Dpad, _ptr(self.Wt[i]),

@@ -29,6 +29,10 @@ extern "C" {
 enum { CLSM_OK = 0, CLSM_EINVAL = -1, CLSM_ECUDA = -2, CLSM_EWORKSPACE = -3, CLSM_EUNSUPPORTED = -4 };
 enum { CLSM_F32 = 0, CLSM_BF16 = 1 };
 enum { CLSM_ACT_LINEAR = 0, CLSM_ACT_RELU = 1, CLSM_ACT_TANH = 2 };
+/* OR into the `act` argument of clsm_dense_fwd / clsm_dense_bwd: run their GEMMs on the tensor cores with TF32
+ * operands (10-bit mantissa, fp32 accumulation) instead of exact fp32 on the CUDA cores.  The host model sets it
+ * in its bf16 precision mode and never in the fp32 parity mode. */
+#define CLSM_MATH_TF32 0x100
 /* conv_pool_fwd implementation selector */
 enum { CLSM_IMPL_AUTO = 0, CLSM_IMPL_SIMT = 1, CLSM_IMPL_TCGEN05 = 2 };
 

@@ -202,6 +202,42 @@ def test_dense_fwd_bwd(S, Pn, H, act):
         call("clsm_dense_bwd", P(pd_), P(sem), P(sem), S, Pn, Pn, P(wd_), H, _lib.ACT[act], P(dWd), P(dbd), P(G), P(ws), 8, ST())
 
 
+@pytest.mark.parametrize("S,Pn,H", [(5, 7, 3), (130, 300, 128), (257, 600, 150), (1000, 1200, 128), (1, 1, 1)])
+@pytest.mark.parametrize("act", ["relu", "tanh"])
+def test_dense_fwd_bwd_tf32(S, Pn, H, act):
+    """act | CLSM_MATH_TF32: the same GEMMs on the tensor cores with TF32 operands.  Each operand is rounded to a
+    10-bit mantissa (relative 2^-11), so every result is within 2 * 2^-11 (+ fp32 accumulation) of the sum of |terms|."""
+    rng = np.random.RandomState(4)
+    pooled = rng.uniform(0, 1, size=(S, Pn)) * (rng.rand(S, Pn) > 0.3)
+    Wd = rng.uniform(-0.2, 0.2, size=(Pn, H))
+    bd = rng.uniform(-0.1, 0.1, size=H)
+    dsem = rng.randn(S, H)
+    flag = _lib.ACT[act] | _lib.MATH_TF32
+    tol = 1.2e-3
+    sem = torch.empty((S, H), dtype=torch.float32, device=DEV)
+    pd_, wd_, bd_ = dev(pooled, torch.float32), dev(Wd, torch.float32), dev(bd, torch.float32)
+    call("clsm_dense_fwd", P(pd_), S, Pn, Pn, P(wd_), P(bd_), H, flag, P(sem), ST())
+    pre = pooled @ Wd + bd
+    mag = np.abs(pooled) @ np.abs(Wd) + np.abs(bd)
+    got = sem.cpu().numpy()
+    # the activations used here are 1-Lipschitz: an error of e before them is at most e after
+    assert (np.abs(got - O.act_fwd(pre, act)) <= tol * mag + 1e-6).all()
+
+    ws_bytes = lib.clsm_dense_bwd_workspace_bytes(S, Pn, H)
+    ws = torch.full((ws_bytes,), 0xA5, dtype=torch.uint8, device=DEV)
+    dWd = torch.empty((Pn, H), dtype=torch.float32, device=DEV)
+    dbd = torch.empty(H, dtype=torch.float32, device=DEV)
+    G = torch.empty((S, Pn), dtype=torch.float32, device=DEV)
+    dsem_d = dev(dsem, torch.float32)
+    call("clsm_dense_bwd", P(pd_), P(sem), P(dsem_d), S, Pn, Pn, P(wd_), H, flag, P(dWd), P(dbd), P(G), P(ws), ws_bytes, ST())
+    semn = got.astype(np.float64)
+    dpre = dsem * O.act_grad_from_output(semn, act)
+    assert (np.abs(dWd.cpu().numpy() - pooled.T @ dpre) <= tol * (np.abs(pooled).T @ np.abs(dpre)) + 1e-5).all()
+    np.testing.assert_allclose(dbd.cpu().numpy(), dpre.sum(0), rtol=1e-4, atol=1e-5)          # column sum stays fp32
+    gate = O.act_grad_from_output(pooled, act)
+    assert (np.abs(G.cpu().numpy() - (dpre @ Wd.T) * gate) <= tol * (np.abs(dpre) @ np.abs(Wd).T) * np.abs(gate) + 1e-5).all()
+
+
 # ------------------------------------------------------------------ cosine / softmax / loss
 @pytest.mark.parametrize("B,J,H", [(7, 3, 150), (64, 4, 128), (5, 50, 128), (3, 0, 8)])
 def test_sim_loss_fwd_bwd(B, J, H):
