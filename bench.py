@@ -152,6 +152,7 @@ def main():
     ap.add_argument("--conv-impl", default="auto")
     ap.add_argument("--lazy-adam", action="store_true", help="row-sparse table Adam (NOT the reference's semantics)")
     ap.add_argument("--no-extras", action="store_true", help="skip cpu_baseline / encode / topk / breakdown")
+    ap.add_argument("--dp-profile", action="store_true", help="N>1: device time of exchange / Adam / allgather per step, to stderr")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -257,6 +258,9 @@ def main():
         "clocks": clocks,
     }
 
+    if world > 1 and args.dp_profile:
+        dp_profile(net, resident_step, torch, rank)
+
     if rank == 0 and not args.no_extras:
         pk = peaks()
         # ---- per-phase device times of instrumented steps (events between C-ABI calls)
@@ -312,6 +316,46 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def dp_profile(net, resident_step, torch, rank):
+    """Device time of the data-parallel phases of a step (5 steps, median): everything before the exchange
+    (forward + backward), the gradient exchange, the sharded Adam, the compute-row allgather."""
+    marks = []
+
+    def wrap(obj, name, tag):
+        orig = getattr(obj, name)
+
+        def f(*a, **k):
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            r = orig(*a, **k)
+            e.record()
+            marks.append((tag, s, e))
+            return r
+        setattr(obj, name, f)
+        return orig
+    o1 = wrap(net.dp, "exchange", "exchange")
+    o2 = wrap(net.dp, "after_adam", "allgather")
+    o3 = wrap(net.query_model, "adam", "adam")
+    o4 = wrap(net.doc_model, "adam", "adam")
+    runs = []
+    for i in range(5):
+        marks.clear()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        resident_step(i)
+        s1.record()
+        torch.cuda.synchronize()
+        agg = {"step": s0.elapsed_time(s1)}
+        for tag, s, e in marks:
+            agg[tag] = agg.get(tag, 0.0) + s.elapsed_time(e)
+        agg["fwd_bwd"] = s0.elapsed_time(marks[0][1])
+        runs.append(agg)
+    net.dp.exchange, net.dp.after_adam, net.query_model.adam, net.doc_model.adam = o1, o2, o3, o4
+    if rank == 0:
+        med = {k: round(float(np.median([r[k] for r in runs])), 3) for k in runs[0]}
+        sys.stderr.write("[dp profile, rank 0, ms] %s\n" % json.dumps(med))
 
 
 def profile_phases(net, B, bq, bd, resident_step, torch):

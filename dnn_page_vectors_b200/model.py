@@ -226,9 +226,20 @@ class Tower(object):
         st = _stream()
         call("clsm_adam_dense", _ptr(self.flat), _ptr(self.flat_m), _ptr(self.flat_v), _ptr(self.flat_g),
              self.n_small, step, p.lr, p.beta_1, p.beta_2, p.epsilon, st)
+        lo, hi = self.shard
+        if isinstance(sparse_grad, dict):
+            # peer-memory data parallel path (parallel.py): gradient pieces of all ranks sit in this rank's
+            # receive buffers; the kernel also stores the refreshed bf16 rows into every rank's compute table
+            if hi > lo:
+                dp = self.net.dp
+                call("clsm_adam_table_dp", _ptr(self.E[lo:hi]), _ptr(self.E_m[lo:hi]), _ptr(self.E_v[lo:hi]), hi - lo, self.D,
+                     dp.world, _ptr(sparse_grad["map_in"]), self.rows_per_owner, _ptr(sparse_grad["rows_in"]),
+                     sparse_grad["cap"], self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
+                     self._peer_Ec_rows, self.Dpad, st)
+            self.refresh_compute_copies(table_too=False)
+            return
         row_of_id, dE_rows, uniq, n_uniq = sparse_grad if sparse_grad is not None else (
             b["row_of_id"], b["dE_rows"], b["uniq"], b["n_uniq"])
-        lo, hi = self.shard
         if self.net.lazy_table_adam:
             call("clsm_adam_rows", _ptr(self.E), _ptr(self.E_m), _ptr(self.E_v), self.D, _ptr(uniq), _ptr(n_uniq),
                  dE_rows.shape[0], _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,

@@ -11,6 +11,12 @@ dssm_cnn_v2/cnn_dssm_tf.py:139-156); SURVEY 8e replaces that with
               the deterministic sort + segmented reduce over what it received, applies the dense Keras Adam
               to ITS rows only (1/N of the 14 GB optimizer pass), and the refreshed bf16 compute rows are
               allgathered in place.  No (V, D) gradient is ever allreduced and replicas stay bit-identical.
+              On NVLink (bf16 mode, the default) the all-to-all and the allgather are not NCCL calls at all: the
+              receive buffers and compute tables of all ranks are mapped into every process (CUDA IPC) and two
+              kernels of libclsm_b200 do the moving -- clsm_dp_push_rows stores each owner's piece of the
+              gradient straight into the owner's memory, clsm_adam_table_dp runs the owner's Adam pass and
+              stores every refreshed bf16 row into all ranks' tables from the same kernel, so the NVLink
+              traffic overlaps the HBM-bound optimizer row by row and the host never waits for a count.
   encode    : pages split by contiguous row ranges, no communication;
   retrieval : queries replicated, each rank scans its shard, allgather of the (Q, k) lists and a
               k-way merge ordered (score desc, id asc), so the answer does not depend on the shard count.
@@ -74,6 +80,34 @@ def split_points(sorted_ids, rows_per_owner, world):
     return edges[1:] - edges[:-1]
 
 
+def share_across_ranks(t, group=None):
+    """Map tensor `t` of every rank into this process (CUDA IPC through torch's own tensor-sharing plumbing).
+    Returns one tensor per rank, all addressable from this rank's device; entry [rank] is `t` itself.
+    Collective: every rank of the group must call it with a tensor of the same role."""
+    import inspect
+    from torch.multiprocessing import reductions
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    fn, args = reductions.reduce_tensor(t)
+    objs = [None] * world
+    dist.all_gather_object(objs, (fn, args), group=group)
+    dev_arg = list(inspect.signature(reductions.rebuild_cuda_tensor).parameters).index("storage_device")
+    out = []
+    for r in range(world):
+        if r == rank:
+            out.append(t)
+            continue
+        f, a = objs[r]
+        a = list(a)
+        a[dev_arg] = torch.cuda.current_device()       # open the peer's allocation in THIS device's context
+        out.append(f(*a))
+    return out
+
+
+def _ptr_array(ptrs):
+    import ctypes
+    return (ctypes.c_void_p * len(ptrs))(*[int(x) for x in ptrs])
+
+
 class DataParallel(object):
     """Attach to a CLSM: DataParallel(net) sets net.dp; step_resident() then calls exchange()/after_adam()."""
 
@@ -96,6 +130,19 @@ class DataParallel(object):
                 # compute copy padded to world * R rows so the in-place allgather has equal slices
                 tower.E_c = torch.zeros((R * self.world, tower.Dpad), dtype=tower.E_c.dtype, device=tower.E_c.device)
             tower.refresh_compute_copies(table_too=True)
+        # peer-memory path: bf16 compute tables present, rows are whole float4s, CUDA tensors, not switched off
+        import os
+        towers = (net.query_model, net.doc_model)
+        self.p2p = (self.world > 1 and os.environ.get("CLSM_DP_P2P", "1") != "0"
+                    and all(t.E_c is not None and t.E_c.is_cuda and t.D % 4 == 0 for t in towers)
+                    and self.world <= 16 and not getattr(net, "lazy_table_adam", False))
+        if self.p2p:
+            for tower in towers:
+                R = tower.rows_per_owner
+                peers = share_across_ranks(tower.E_c, group)
+                tower._peer_Ec = peers                      # keep the mappings alive
+                off = self.rank * R * tower.Dpad * tower.E_c.element_size()
+                tower._peer_Ec_rows = _ptr_array([t.data_ptr() + off for t in peers])
         net.dp = self
 
     # ------------------------------------------------------------------ training exchange
@@ -104,6 +151,8 @@ class DataParallel(object):
         reduce it there.  Returns per tower (row_of_id, dE_rows, uniq, n_uniq) of the rows this rank owns."""
         from .model import _ptr, _stream
         from ._lib import call, lib
+        if self.p2p:
+            return self._exchange_p2p(net, bq, bd)
         allreduce_flat([net.query_model.flat_g, net.doc_model.flat_g], self.group)
         towers = ((net.query_model, bq, "q"), (net.doc_model, bd, "d"))
         W = self.world
@@ -149,8 +198,52 @@ class DataParallel(object):
             out.append((g["row_of_id"], g["rows"], g["uniq"], g["n_uniq"]))
         return out[0], out[1]
 
+    def _exchange_p2p(self, net, bq, bd):
+        """Peer-memory exchange: push each owner's piece of both towers' row-sparse gradients into the owner's
+        receive buffers, then allreduce the small gradients -- the collective also orders the pushes before the
+        owners' Adam kernels.  Returns per tower the dict Tower.adam() hands to clsm_adam_table_dp."""
+        from .model import _ptr, _stream
+        from ._lib import call
+        W = self.world
+        out = []
+        for tower, b, tag in ((net.query_model, bq, "q"), (net.doc_model, bd, "d")):
+            g = self._bufs.get(tag)
+            if g is None:
+                # first step: size and map the receive buffers (collective)
+                nmax = torch.tensor([int(b["n_tok"])], dtype=torch.int64, device=b["dE_rows"].device)
+                dist.all_reduce(nmax, op=dist.ReduceOp.MAX, group=self.group)
+                R = tower.rows_per_owner
+                cap = int(min(R, int(nmax.item())))
+                dev = b["dE_rows"].device
+                rows_in = torch.empty((W, cap, tower.Dpad), dtype=torch.float32, device=dev)
+                map_in = torch.full((W, R), -1, dtype=torch.int32, device=dev)
+                peers_rows = share_across_ranks(rows_in, self.group)
+                peers_map = share_across_ranks(map_in, self.group)
+                g = {"p2p": True, "cap": cap, "tok_basis": int(nmax.item()), "rows_in": rows_in, "map_in": map_in,
+                     "_keep": (peers_rows, peers_map),
+                     "peer_rows": _ptr_array([t.data_ptr() + self.rank * cap * tower.Dpad * 4 for t in peers_rows]),
+                     "peer_map": _ptr_array([t.data_ptr() + self.rank * R * 4 for t in peers_map]),
+                     "seg": torch.zeros(W + 1, dtype=torch.int32, device=dev)}
+                self._bufs[tag] = g
+            if int(b["n_tok"]) > g["tok_basis"]:
+                raise RuntimeError("data-parallel batch grew after the first step (%d > %d tokens per rank): the peer "
+                                   "receive buffers were sized from the first step" % (int(b["n_tok"]), g["tok_basis"]))
+            call("clsm_dp_push_rows", _ptr(b["uniq"]), _ptr(b["n_uniq"]), b["dE_rows"].shape[0], _ptr(b["dE_rows"]), tower.Dpad,
+                 tower.D, _ptr(b["row_of_id"]), tower.V1, tower.rows_per_owner, W, g["peer_rows"], g["peer_map"], g["cap"],
+                 _ptr(g["seg"]), _stream())
+            out.append(g)
+        allreduce_flat([net.query_model.flat_g, net.doc_model.flat_g], self.group)
+        return out[0], out[1]
+
     def after_adam(self, net):
-        """Every owner has refreshed the bf16 compute rows of its slice: allgather them in place."""
+        """Every owner has refreshed the bf16 compute rows of its slice: allgather them in place.  (Peer-memory
+        path: the Adam kernels already stored them everywhere; one tiny collective orders those stores before
+        the next step's gathers.)"""
+        if self.p2p:
+            if not hasattr(self, "_tick"):
+                self._tick = torch.zeros(1, dtype=torch.float32, device=net.query_model.E_c.device)
+            dist.all_reduce(self._tick, group=self.group)
+            return
         for tower in (net.query_model, net.doc_model):
             if tower.E_c is None:
                 self.gather_masters(tower, state=False)

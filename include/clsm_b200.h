@@ -156,6 +156,32 @@ int clsm_adam_rows(float* p, float* m, float* v, int D, const int32_t* uniq_ids,
 /* fp32 (n_rows, D) -> bf16 (n_rows, ld_copy) with zero pad columns */
 int clsm_table_to_bf16(const float* p, int64_t n_rows, int D, void* bf16_copy, int ld_copy, void* stream);
 
+/* ---- data-parallel table optimizer over peer memory ------------------------------------------
+ * No counterpart in the reference: its only multi-device code pins tower instances to devices
+ * (cnn_dssm_tf.py:139-156).  One process per GPU; rank r owns table rows [r*R, (r+1)*R), R = rows_per_owner.
+ * The caller maps every rank's receive buffers and bf16 compute tables into this process (CUDA IPC) and passes
+ * HOST arrays of `world` device pointers (world <= 16).
+ *
+ * clsm_dp_push_rows: cut this rank's row-sparse gradient (output of clsm_emb_scatter: uniq_ids ascending,
+ *   n_uniq on the device, compact dE_rows (max_uniq, ldg), row_of_id (n_rows)) at the ownership boundaries and
+ *   store owner o's piece into peer_rows[o] (this rank's (cap, ldg) slab of o's receive buffer, rows compact
+ *   from 0) and the rebased map slice into peer_map[o] (this rank's (R) slab: compact row inside the piece or
+ *   -1).  cap >= min(R, tokens per rank).  seg_scratch: world + 1 ints of device scratch.
+ * clsm_adam_table_dp: dense Keras Adam (same arithmetic as clsm_adam_table) over this rank's n_rows owned rows
+ *   p/m/v (n_rows, D); the gradient of a row is the sum over sources s = 0..world-1, in that order, of
+ *   rows_in[s][maps_in[s][row]] where the map entry is >= 0 (maps_in (world, R), rows_in (world, cap, ldg), both
+ *   local); the refreshed bf16 row is stored at the same row offset of every bf16_copies[s] (each rank's view
+ *   of its compute table at this rank's first owned row).  D, ldg, ld_copy multiples of 4.
+ * Ordering is the caller's: a collective (or any cross-rank barrier) on the same stream between the pushes and
+ * the Adam call, and another before the next read of the compute tables. */
+int clsm_dp_push_rows(const int32_t* uniq_ids, const int32_t* n_uniq, int64_t max_uniq, const float* dE_rows, int ldg, int D,
+                      const int32_t* row_of_id, int64_t n_rows, int64_t rows_per_owner, int world,
+                      void* const* peer_rows, void* const* peer_map, int64_t cap, int32_t* seg_scratch, void* stream);
+int clsm_adam_table_dp(float* p, float* m, float* v, int64_t n_rows, int D, int world,
+                       const int32_t* maps_in, int64_t rows_per_owner, const float* rows_in, int64_t cap, int ldg,
+                       int step, float lr, float b1, float b2, float eps,
+                       void* const* bf16_copies, int ld_copy, void* stream);
+
 /* ---- page vectors + retrieval (no script in the reference; composition of model() and RTF) ---
  * clsm_normalize_rows: vec (N, H) = sem / sqrt(max(|sem|^2, FLT_MIN))   (RTF's norm, :63-72)
  * clsm_cos_topk: scores = Qn . Cn^T over corpus rows [0, N), top-k per query ordered by
