@@ -37,26 +37,48 @@ def main():
         ref = CLSM(mp, Lq, Ld, embedding_weights=table, conv_impl=conv).compile()
         ref_losses = [ref.train_on_batch(x)[0] for _ in range(3)]
         ref_w = ref.get_weights()
+        ref1 = CLSM(mp, Lq, Ld, embedding_weights=table, conv_impl=conv).compile()      # one step only: gradient check
+        ref1.train_on_batch(x)
         # data parallel
         net = CLSM(mp, Lq, Ld, embedding_weights=table, conv_impl=conv).compile()
         DataParallel(net)
         lo, hi = shard_range(Bg, rank, world)
         xl = [a[lo:hi] for a in x]
         losses = []
-        for _ in range(3):
+        for it in range(3):
             l, _ = net.train_on_batch(xl)
             la = net.dp.reduce_metrics(torch.tensor([l, 0.0], device="cuda"))
             losses.append(float(la[0]))
+            if it == 0:
+                # Gradient-level equivalence, free of Adam's amplification: after the first step the first moment
+                # is exactly 0.1 * gradient, so compare m of every parameter (tables gathered from their owners)
+                # with the single-process run.  fp32 mode: summation order only.  bf16 mode: the tensor cores
+                # accumulate each rank's tokens separately, so allow 2e-5 of the tensor's scale.
+                gtol = 2e-6 if precision == "fp32" else 2e-5
+                for tower, rt, tag in ((net.query_model, ref1.query_model, "query"), (net.doc_model, ref1.doc_model, "doc")):
+                    net.dp.gather_masters(tower, state=True)
+                    for name, a, b in (("small", tower.flat_m, rt.flat_m), ("E", tower.E_m, rt.E_m)):
+                        a, b = a.double(), b.double()
+                        scale = float(b.abs().max()) + 1e-30
+                        bad = float(((a - b).abs() > gtol * scale).double().mean())
+                        if bad > 1e-3:
+                            ok = False
+                            print("rank %d %s %s/%s first-step gradient differs: frac %.3g max %.3g of scale" %
+                                  (rank, precision, tag, name, bad, float((a - b).abs().max()) / scale))
         w = net.get_weights()                                              # collective: gathers the sharded masters
         for a, b in zip(losses, ref_losses):
-            if abs(a - b) > 1e-5 * max(1.0, abs(b)):
+            if abs(a - b) > (1e-5 if precision == "fp32" else 1e-4) * max(1.0, abs(b)):
                 ok = False
                 print("rank %d %s loss mismatch %r vs %r" % (rank, precision, losses, ref_losses))
         for tag in ("query", "doc"):
             for name in w[tag]:
                 err = np.abs(w[tag][name] - ref_w[tag][name])
-                # Adam amplifies a sign flip of a near-zero gradient to a full step: allow a few outliers
-                if not ((err > tol).mean() < 2e-3 and err.max() < 7e-3):
+                # Adam amplifies a sign flip of a near-zero gradient to a full step: allow a few outliers.  In bf16
+                # mode the tensor-core accumulation order differs between N ranks and one process, the flips of
+                # step 1 perturb steps 2-3 everywhere at the 1e-5 level, and the fraction grows with N: the
+                # gradient check above is the sharp one there, this is a sanity bound on the trajectory.
+                frac_ok = 2e-3 if precision == "fp32" else 0.15
+                if not ((err > tol).mean() < frac_ok and err.max() < 7e-3):
                     ok = False
                     print("rank %d %s %s/%s max err %.3g frac %.3g" % (rank, precision, tag, name, err.max(), (err > tol).mean()))
         # replicas identical: compare a checksum of the compute tables and small params across ranks
