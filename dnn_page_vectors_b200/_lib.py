@@ -46,7 +46,7 @@ SIGNATURES = {
     "clsm_adam_rows": (i32, [vp, vp, vp, i32, vp, vp, i64, vp, i32, i32, f32, f32, f32, f32, vp, i32, vp]),
     "clsm_table_to_bf16": (i32, [vp, i64, i32, vp, i32, vp]),
     "clsm_dp_push_rows": (i32, [vp, vp, i64, vp, i32, i32, vp, i64, i64, i32, vp, vp, i64, vp, vp]),
-    "clsm_adam_table_dp": (i32, [vp, vp, vp, i64, i32, i32, vp, i64, vp, i64, i32, i32, f32, f32, f32, f32, vp, i32, vp]),
+    "clsm_adam_table_dp": (i32, [vp, vp, vp, i64, i32, i32, vp, i64, vp, i64, i32, i32, f32, f32, f32, f32, vp, i32, i32, vp]),
     "clsm_normalize_rows": (i32, [vp, i64, i32, vp, vp]),
     "clsm_cos_topk_workspace_bytes": (sz, [i64, i64, i32]),
     "clsm_cos_topk": (i32, [vp, i64, vp, i64, i32, i32, i64, vp, vp, vp, sz, vp]),

@@ -9,7 +9,7 @@
 //   2. (any collective on the same stream -- the allreduce of the small gradients -- orders the pushes)
 //   3. adam_table_dp: the owner walks ITS rows once: g = sum over sources s = 0..world-1 (fixed order) of the
 //      pushed row if map_in[s][row] >= 0; dense Keras Adam on p, m, v; the refreshed bf16 compute row is stored
-//      into EVERY rank's compute table (local + peers).  The HBM-bound optimizer pass and the NVLink-bound
+//      into EVERY rank's compute table (local + peers) -- if its bf16 image changed.  The HBM-bound optimizer pass and the NVLink-bound
 //      "allgather" are one kernel, so the transfer overlaps the math row by row.
 #include "common.cuh"
 #include <math.h>
@@ -70,6 +70,7 @@ struct AdamDpP {
   const int32_t* maps; int64_t R; const float* rows; int64_t cap; int ldg;
   float b1, b2, omb1, omb2, lr_t, eps;
   __nv_bfloat16* copies[MAX_WORLD]; int ld_copy;
+  int self;                // index of this rank's own table in copies[]
 };
 
 __device__ __forceinline__ void adam1(float& p, float& m, float& v, float g, const AdamDpP& c) {
@@ -108,8 +109,18 @@ __global__ void __launch_bounds__(256) adam_table_dp_kernel(AdamDpP c) {
   uint2 pk;
   pk.x = *reinterpret_cast<uint32_t*>(&lo);
   pk.y = *reinterpret_cast<uint32_t*>(&hi);
+  // Replicas hold identical compute tables, so the old local value is also what every peer holds: only rows
+  // whose bf16 image actually changed cross NVLink.  A row without a recent gradient moves by lr * m / sqrt(v)
+  // with m decaying 10 % per step -- far below bf16 resolution after a dozen steps -- so most of the table
+  // stays put and the broadcast shrinks to the rows touched recently.
   const int64_t coff = r * c.ld_copy + q * 4;
-  for (int s = 0; s < c.world; ++s) *reinterpret_cast<uint2*>(c.copies[s] + coff) = pk;
+  uint2* mine = reinterpret_cast<uint2*>(c.copies[c.self] + coff);
+  const uint2 old = *mine;
+  if (old.x != pk.x || old.y != pk.y) {
+    *mine = pk;
+    for (int s = 0; s < c.world; ++s)
+      if (s != c.self) *reinterpret_cast<uint2*>(c.copies[s] + coff) = pk;
+  }
 }
 
 }  // namespace
@@ -150,8 +161,9 @@ int clsm_dp_push_rows(const int32_t* uniq_ids, const int32_t* n_uniq, int64_t ma
 int clsm_adam_table_dp(float* p, float* m, float* v, int64_t n_rows, int D, int world,
                        const int32_t* maps_in, int64_t rows_per_owner, const float* rows_in, int64_t cap, int ldg,
                        int step, float lr, float b1, float b2, float eps,
-                       void* const* bf16_copies, int ld_copy, void* stream) {
+                       void* const* bf16_copies, int self_rank, int ld_copy, void* stream) {
   CLSM_REQUIRE(world >= 1 && world <= MAX_WORLD, "adam_table_dp: world must be 1..16");
+  CLSM_REQUIRE(self_rank >= 0 && self_rank < world, "adam_table_dp: self_rank out of range");
   CLSM_REQUIRE(n_rows > 0 && n_rows <= rows_per_owner && D > 0 && D % 4 == 0 && step >= 1 && ldg >= D && ldg % 4 == 0 && cap > 0,
                "adam_table_dp: bad sizes (D and ldg must be multiples of 4)");
   CLSM_REQUIRE(bf16_copies != nullptr && ld_copy >= D && ld_copy % 4 == 0, "adam_table_dp: bad compute-copy arguments");
@@ -165,7 +177,7 @@ int clsm_adam_table_dp(float* p, float* m, float* v, int64_t n_rows, int D, int 
     CLSM_REQUIRE(bf16_copies[s] != nullptr, "adam_table_dp: null compute-copy pointer");
     c.copies[s] = static_cast<__nv_bfloat16*>(bf16_copies[s]);
   }
-  c.ld_copy = ld_copy;
+  c.ld_copy = ld_copy; c.self = self_rank;
   const int64_t items = n_rows * (D / 4);
   adam_table_dp_kernel<<<static_cast<unsigned>(ceil_div64(items, 256)), 256, 0, as_stream(stream)>>>(c);
   CLSM_LAUNCH_CHECK();

@@ -235,7 +235,7 @@ class Tower(object):
                 call("clsm_adam_table_dp", _ptr(self.E[lo:hi]), _ptr(self.E_m[lo:hi]), _ptr(self.E_v[lo:hi]), hi - lo, self.D,
                      dp.world, _ptr(sparse_grad["map_in"]), self.rows_per_owner, _ptr(sparse_grad["rows_in"]),
                      sparse_grad["cap"], self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
-                     self._peer_Ec_rows, self.Dpad, st)
+                     self._peer_Ec_rows, dp.rank, self.Dpad, st)
             self.refresh_compute_copies(table_too=False)
             return
         row_of_id, dE_rows, uniq, n_uniq = sparse_grad if sparse_grad is not None else (

@@ -171,7 +171,9 @@ int clsm_table_to_bf16(const float* p, int64_t n_rows, int D, void* bf16_copy, i
  *   p/m/v (n_rows, D); the gradient of a row is the sum over sources s = 0..world-1, in that order, of
  *   rows_in[s][maps_in[s][row]] where the map entry is >= 0 (maps_in (world, R), rows_in (world, cap, ldg), both
  *   local); the refreshed bf16 row is stored at the same row offset of every bf16_copies[s] (each rank's view
- *   of its compute table at this rank's first owned row).  D, ldg, ld_copy multiples of 4.
+ *   of its compute table at this rank's first owned row; bf16_copies[self_rank] is this rank's own).  Replicas
+ *   must hold identical compute tables on entry: a 4-element group is sent to the peers only when its bf16 image
+ *   differs from the local old one.  D, ldg, ld_copy multiples of 4.
  * Ordering is the caller's: a collective (or any cross-rank barrier) on the same stream between the pushes and
  * the Adam call, and another before the next read of the compute tables. */
 int clsm_dp_push_rows(const int32_t* uniq_ids, const int32_t* n_uniq, int64_t max_uniq, const float* dE_rows, int ldg, int D,
@@ -180,7 +182,7 @@ int clsm_dp_push_rows(const int32_t* uniq_ids, const int32_t* n_uniq, int64_t ma
 int clsm_adam_table_dp(float* p, float* m, float* v, int64_t n_rows, int D, int world,
                        const int32_t* maps_in, int64_t rows_per_owner, const float* rows_in, int64_t cap, int ldg,
                        int step, float lr, float b1, float b2, float eps,
-                       void* const* bf16_copies, int ld_copy, void* stream);
+                       void* const* bf16_copies, int self_rank, int ld_copy, void* stream);
 
 /* ---- page vectors + retrieval (no script in the reference; composition of model() and RTF) ---
  * clsm_normalize_rows: vec (N, H) = sem / sqrt(max(|sem|^2, FLT_MIN))   (RTF's norm, :63-72)
