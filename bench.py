@@ -271,10 +271,13 @@ def main():
     if world > 1 and args.dp_profile:
         dp_profile(net, resident_step, torch, rank)
 
+    phases = None
+    if not args.no_extras:
+        # ---- per-phase device times of instrumented steps (events between C-ABI calls).  Every rank runs
+        # them (the steps contain collectives); rank 0 reports its own.
+        phases = profile_phases(net, B, bq, bd, resident_step, torch)
     if rank == 0 and not args.no_extras:
         pk = peaks()
-        # ---- per-phase device times of instrumented steps (events between C-ABI calls)
-        phases = profile_phases(net, B, bq, bd, resident_step, torch)
         line["kernels"] = phases
         fwd = flops_pair_fwd(c) * B
         # per-LAUNCH figures of the document tower (the larger of the two launches of each kernel): S = B*(1+J)
@@ -307,10 +310,12 @@ def main():
                                     "frac": (v[1] / (v[2] * 1e-3) / v[3] if v[2] > 0 else None), "launch_ms": v[2]} for k, v in cand.items()}
         line["train_flops_per_pair_3x"] = 3 * flops_pair_fwd(c)
         line["model_tflops_3x"] = 3 * fwd * (steps / (ms * 1e-3)) / 1e12
-        try:
-            line["encode"], line["topk"] = bench_inference(net, c, torch, pk)
-        except Exception as e:          # keep the headline line even if the extra leg fails
-            line["encode"] = {"error": repr(e)}
+        if world == 1:
+            try:
+                line["encode"], line["topk"] = bench_inference(net, c, torch, pk)
+            except Exception as e:          # keep the headline line even if the extra leg fails
+                line["encode"] = {"error": repr(e)}
+    if rank == 0 and not args.no_extras and world == 1:       # CPU baseline: rank 0 at N = 1 only
         try:
             from oracle import torch_cpu_port as CP
             Bs = 64
