@@ -231,7 +231,9 @@ def main():
     barrier()
     launches = int(lib.clsm_launch_count() - l0)
     ms = e0.elapsed_time(e1)
-    # ---- e2e: host numpy batches through the public API (train_on_batch), loss read back each step
+    # ---- e2e: host batches in PINNED memory through the public API (train_on_batch): ids H2D and loss D2H
+    # inside every step
+    batches = [[torch.as_tensor(a).pin_memory() for a in x] for x in batches]
     for i in range(2):
         net.train_on_batch(batches[i % len(batches)])
     barrier()

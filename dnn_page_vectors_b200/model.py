@@ -332,6 +332,8 @@ class CLSM(object):
     def _stage(self, x, train):
         if len(x) != 2 + self.J:
             raise ValueError("expected %d input arrays [query, pos_doc, %d neg_docs], got %d" % (2 + self.J, self.J, len(x)))
+        if all(isinstance(a, torch.Tensor) for a in x):
+            return self._stage_tensors(x, train)
         B = int(np.asarray(x[0]).shape[0])
         key = (B, train)
         pin = self._pinned.get(key)
@@ -348,6 +350,25 @@ class CLSM(object):
         bd = self.doc_model.buffers(B * (1 + self.J), train)
         bq["tok"].copy_(pq, non_blocking=True)
         bd["tok"].view(B, 1 + self.J, self.document_length).copy_(pdoc, non_blocking=True)
+        return B, bq, bd
+
+    def _stage_tensors(self, x, train):
+        """Batches handed over as int32 torch tensors (pinned host memory, or already on the device): no host-side
+        repacking.  Each array goes to the device with one asynchronous contiguous copy and the (pair, document)
+        interleave of the document tower happens there."""
+        B = int(x[0].shape[0])
+        for a in x:
+            if a.dtype != torch.int32 or not a.is_contiguous():
+                raise ValueError("tensor batches must be contiguous int32 (pinned host or device memory)")
+        bq = self.query_model.buffers(B, train)
+        bd = self.doc_model.buffers(B * (1 + self.J), train)
+        bq["tok"].copy_(x[0], non_blocking=True)
+        stage = bd.get("tok_stage")
+        if stage is None:
+            stage = bd["tok_stage"] = torch.empty((1 + self.J, B, self.document_length), dtype=torch.int32, device=self.device)
+        for j in range(1 + self.J):
+            stage[j].copy_(x[1 + j], non_blocking=True)
+        bd["tok"].view(B, 1 + self.J, self.document_length).copy_(stage.permute(1, 0, 2))
         return B, bq, bd
 
     def _head_bufs(self, B):

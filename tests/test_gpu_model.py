@@ -283,3 +283,24 @@ def test_fit_generator_on_synthetic_file(tmp_path):
     assert set(h) == {"loss", "acc", "val_loss", "val_acc"} and len(h["loss"]) == 4
     assert h["loss"][-1] < h["loss"][0] and h["val_loss"][-1] < h["val_loss"][0]    # it learns
     assert os.path.exists(conf.trained_model_dir + "/weights.03.pt")
+
+
+def test_pinned_tensor_batches_equal_numpy_batches():
+    """train_on_batch / test_on_batch accept int32 torch tensors (pinned host or device memory) and skip the
+    host-side repacking; the step must be identical to the NumPy path."""
+    cfg = dict(CFG_SMALL, B=8)
+    x = synth(9, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"])
+    net_a, _, _ = build("fp32", "relu", conv_impl="simt", **cfg)
+    net_b, _, _ = build("fp32", "relu", conv_impl="simt", **cfg)
+    xt = [torch.as_tensor(a).pin_memory() for a in x]
+    for _ in range(2):
+        la = net_a.train_on_batch(x)
+        lb = net_b.train_on_batch(xt)
+        assert la == lb
+    wa, wb = net_a.get_weights(), net_b.get_weights()
+    for tag in ("query", "doc"):
+        for name in wa[tag]:
+            assert np.array_equal(wa[tag][name], wb[tag][name]), (tag, name)
+    assert net_a.test_on_batch(x) == net_b.test_on_batch([t.to(DEV) for t in xt])
+    with pytest.raises(ValueError):
+        net_b.train_on_batch([t.long() for t in xt])
