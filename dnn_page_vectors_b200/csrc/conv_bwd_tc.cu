@@ -16,6 +16,9 @@
 //
 // 448 threads: warp 0 TMA producer (weights), warp 1 MMA issuer + TMEM owner, warps 2-9 epilogue,
 // warps 10-13 Gt builders.  One CTA per SM, persistent over 160-token tiles.
+// This file holds two tilings of each gradient: dx_tc / dw_tc (first: per-(window offset, filter block) operand
+// tiles) and dx2_tc / dw2_tc (default where they fit: the one-hot tile is built once and shared by all window
+// offsets through row-shifted descriptors).  DESIGN.md section 4b has the measurements.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 #include <stdlib.h>

@@ -2,10 +2,12 @@
 //   replaces Convolution1D(valid) + MaxPooling1D + Flatten, dssm_cnn_v2/cnn_dssm_tf.py:84-100.
 //
 // Implicit GEMM, no im2col, computed TRANSPOSED:  D[f, t] = sum_{j,c} Wt[f, j*Dpad + c] * X[r0 + t + j, c].
-//   A operand = filter weights Wt (Fpad, k*Dpad) K-major, in M tiles of 128 filters;
-//   B operand = the gathered token matrix X (S*L, Dpad) bf16, NT flat token rows per tile.  Output
-//   column t needs input rows t .. t+k-1, so K-chunk (j, c) of B is simply the TMA box at row coordinate
-//   r0 + j, column c*64 of the SAME 2-D tensor map.
+//   A operand = filter weights Wt (Fpad, k*Dpad) K-major, in M tiles of 128 filters, streamed one
+//               (M tile, j, c) chunk of 16 KB per shared-memory slot;
+//   B operand = the gathered token matrix X (S*L, Dpad) bf16.  Default (resident-tile) mode: one TMA box of
+//               NT + k - 1 token rows per 64-column chunk stays in shared memory for the whole tile; output
+//               column t needs input rows t .. t+k-1, so window offset j is the SAME box read through a B
+//               descriptor advanced by j rows (the UMMA swizzle works on absolute address bits).
 // Filters sit on TMEM lanes and time on TMEM columns, so the max over time is a per-thread running
 // maximum over the columns a thread reads back (tcgen05.ld 32x32b) -- no cross-lane reduction at all
 // (a 32x32 cross-lane max costs ~700-850 cycles per warp whichever way it is done: measured
@@ -14,11 +16,13 @@
 // atomicMax per (thread, sequence piece) into the (S, P) key array.  Pre-activations never reach HBM.
 //
 // Warp roles (320 threads, 1 CTA / SM, persistent over tiles):
-//   warp 0  lane 0 : TMA producer   (smem ring: full/empty mbarriers)
-//   warp 1  lane 0 : tcgen05.mma issuer; warp 1 also owns the TMEM allocation
-//   warps 2..9     : epilogue; TMEM lane quarter = warp % 4, column half = (warp - 2) / 4
-// Optional CTA pairs (cluster of 2): both CTAs run neighbouring tiles in K-lockstep and each loads HALF
-// of every weight chunk, multicast into both CTAs' shared memory.
+//   warp 0 : TMA producer   (weight ring + token slots: full/empty mbarriers)
+//   warp 1 : tcgen05.mma issuer, also owns the TMEM allocation.  Both run their loops with the WHOLE warp
+//            (warp-uniform addresses -> uniform registers, see tc_ptx.cuh); one elected lane issues.
+//   warps 2..9 : epilogue; TMEM lane quarter = warp % 4, column half = (warp - 2) / 4
+// The (tile, M tile) units rotate through 512 / NT accumulator regions, so the epilogue of one unit overlaps
+// the MMAs of the next.  Switches (A/B measurements): CLSM_CONV_TC_SHIFT=0 = first tiling (K-outer loop, all M
+// tiles per stage, one accumulator set); CLSM_CONV_TC_VARIANT=1 = CTA pairs with multicast weights (first tiling).
 #include "common.cuh"
 #include "tc_ptx.cuh"
 #include <stdlib.h>
