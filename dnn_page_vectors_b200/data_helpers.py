@@ -125,6 +125,81 @@ class DataHelpers(object):
                                          conf.document_length, level, ng) for i in range(J)]
                     yield [q, pos] + negs, np.ones(len(recs))
 
+    # ------------------------------------------------------------------ added
+    def pretokenize(self, vocab_index_dict, mode=None, out_dir=None, chunk_lines=4096):
+        """One-off conversion of the JSON-lines file of `mode` into int32 arrays on disk, so that epochs after the
+        first never touch JSON, regexes or dict lookups again (the reference's generator redoes all three for
+        every line of every epoch, data_helpers.py:148-196).
+
+        Writes `<out_dir>/{q,pos,neg0..negJ-1}.npy` (one contiguous (n, L) int32 matrix per model input, rows =
+        the records load_data_generator would keep), `line.npy` (int64 source line number of each kept record:
+        batch boundaries of the original generator are reproduced from it) and `meta.json`.  Returns out_dir."""
+        if mode not in ("training", "validation"):
+            raise Exception("Please provide mode as either 'training' or 'validation'")
+        conf = self.conf
+        path = conf.model_training_data if mode == "training" else conf.model_validation_data
+        out_dir = out_dir or (path + ".packed")
+        os.makedirs(out_dir, exist_ok=True)
+        J, Lq, Ld = conf.num_negative_examples, conf.query_length, conf.document_length
+        level, ng = conf.feature_level, conf.default_ngram
+        parts = {name: [] for name in ["q", "pos"] + ["neg%d" % i for i in range(J)]}
+        lines, n_lines = [], 0
+        with open(path, "r", encoding="utf-8") as fin:
+            while True:
+                rows = list(islice(fin, chunk_lines))
+                if not rows:
+                    break
+                recs = []
+                for k, row in enumerate(rows):
+                    d = json.loads(row)
+                    if len(d["doc_incorr"]) == J:
+                        recs.append(d)
+                        lines.append(n_lines + k)
+                n_lines += len(rows)
+                parts["q"].append(self.du.pack([d["q"] for d in recs], vocab_index_dict, Lq, level, ng))
+                parts["pos"].append(self.du.pack([d["doc_corr"] for d in recs], vocab_index_dict, Ld, level, ng))
+                for i in range(J):
+                    parts["neg%d" % i].append(self.du.pack([d["doc_incorr"][i] for d in recs], vocab_index_dict, Ld, level, ng))
+        for name, blocks in parts.items():
+            width = Lq if name == "q" else Ld
+            arr = np.concatenate(blocks, axis=0) if blocks else np.empty((0, width), dtype=np.int32)
+            np.save(os.path.join(out_dir, name + ".npy"), np.ascontiguousarray(arr, dtype=np.int32))
+        np.save(os.path.join(out_dir, "line.npy"), np.asarray(lines, dtype=np.int64))
+        with open(os.path.join(out_dir, "meta.json"), "w") as f:
+            json.dump({"source": os.path.abspath(path), "records": len(lines), "lines": n_lines, "J": J, "Lq": Lq, "Ld": Ld,
+                       "feature_level": level, "ngram": ng, "vocab_size": len(vocab_index_dict)}, f)
+        return out_dir
+
+    def load_packed_generator(self, packed_dir, batch_size=128, nb_epochs=1, pinned=False):
+        """Same yields as load_data_generator(mode, batch_size, nb_epochs) -- `([q, pos, neg_0..], ones)`, the
+        same batch boundaries (batch b = the kept records among source lines [b*batch_size, (b+1)*batch_size)),
+        the same nb_epochs + 2 passes -- read from the arrays pretokenize() wrote (memory-mapped).
+        pinned=True yields contiguous int32 torch tensors in pinned host memory instead of NumPy arrays
+        (two rotating buffer sets): CLSM.train_on_batch copies those to the device without repacking."""
+        with open(os.path.join(packed_dir, "meta.json")) as f:
+            meta = json.load(f)
+        names = ["q", "pos"] + ["neg%d" % i for i in range(meta["J"])]
+        arrs = [np.load(os.path.join(packed_dir, n + ".npy"), mmap_mode="r") for n in names]
+        line = np.load(os.path.join(packed_dir, "line.npy"))
+        n_batches = (meta["lines"] + batch_size - 1) // batch_size
+        cuts = np.searchsorted(line, np.arange(n_batches + 1, dtype=np.int64) * batch_size)
+        bufs, turn = None, 0
+        if pinned:
+            import torch
+            bufs = [[torch.empty((batch_size, a.shape[1]), dtype=torch.int32).pin_memory() for a in arrs] for _ in range(2)]
+        for _ in range(nb_epochs + 2):               # data_helpers.py:148
+            for b in range(n_batches):
+                lo, hi = int(cuts[b]), int(cuts[b + 1])
+                if pinned:
+                    out = []
+                    for a, t in zip(arrs, bufs[turn]):
+                        t.numpy()[:hi - lo] = a[lo:hi]
+                        out.append(t[:hi - lo])
+                    turn ^= 1
+                    yield out, np.ones(hi - lo)
+                else:
+                    yield [np.array(a[lo:hi]) for a in arrs], np.ones(hi - lo)
+
     # ------------------------------------------------------------------ :202-222
     def get_vocab_index_embedding_weights(self, embedding_dim, embedding_weights_masking,
                                           load_embeddings_pickled=False, load_vocab_pickled=False):

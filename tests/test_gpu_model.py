@@ -283,6 +283,16 @@ def test_fit_generator_on_synthetic_file(tmp_path):
     assert set(h) == {"loss", "acc", "val_loss", "val_acc"} and len(h["loss"]) == 4
     assert h["loss"][-1] < h["loss"][0] and h["val_loss"][-1] < h["val_loss"][0]    # it learns
     assert os.path.exists(conf.trained_model_dir + "/weights.03.pt")
+    # the same run fed from the pre-tokenised corpus as pinned int32 tensors: identical history
+    np.random.seed(1337)
+    W2, vocab2 = dh.get_vocab_index_embedding_weights(100, False)
+    net2 = CLSM(mp, conf.query_length, conf.document_length, embedding_weights=W2, device=DEV, conv_impl="simt").compile()
+    ptrain, pval = dh.pretokenize(vocab2, mode="training"), dh.pretokenize(vocab2, mode="validation")
+    hist2 = net2.fit_generator(dh.load_packed_generator(ptrain, batch_size=32, nb_epochs=4, pinned=True),
+                               samples_per_epoch=96, nb_epoch=4,
+                               validation_data=dh.load_packed_generator(pval, batch_size=32, nb_epochs=4, pinned=True),
+                               nb_val_samples=96, verbose=0)
+    assert hist2.history == h
 
 
 def test_pinned_tensor_batches_equal_numpy_batches():
