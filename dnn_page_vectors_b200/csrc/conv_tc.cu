@@ -85,7 +85,11 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   const int warp = warp_id_uniform(), lane = threadIdx.x % 32;   // warp index as a provably warp-uniform value
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), CLUSTER ? 2 : 1); }
+    // weight slots of a CTA pair are freed by BOTH CTAs' MMAs; token slots (mode 1: s >= wstages) are CTA-local
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), (CLUSTER && (p.shift_mode == 0 || s < p.wstages)) ? 2 : 1);
+    }
     for (int m = 0; m < 4; ++m) { mbar_init(tfull_bar(m), 1); mbar_init(tempty_bar(m), NUM_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -159,7 +163,11 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
               mbar_wait(empty_bar(ws), wphase ^ 1u);
               if (elect_one()) {
                 mbar_expect_tx(full_bar(ws), MT_BYTES);
-                tma_load_2d(w_ring + ws * MT_BYTES, &tmW, (j * p.cpj + cc) * KCHUNK, m * MT, full_bar(ws));
+                if (CLUSTER)      // my 64-filter half of the chunk, written into both CTAs of the pair
+                  tma_load_2d_mc(w_ring + ws * MT_BYTES + static_cast<uint32_t>(crank) * (MT_BYTES / 2), &tmW, (j * p.cpj + cc) * KCHUNK,
+                                 m * MT + crank * (MT / 2), full_bar(ws), static_cast<uint16_t>(3));
+                else
+                  tma_load_2d(w_ring + ws * MT_BYTES, &tmW, (j * p.cpj + cc) * KCHUNK, m * MT, full_bar(ws));
               }
               if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
             }
@@ -232,7 +240,8 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
 #pragma unroll
               for (int ks = 0; ks < KCHUNK / 16; ++ks)   // token rows j .. j+NT-1 of the resident box (128 B = 8 units per row)
                 tc_mma_bf16_u(d_tmem, a_lo + ks * 2, x_lo + static_cast<uint32_t>(j) * 8u + ks * 2, idesc, (cc | j | ks) != 0 ? 1u : 0u);
-              tc_commit_u(empty_bar(ws));
+              if (CLUSTER) { if (elect_one()) tc_commit_mc(empty_bar(ws), static_cast<uint16_t>(3)); }   // frees the slot in BOTH CTAs
+              else tc_commit_u(empty_bar(ws));
               if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
             }
             if (m == p.n_mt - 1) tc_commit_u(empty_bar(p.wstages + cc));   // last M tile is done with this token slot
@@ -431,7 +440,6 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
   // (4 KB weights written + 4 KB read + 5 KB tokens read + 1.7 KB tokens written per MMA at 128 B/clk).  Mode 1
   // with 224-token tiles needs 37 % fewer bytes per flop, never waits for TMEM, and is 14 % faster end to end.
   { const char* e = getenv("CLSM_CONV_TC_SHIFT"); p.shift_mode = (e != nullptr && e[0] == '0') ? 0 : 1; }
-  if (cluster) p.shift_mode = 0;
   int smem_bytes = 0;
   if (p.shift_mode != 0) {
     // mode 1 is not tied to n_mt * NT <= 512: the (tile, M tile) units rotate through 512 / NT regions.
@@ -476,7 +484,7 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
   if (!make_map_2d(&tmX, X, static_cast<uint64_t>(Dpad), static_cast<uint64_t>(n_rows), KCHUNK,
                    static_cast<uint32_t>(p.shift_mode ? p.xrows : p.NT)) ||
       !make_map_2d(&tmW, Wt, static_cast<uint64_t>(k) * Dpad, static_cast<uint64_t>(Fpad), KCHUNK,
-                   static_cast<uint32_t>(p.shift_mode ? MT : p.wbox))) {
+                   static_cast<uint32_t>(p.shift_mode ? (cluster ? MT / 2 : MT) : p.wbox))) {
     clsm_set_error("conv_pool_fwd(tcgen05): cuTensorMapEncodeTiled failed");
     return CLSM_ECUDA;
   }
@@ -511,7 +519,17 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
     CLSM_CUDA(cudaLaunchKernelEx(&cfg, conv_pool_tc_kernel<CL, N>, tmX, tmW, p));                                        \
   } while (0)
   const int nch = p.NT / 32;
-  if (cluster) { if (nch == 4) TC_LAUNCH(true, 4); else if (nch == 5) TC_LAUNCH(true, 5); else TC_LAUNCH(true, 8); }
+  if (cluster) {
+    switch (nch) {
+      case 2: TC_LAUNCH(true, 2); break;
+      case 3: TC_LAUNCH(true, 3); break;
+      case 4: TC_LAUNCH(true, 4); break;
+      case 5: TC_LAUNCH(true, 5); break;
+      case 6: TC_LAUNCH(true, 6); break;
+      case 7: TC_LAUNCH(true, 7); break;
+      default: TC_LAUNCH(true, 8); break;
+    }
+  }
   else {
     switch (nch) {
       case 2: TC_LAUNCH(false, 2); break;
