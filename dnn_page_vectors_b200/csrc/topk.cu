@@ -331,13 +331,6 @@ __global__ void kth_key_kernel(const u64* __restrict__ best, int64_t nq, int k, 
   const int64_t q = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (q < nq) thr[q] = best[q * k + (k - 1)];          // 0 while fewer than k candidates exist
 }
-// level-2 input row of query q: [lists of this segment (n_lists*k) | running best (k)]
-__global__ void append_best_kernel(u64* __restrict__ lists, int64_t stride, int64_t off, const u64* __restrict__ best, int64_t nq, int k) {
-  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= nq * k) return;
-  const int64_t q = i / k;
-  lists[q * stride + off + (i - q * k)] = best[i];
-}
 __global__ void normalize_rows_bf16_kernel(const float* __restrict__ sem, int64_t N, int H, __nv_bfloat16* __restrict__ vec) {
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const int64_t r = static_cast<int64_t>(blockIdx.x) * (blockDim.x / 32) + warp;
@@ -350,13 +343,59 @@ __global__ void normalize_rows_bf16_kernel(const float* __restrict__ sem, int64_
   for (int h = lane; h < H; h += 32) vec[r * H + h] = __float2bfloat16_rn(sem[r * H + h] / n);
 }
 
-struct TcPlan { size_t off_keys, off_l1, off_l2, off_best, off_thr, total; int64_t l1_lists; };
-TcPlan tc_plan(int k) {
+// Later segments run behind the threshold of everything scanned so far, so their survivors are few (k * rows / rows
+// already scanned, on average): the scan appends them to a COMPACT per-query list and one CTA per query folds the
+// list into the running best-k.  That makes the selection cost independent of the segment length, so the segments
+// double in size (fewer, longer scans).  A list holds a whole segment, so no ordering of the corpus can overflow it.
+constexpr int64_t SEG_MAX = 8 * SEG;            // 524288 rows: 4 MiB of list per query in the worst case
+
+// best (k, sorted descending, 0 = empty) <- k largest of best U list[0:cnt]; thr <- its k-th key; cnt <- 0
+__global__ void __launch_bounds__(TPB)
+select_compact_kernel(const u64* __restrict__ lists, int64_t cap, int* __restrict__ cnt, int k,
+                      u64* __restrict__ best, u64* __restrict__ thr) {
+  __shared__ unsigned s_hist[256];
+  __shared__ unsigned s_ctl[4];
+  __shared__ u64 s_out[KMAX];
+  __shared__ u64 s_best[KMAX];
+  const int tid = threadIdx.x;
+  const int64_t q = blockIdx.x;
+  const u64* list = lists + q * cap;
+  int64_t n = cnt[q];
+  if (n > cap) n = cap;
+  if (tid < KMAX) s_best[tid] = tid < k ? best[q * k + tid] : 0ull;
+  __syncthreads();
+  for (int64_t off = 0; off < n; off += R - KMAX) {
+    u64 keys[KPT];
+#pragma unroll
+    for (int i = 0; i < KPT; ++i) {
+      const int idx = tid + i * TPB;
+      if (idx < KMAX) keys[i] = s_best[idx];
+      else { const int64_t j = off + idx - KMAX; keys[i] = j < n ? list[j] : 0ull; }
+    }
+    select_topk(keys, k, s_hist, s_ctl, s_out);
+    __syncthreads();
+    if (tid < KMAX) s_best[tid] = tid < k ? s_out[tid] : 0ull;
+    __syncthreads();
+  }
+  if (tid < k) best[q * k + tid] = s_best[tid];
+  if (tid == 0) { thr[q] = s_best[k - 1]; cnt[q] = 0; }
+}
+
+struct TcPlan { size_t off_keys, off_l1, off_l2, off_best, off_thr, off_cnt, total; int64_t l1_lists, cap; };
+TcPlan tc_plan(int k, int64_t N) {
   TcPlan p{};
   size_t o = 0;
   auto take = [&](size_t b) { size_t r = o; o += align_up(b, 256); return r; };
   p.l1_lists = SEG / R;                                           // 32 chunks of 2048 keys
-  p.off_keys = take(static_cast<size_t>(128) * SEG * 8);
+  // list capacity per query = the longest segment this corpus will use (dense first segment: SEG)
+  p.cap = SEG;
+  for (int64_t done = SEG, seg = SEG; done < N; done += seg, seg = (2 * seg < SEG_MAX ? 2 * seg : SEG_MAX)) {
+    const int64_t len = (N - done < seg) ? N - done : seg;
+    if (len > p.cap) p.cap = len;
+  }
+  p.cap = (p.cap + 1) / 2 * 2;
+  p.off_keys = take(static_cast<size_t>(128) * p.cap * 8);
+  p.off_cnt = take(128 * 4);
   p.off_l1 = take(static_cast<size_t>(128) * (p.l1_lists + 1) * k * 8);   // + running best appended
   p.off_l2 = take(static_cast<size_t>(128) * 4 * k * 8);
   p.off_best = take(static_cast<size_t>(128) * k * 8);
@@ -369,7 +408,7 @@ TcPlan tc_plan(int k) {
 
 int clsm_score_keys_tc(const void* Qn, int64_t nQ, int64_t q_begin, const void* Cn, int64_t N, int H,
                        int64_t row_begin, int64_t row_end, unsigned long long* keys, int64_t seg_cap,
-                       const unsigned long long* thr, cudaStream_t st);     // topk_tc.cu
+                       const unsigned long long* thr, int* cnt, cudaStream_t st);     // topk_tc.cu
 
 extern "C" {
 
@@ -381,14 +420,14 @@ int clsm_normalize_rows_bf16(const float* sem, int64_t N, int H, void* vec, void
   return CLSM_OK;
 }
 
-size_t clsm_cos_topk_bf16_workspace_bytes(int64_t nQ, int64_t N, int k) { (void)nQ; (void)N; return tc_plan(k).total; }
+size_t clsm_cos_topk_bf16_workspace_bytes(int64_t nQ, int64_t N, int k) { (void)nQ; return tc_plan(k, N > 0 ? N : 1).total; }
 
 int clsm_cos_topk_bf16(const void* Qn, int64_t nQ, const void* Cn, int64_t N, int H, int k,
                        int64_t id_base, float* out_score, int64_t* out_id,
                        void* ws, size_t ws_bytes, void* stream) {
   CLSM_REQUIRE(nQ > 0 && N > 0 && N < (1ll << 31), "cos_topk_bf16: bad sizes");
   CLSM_REQUIRE(k >= 1 && k <= KMAX, "cos_topk_bf16: k must be in [1, %d]", KMAX);
-  const TcPlan p = tc_plan(k);
+  const TcPlan p = tc_plan(k, N);
   if (ws_bytes < p.total) { clsm_set_error("cos_topk_bf16: workspace too small (%zu < %zu)", ws_bytes, p.total); return CLSM_EWORKSPACE; }
   cudaStream_t st = as_stream(stream);
   char* w = static_cast<char*>(ws);
@@ -397,34 +436,31 @@ int clsm_cos_topk_bf16(const void* Qn, int64_t nQ, const void* Cn, int64_t N, in
   u64* l2 = reinterpret_cast<u64*>(w + p.off_l2);
   u64* best = reinterpret_cast<u64*>(w + p.off_best);
   u64* thr = reinterpret_cast<u64*>(w + p.off_thr);
+  int* cnt = reinterpret_cast<int*>(w + p.off_cnt);
   const int64_t l1_stride = (p.l1_lists + 1) * k;
-  // the scan writes survivors only and the level-1 select zeroes what it reads, so the key matrix is
-  // all-empty between segments; it has to start that way
-  CLSM_CUDA(cudaMemsetAsync(keys, 0, static_cast<size_t>(128) * SEG * 8, st));
   for (int64_t qb = 0; qb < nQ; qb += 128) {
     const int64_t nq = (nQ - qb < 128) ? nQ - qb : 128;
+    // first segment, DENSE: the scan writes every key at its row position, two selection levels reduce the
+    // 2048-key chunks to the block's best-k list.  The level-1 select zeroes what it reads; the region must
+    // start all-empty (later segments of the previous block left their compact lists in it).
+    CLSM_CUDA(cudaMemsetAsync(keys, 0, static_cast<size_t>(128) * SEG * 8, st));
     CLSM_CUDA(cudaMemsetAsync(best, 0, static_cast<size_t>(nq) * k * 8, st));
-    bool have_thr = false;
-    for (int64_t r0 = 0; r0 < N; r0 += SEG) {
-      const int64_t r1 = (r0 + SEG < N) ? r0 + SEG : N;
-      const int64_t rows = r1 - r0;
-      int rc = clsm_score_keys_tc(Qn, nQ, qb, Cn, N, H, r0, r1, keys, SEG, have_thr ? thr : nullptr, st);
+    CLSM_CUDA(cudaMemsetAsync(cnt, 0, 128 * 4, st));
+    {
+      const int64_t r1 = SEG < N ? SEG : N;
+      int rc = clsm_score_keys_tc(Qn, nQ, qb, Cn, N, H, 0, r1, keys, SEG, nullptr, nullptr, st);
       if (rc != CLSM_OK) return rc;
-      // level 1: every 2048-key chunk of the segment -> its k best
-      const int64_t n_chunks = ceil_div64(rows, R);
+      const int64_t n_chunks = ceil_div64(r1, R);
       {
         dim3 grid(static_cast<unsigned>(nq), static_cast<unsigned>(n_chunks));
-        topk_merge_kernel<true><<<grid, TPB, 0, st>>>(keys, SEG, ((rows + 1) / 2) * 2, k, l1, l1_stride);
+        topk_merge_kernel<true><<<grid, TPB, 0, st>>>(keys, SEG, ((r1 + 1) / 2) * 2, k, l1, l1_stride);
         CLSM_LAUNCH_CHECK();
       }
-      // level 2: those lists + the running best list -> new running best
-      append_best_kernel<<<static_cast<unsigned>(ceil_div64(nq * k, 256)), 256, 0, st>>>(l1, l1_stride, n_chunks * k, best, nq, k);
-      CLSM_LAUNCH_CHECK();
       u64* bufs[2] = {l1, l2};
-      int64_t n_in = (n_chunks + 1) * k;
+      int64_t n_in = n_chunks * k;
       int src = 0;
       int64_t stride = l1_stride;
-      while (true) {                                   // (n_chunks+1)*k <= 33*128 keys: at most two more levels
+      while (true) {                                   // 32 lists of k keys: at most two more levels
         const int64_t nc = ceil_div64(n_in, R);
         const int dst = src ^ 1;
         u64* out = (nc == 1) ? best : bufs[dst];
@@ -436,7 +472,14 @@ int clsm_cos_topk_bf16(const void* Qn, int64_t nQ, const void* Cn, int64_t N, in
       }
       kth_key_kernel<<<1, 128, 0, st>>>(best, nq, k, thr);
       CLSM_LAUNCH_CHECK();
-      have_thr = true;
+    }
+    // remaining segments, COMPACT, doubling in length
+    for (int64_t r0 = SEG, seg = SEG; r0 < N; r0 += seg, seg = (2 * seg < SEG_MAX ? 2 * seg : SEG_MAX)) {
+      const int64_t r1 = (r0 + seg < N) ? r0 + seg : N;
+      int rc = clsm_score_keys_tc(Qn, nQ, qb, Cn, N, H, r0, r1, keys, p.cap, thr, cnt, st);
+      if (rc != CLSM_OK) return rc;
+      select_compact_kernel<<<static_cast<unsigned>(nq), TPB, 0, st>>>(keys, p.cap, cnt, k, best, thr);
+      CLSM_LAUNCH_CHECK();
     }
     const int64_t n = nq * k;
     topk_decode_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(best, n, id_base, out_score + qb * k, out_id + qb * k);

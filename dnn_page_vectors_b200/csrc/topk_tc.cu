@@ -36,6 +36,9 @@ struct ScoreParams {
   u64* keys;                    // (QB, seg_cap): keys[(q - q_begin) * seg_cap + (row - row_begin)]
   int64_t seg_cap;
   const u64* thr;               // (128) or nullptr: only keys >= thr[q - q_begin] are kept
+  int* cnt;                     // (128) or nullptr.  Non-null = COMPACT mode: survivor i of query q goes to
+                                // keys[q * seg_cap + atomicAdd(cnt[q], 1)] (order irrelevant: keys are unique and the
+                                // selection is exact); null = DENSE mode: keys[q * seg_cap + (row - row_begin)]
   int stages;
 };
 
@@ -122,6 +125,10 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int64_t q = p.q_begin + ql;
     const bool qok = q < p.nQ;
     const u64 thr = (p.thr != nullptr && qok) ? p.thr[ql] : 0ull;      // thresholds are indexed inside the query block
+    // Compact mode rejects on the SCORE alone (one float compare per row; a tree max per 64 rows decides whether
+    // anything in the batch needs a key at all).  A row that ties the threshold score but loses on the id passes
+    // this test and is dropped by the exact 64-bit compare below; the selection is exact either way.
+    const float thr_f = thr != 0ull ? ordered_to_f32(static_cast<uint32_t>(thr >> 32)) : -INFINITY;
     u64* krow = p.keys + static_cast<int64_t>(ql) * p.seg_cap;
     int acc = 0; uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
@@ -136,7 +143,34 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int c = 0; c < 4; ++c) tc_ld16_async(taddr + cb + c * 16, v[c]);
         tc_wait_ld();
         if (cb + 64 >= NT) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(acc)); }
-        if (qok) {
+        if (!qok) continue;
+        if (p.cnt != nullptr) {
+          float m[4];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            float x[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) x[i] = __uint_as_float(v[c][i]);
+            m[c] = fmaxf(fmaxf(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])), fmaxf(fmaxf(x[4], x[5]), fmaxf(x[6], x[7]))),
+                         fmaxf(fmaxf(fmaxf(x[8], x[9]), fmaxf(x[10], x[11])), fmaxf(fmaxf(x[12], x[13]), fmaxf(x[14], x[15]))));
+          }
+          if (fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3])) >= thr_f) {       // rare behind a threshold
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              if (m[c] >= thr_f) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                  const float x = __uint_as_float(v[c][i]);
+                  const int64_t row = r0 + cb + c * 16 + i;
+                  if (x >= thr_f && row < p.row_end) {
+                    const u64 key = (static_cast<u64>(f32_to_ordered(x + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row));
+                    if (key >= thr) { const int pos = atomicAdd(p.cnt + ql, 1); if (pos < p.seg_cap) krow[pos] = key; }
+                  }
+                }
+              }
+            }
+          }
+        } else {
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
 #pragma unroll
@@ -151,7 +185,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 k1 = (static_cast<u64>(f32_to_ordered(__uint_as_float(v[c][i + 1]) + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row + 1));
                 if (k1 < thr) k1 = 0ull;
               }
-              if ((k0 | k1) != 0ull)       // survivors only: the matrix is all-empty on entry (topk.cu clears what it reads)
+              if ((k0 | k1) != 0ull)       // dense, survivors only: the matrix is all-empty on entry (topk.cu clears what it reads)
                 *reinterpret_cast<ulonglong2*>(krow + (row - p.row_begin)) = make_ulonglong2(k0, k1);
             }
           }
@@ -200,14 +234,14 @@ bool make_map(CUtensorMap* map, const void* ptr, uint64_t cols, uint64_t rows, u
 // Scores queries [q_begin, q_begin+128) against corpus rows [row_begin, row_end) into keys (128, seg_cap).
 int clsm_score_keys_tc(const void* Qn, int64_t nQ, int64_t q_begin, const void* Cn, int64_t N, int H,
                        int64_t row_begin, int64_t row_end, unsigned long long* keys, int64_t seg_cap,
-                       const unsigned long long* thr, cudaStream_t st) {
+                       const unsigned long long* thr, int* cnt, cudaStream_t st) {
   CLSM_REQUIRE(H == 64 || H == 128, "cos_topk(bf16): the tensor-core scan takes H = 64 or 128 (use clsm_cos_topk otherwise)");
   CLSM_REQUIRE(N < (1ll << 31) && seg_cap % 2 == 0, "cos_topk(bf16): corpus shard too large or odd segment");
   ScoreParams p{};
   p.row_begin = row_begin; p.row_end = row_end; p.q_begin = q_begin; p.nQ = nQ;
   p.hchunks = H / 64;
   p.n_tiles = static_cast<int>(ceil_div64(row_end - row_begin, NT));
-  p.keys = keys; p.seg_cap = seg_cap; p.thr = thr;
+  p.keys = keys; p.seg_cap = seg_cap; p.thr = thr; p.cnt = cnt;
   const int q_bytes = p.hchunks * QB * 128;
   const int stage_bytes = p.hchunks * NT * 128;
   int stages = (SMEM_LIMIT - 2048 - q_bytes) / stage_bytes;

@@ -531,3 +531,31 @@ def test_cos_topk_bf16_matches_oracle(Q, N, H, k):
     sc2 = torch.empty_like(sc); ids2 = torch.empty_like(ids)
     call("clsm_cos_topk_bf16", P(qd), Q, P(cd), N, H, k, 1000, P(sc2), P(ids2), P(ws), ws_bytes, ST())
     assert torch.equal(ids2, ids) and torch.equal(sc2, sc)
+
+
+def test_cos_topk_bf16_adversarial_order_and_many_queries():
+    """Rows ordered so that every later row scores higher for query 0: the running threshold never prunes anything,
+    every row of every later segment survives into the compact lists (their capacity is a whole segment) and the
+    per-query fold has to walk them in many rounds.  Also more than one 128-query block."""
+    rng = np.random.RandomState(14)
+    N, H, Q, k = 200000, 64, 130, 100
+    c = O.normalise_rows(rng.randn(N, H))
+    u = O.normalise_rows(rng.randn(1, H))[0]
+    order = np.argsort(c @ u, kind="stable")                 # ascending similarity to u
+    c = bf16_round(c[order])
+    q = bf16_round(O.normalise_rows(rng.randn(Q, H)))
+    q[0] = bf16_round(u[None, :])[0]
+    cd, qd = dev(c).to(torch.bfloat16), dev(q).to(torch.bfloat16)
+    ws_bytes = lib.clsm_cos_topk_bf16_workspace_bytes(Q, N, k)
+    ws = torch.full((ws_bytes,), 0xA5, dtype=torch.uint8, device=DEV)
+    sc = torch.empty((Q, k), dtype=torch.float32, device=DEV)
+    ids = torch.empty((Q, k), dtype=torch.int64, device=DEV)
+    call("clsm_cos_topk_bf16", P(qd), Q, P(cd), N, H, k, 0, P(sc), P(ids), P(ws), ws_bytes, ST())
+    osc, oid = O.cos_topk(q.astype(np.float64), c.astype(np.float64), k, id_base=0)
+    got_s, got_i = sc.cpu().numpy(), ids.cpu().numpy()
+    np.testing.assert_allclose(got_s, osc, rtol=2e-5, atol=2e-6)
+    mism = got_i != oid
+    assert mism.mean() < 0.02
+    for r, j in np.argwhere(mism):
+        assert abs(got_s[r, j] - osc[r, j]) < 1e-5
+    assert (got_i[0] >= N - 2000).all()                      # query 0's neighbours are the last rows
