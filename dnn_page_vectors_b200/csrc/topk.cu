@@ -346,8 +346,9 @@ __global__ void normalize_rows_bf16_kernel(const float* __restrict__ sem, int64_
 // Later segments run behind the threshold of everything scanned so far, so their survivors are few (k * rows / rows
 // already scanned, on average): the scan appends them to a COMPACT per-query list and one CTA per query folds the
 // list into the running best-k.  That makes the selection cost independent of the segment length, so the segments
-// double in size (fewer, longer scans).  A list holds a whole segment, so no ordering of the corpus can overflow it.
-constexpr int64_t SEG_MAX = 8 * SEG;            // 524288 rows: 4 MiB of list per query in the worst case
+// grow fourfold (fewer, longer scans).  A list holds a whole segment, so no ordering of the corpus can overflow it.
+constexpr int64_t SEG_MAX = 16 * SEG;           // 1 Mi rows: 8 MiB of list per query in the worst case
+constexpr int64_t GROW = 4;                     // every launch costs ~45 us whatever its length: few, long segments
 
 // best (k, sorted descending, 0 = empty) <- k largest of best U list[0:cnt]; thr <- its k-th key; cnt <- 0
 __global__ void __launch_bounds__(TPB)
@@ -389,7 +390,7 @@ TcPlan tc_plan(int k, int64_t N) {
   p.l1_lists = SEG / R;                                           // 32 chunks of 2048 keys
   // list capacity per query = the longest segment this corpus will use (dense first segment: SEG)
   p.cap = SEG;
-  for (int64_t done = SEG, seg = SEG; done < N; done += seg, seg = (2 * seg < SEG_MAX ? 2 * seg : SEG_MAX)) {
+  for (int64_t done = SEG, seg = GROW * SEG; done < N; done += seg, seg = (GROW * seg < SEG_MAX ? GROW * seg : SEG_MAX)) {
     const int64_t len = (N - done < seg) ? N - done : seg;
     if (len > p.cap) p.cap = len;
   }
@@ -473,8 +474,8 @@ int clsm_cos_topk_bf16(const void* Qn, int64_t nQ, const void* Cn, int64_t N, in
       kth_key_kernel<<<1, 128, 0, st>>>(best, nq, k, thr);
       CLSM_LAUNCH_CHECK();
     }
-    // remaining segments, COMPACT, doubling in length
-    for (int64_t r0 = SEG, seg = SEG; r0 < N; r0 += seg, seg = (2 * seg < SEG_MAX ? 2 * seg : SEG_MAX)) {
+    // remaining segments, COMPACT, each four times as long as the one before
+    for (int64_t r0 = SEG, seg = GROW * SEG; r0 < N; r0 += seg, seg = (GROW * seg < SEG_MAX ? GROW * seg : SEG_MAX)) {
       const int64_t r1 = (r0 + seg < N) ? r0 + seg : N;
       int rc = clsm_score_keys_tc(Qn, nQ, qb, Cn, N, H, r0, r1, keys, p.cap, thr, cnt, st);
       if (rc != CLSM_OK) return rc;

@@ -21,7 +21,7 @@ namespace {
 constexpr int QB = 128;                       // queries per block (UMMA M)
 constexpr int NT = 256;                       // corpus rows per tile (UMMA N)
 constexpr int KCHUNK = 64;
-constexpr int NUM_EPI_WARPS = 4;
+constexpr int NUM_EPI_WARPS = 8;              // lane quarter = warp % 4, half of the tile's columns = (warp - 2) / 4
 constexpr int NUM_THREADS = 64 + NUM_EPI_WARPS * 32;
 constexpr int SMEM_LIMIT = 227 * 1024;
 
@@ -41,6 +41,13 @@ struct ScoreParams {
                                 // selection is exact); null = DENSE mode: keys[q * seg_cap + (row - row_begin)]
   int stages;
 };
+
+// Out of line on purpose: lanes are different queries, so a survivor in one lane must not make the other 31
+// execute a predicated copy of this body for each of their rows -- the scan loop stays compare + branch.
+__device__ __noinline__ void append_survivor(float x, int64_t row, u64 thr, int* cnt, u64* krow, int64_t cap) {
+  const u64 key = (static_cast<u64>(f32_to_ordered(x + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row));
+  if (key >= thr) { const int pos = atomicAdd(cnt, 1); if (pos < cap) krow[pos] = key; }
+}
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmC, const ScoreParams p) {
@@ -136,13 +143,14 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(acc * NT);
+      const int cb_begin = ((warp - 2) >> 2) * (NT / 2);               // this warp's half of the tile's columns
 #pragma unroll 1
-      for (int cb = 0; cb < NT; cb += 64) {
+      for (int cb = cb_begin; cb < cb_begin + NT / 2; cb += 64) {
         uint32_t v[4][16];
 #pragma unroll
         for (int c = 0; c < 4; ++c) tc_ld16_async(taddr + cb + c * 16, v[c]);
         tc_wait_ld();
-        if (cb + 64 >= NT) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(acc)); }
+        if (cb + 64 >= cb_begin + NT / 2) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(acc)); }
         if (!qok) continue;
         if (p.cnt != nullptr) {
           float m[4];
@@ -161,10 +169,9 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
                   const float x = __uint_as_float(v[c][i]);
-                  const int64_t row = r0 + cb + c * 16 + i;
-                  if (x >= thr_f && row < p.row_end) {
-                    const u64 key = (static_cast<u64>(f32_to_ordered(x + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row));
-                    if (key >= thr) { const int pos = atomicAdd(p.cnt + ql, 1); if (pos < p.seg_cap) krow[pos] = key; }
+                  if (x >= thr_f) {
+                    const int64_t row = r0 + cb + c * 16 + i;
+                    if (row < p.row_end) append_survivor(x, row, thr, p.cnt + ql, krow, p.seg_cap);
                   }
                 }
               }

@@ -201,8 +201,8 @@ int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_
 /* bf16 corpus, tensor-core scoring (the production retrieval path): Qn (nQ, H) and Cn (N, H) are
  * L2-normalised bf16 (clsm_normalize_rows_bf16), H = 64 or 128 (other widths: clsm_cos_topk).  The corpus is read once per block of
  * 128 queries by a tcgen05 kernel; selection is the same exact radix select, so the order and the
- * independence from sharding are those of clsm_cos_topk.  The workspace grows with N up to 0.5 GiB (N >= 1 M
- * rows): segments after the first are scanned behind the running k-th best score, double in length, and each
+ * independence from sharding are those of clsm_cos_topk.  The workspace grows with N up to 1 GiB (N >= 1.4 M
+ * rows): segments after the first are scanned behind the running k-th best score, grow fourfold, and each
  * query's survivors go to a list that can hold a whole segment, so no corpus order can overflow it. */
 int clsm_normalize_rows_bf16(const float* sem, int64_t N, int H, void* vec, void* stream);
 size_t clsm_cos_topk_bf16_workspace_bytes(int64_t nQ, int64_t N, int k);
