@@ -169,15 +169,25 @@ dx_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const DxParams p) {
         if (m == p.n_mt - 1) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar); }
         if (c < p.Dpad) {
           float* dst = p.dX + rbeg * p.Dpad + c;
+          // Later windows add into dX.  Each element has exactly one writer, so a fire-and-forget reduction
+          // (RED.ADD.F32, result unused; denormal sums flush to zero) equals load + add + store without putting a global-load
+          // latency on every element (that chain made the 4-window configuration 20x slower) and without registers.
+          if (p.accumulate) {
 #pragma unroll
-          for (int q = 0; q < NCH; ++q) {
+            for (int q = 0; q < NCH; ++q) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const int n = q * 16 + i;
-              if (rbeg + n < p.n_rows) {
-                float x = __uint_as_float(v[q][i]);
-                if (p.accumulate) x += dst[static_cast<int64_t>(n) * p.Dpad];
-                dst[static_cast<int64_t>(n) * p.Dpad] = x;
+              for (int i = 0; i < 16; ++i) {
+                const int n = q * 16 + i;
+                if (rbeg + n < p.n_rows) atomicAdd(dst + static_cast<int64_t>(n) * p.Dpad, __uint_as_float(v[q][i]));
+              }
+            }
+          } else {
+#pragma unroll
+            for (int q = 0; q < NCH; ++q) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const int n = q * 16 + i;
+                if (rbeg + n < p.n_rows) dst[static_cast<int64_t>(n) * p.Dpad] = __uint_as_float(v[q][i]);
               }
             }
           }
@@ -412,15 +422,25 @@ dx2_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const Dx2Params p) {
         if (++reg == p.nreg) { reg = 0; rphase ^= 1u; }
         if (c < p.Dpad) {
           float* dst = p.dX + rbeg * p.Dpad + c;
+          // Later windows add into dX.  Each element has exactly one writer, so a fire-and-forget reduction
+          // (RED.ADD.F32, result unused; denormal sums flush to zero) equals load + add + store without putting a global-load
+          // latency on every element (that chain made the 4-window configuration 20x slower) and without registers.
+          if (p.accumulate) {
 #pragma unroll
-          for (int q = 0; q < NCH; ++q) {
+            for (int q = 0; q < NCH; ++q) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const int n = q * 16 + i;
-              if (rbeg + n < p.n_rows) {
-                float x = __uint_as_float(v[q][i]);
-                if (p.accumulate) x += dst[static_cast<int64_t>(n) * p.Dpad];
-                dst[static_cast<int64_t>(n) * p.Dpad] = x;
+              for (int i = 0; i < 16; ++i) {
+                const int n = q * 16 + i;
+                if (rbeg + n < p.n_rows) atomicAdd(dst + static_cast<int64_t>(n) * p.Dpad, __uint_as_float(v[q][i]));
+              }
+            }
+          } else {
+#pragma unroll
+            for (int q = 0; q < NCH; ++q) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const int n = q * 16 + i;
+                if (rbeg + n < p.n_rows) dst[static_cast<int64_t>(n) * p.Dpad] = __uint_as_float(v[q][i]);
               }
             }
           }
