@@ -1,6 +1,6 @@
 """Device time of one resident training step at the other BASELINE.json shapes (cfg3: 50 negatives of 1000 tokens,
 cfg4: four window sizes) -- parity-test shapes, timed here once for DESIGN.md; bench.py stays on cfg2.
-    python scripts/cfg_time.py cfg3|cfg4 [batch]"""
+    python scripts/cfg_time.py cfg3|cfg4|ref [batch]"""
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -8,6 +8,7 @@ import bench
 from dnn_page_vectors_b200 import CLSM, ModelParams
 
 CFG = {"cfg3": dict(V=1_000_000, D=300, windows=(3,), F=300, H=128, J=50, Lq=20, Ld=1000, B=256, act="relu"),
+       "ref": dict(V=50_000, D=100, windows=(3, 4), F=150, H=150, J=3, Lq=20, Ld=975, B=128, act="relu"),     # the reference script's literals
        "cfg4": dict(V=1_000_000, D=300, windows=(1, 2, 3, 5), F=300, H=128, J=4, Lq=20, Ld=100, B=8192, act="relu")}
 name = sys.argv[1]
 c = dict(CFG[name])
