@@ -153,12 +153,20 @@ seg_reduce_ln_kernel(const int32_t* __restrict__ in_key, const float4* __restric
     if (g < 0) { ++e; continue; }
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     int e1 = e;
+    // up to four partial rows of the run in flight at a time, added left to right (same order as one by one)
     while (e1 < CH && (s_key[e1] == g || s_key[e1] < 0)) {
-      if (s_key[e1] == g && active) {
-        const float4 v = in_rows[(b0 + e1) * ncol4 + col];
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      int idx[4], n = 0;
+      while (n < 4 && e1 < CH && (s_key[e1] == g || s_key[e1] < 0)) {
+        if (s_key[e1] == g) idx[n++] = e1;
+        ++e1;
       }
-      ++e1;
+      float4 v[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        v[i] = (i < n && active) ? in_rows[(b0 + idx[i]) * ncol4 + col] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (i < n) { acc.x += v[i].x; acc.y += v[i].y; acc.z += v[i].z; acc.w += v[i].w; }
     }
     const bool final_run = (seg_start[g] >= lo) && (seg_start[g + 1] <= hi);
     if (final_run) {
