@@ -748,14 +748,15 @@ dw_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
 constexpr int DW2_XROWS = DW_KT + 8;                        // token rows per box: the chunk plus the window halo
 constexpr uint32_t DW2_BOX_BYTES = DW2_XROWS * 128u;        // 9216 = 9 swizzle atoms
 
-template <int MAXSEQ>
+template <int MAXSEQ, int NW>        // NW = token-row columns per CTA (UMMA N): 128, or 160 when Dpad is a multiple of 160
 __global__ void __launch_bounds__(DW_THREADS, 1)
 dw2_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t a_bytes = MT_BYTES;                                          // dY^T: 128 f x 64 tokens
-  const uint32_t b_bytes = 2u * DW2_BOX_BYTES;                                // X: two boxes of 72 tokens x 64 columns
+  constexpr int NBOX = (NW + 63) / 64;
+  const uint32_t b_bytes = NBOX * DW2_BOX_BYTES;                              // X: boxes of 72 tokens x 64 columns
   const uint32_t stage_bytes = a_bytes + ((b_bytes + 1023u) & ~1023u);
   const uint32_t bars = base + static_cast<uint32_t>(p.stages) * stage_bytes;
   auto full_bar = [&](int s) { return bars + 8u * s; };
@@ -766,7 +767,7 @@ dw2_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
   const int warp = warp_id_uniform(), lane = threadIdx.x % 32;
   const int split = blockIdx.x / p.n_slices;
   const int slice = blockIdx.x - split * p.n_slices;
-  const int mt = slice / p.n_cr, c0 = (slice - mt * p.n_cr) * DW_NT;           // filter M tile, column slice
+  const int mt = slice / p.n_cr, c0 = (slice - mt * p.n_cr) * NW;           // filter M tile, column slice
   const int64_t ch_begin = static_cast<int64_t>(split) * p.chunks_per_split;
   const int64_t ch_end = (ch_begin + p.chunks_per_split < p.chunks_total) ? ch_begin + p.chunks_per_split : p.chunks_total;
 
@@ -794,14 +795,14 @@ dw2_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
         mbar_wait(empty_bar(stage), phase ^ 1u);
         mbar_expect_tx(full_bar(stage), b_bytes);
         const uint32_t b_dst = base + stage * stage_bytes + a_bytes;
-        tma_load_2d(b_dst, &tmX, c0, r0, full_bar(stage));
-        tma_load_2d(b_dst + DW2_BOX_BYTES, &tmX, c0 + 64, r0, full_bar(stage));
+#pragma unroll
+        for (int b = 0; b < NBOX; ++b) tma_load_2d(b_dst + b * DW2_BOX_BYTES, &tmX, c0 + 64 * b, r0, full_bar(stage));
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
     }
   } else if (warp == 1) {
     {
-      const uint32_t idesc = make_idesc(DW_NT) | (1u << 16);                 // B operand MN-major
+      const uint32_t idesc = make_idesc(NW) | (1u << 16);                 // B operand MN-major
       int stage = 0; uint32_t phase = 0;
       bool first = true;
       long long w_full = 0;
@@ -817,7 +818,7 @@ dw2_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
         for (int ks = 0; ks < DW_KT / 16; ++ks) {
           const uint32_t accum = (first && ks == 0) ? 0u : 1u;
           for (int j = 0; j < p.k; ++j)                                        // token rows 16 ks + j .. of the box
-            tc_mma_bf16_u(tmem_base + static_cast<uint32_t>(j * DW_NT), a_lo + ks * 2, b_lo + ks * 128 + static_cast<uint32_t>(j) * 8u, idesc, accum);
+            tc_mma_bf16_u(tmem_base + static_cast<uint32_t>(j * NW), a_lo + ks * 2, b_lo + ks * 128 + static_cast<uint32_t>(j) * 8u, idesc, accum);
         }
         first = false;
         tc_commit_u(empty_bar(stage));
@@ -918,24 +919,25 @@ dw2_tc_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
     }
     // ---- epilogue (same warps): D_j[f, n] -> part[split][f][j][c0 + n]
     const int lq = warp & 3;
-    const int half = (warp - 2) >> 2;                      // 64 of the 128 columns each
+    const int half = (warp - 2) >> 2;                      // half of the NW columns each
+    constexpr int HW = NW / 2, NQ = HW / 16;
     mbar_wait(tfull_bar, 0);
     tc_fence_after();
     const int fo = mt * MT + lq * 32 + lane;
     for (int j = 0; j < p.k; ++j) {
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(j * DW_NT + half * 64);
-      uint32_t v[4][16];
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(j * NW + half * HW);
+      uint32_t v[NQ][16];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) tc_ld16_async(taddr + q * 16, v[q]);
+      for (int q = 0; q < NQ; ++q) tc_ld16_async(taddr + q * 16, v[q]);
       tc_wait_ld();
       if (fo < p.F) {
-        float* dst = p.part + ((static_cast<int64_t>(split) * p.F + fo) * p.k + j) * p.Dpad + c0 + half * 64;
+        float* dst = p.part + ((static_cast<int64_t>(split) * p.F + fo) * p.k + j) * p.Dpad + c0 + half * HW;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < NQ; ++q) {
 #pragma unroll
           for (int i = 0; i < 16; i += 4) {
             const int n = q * 16 + i;
-            if (c0 + half * 64 + n < p.Dpad)
+            if (c0 + half * HW + n < p.Dpad)
               *reinterpret_cast<float4*>(dst + n) = make_float4(__uint_as_float(v[q][i]), __uint_as_float(v[q][i + 1]),
                                                                  __uint_as_float(v[q][i + 2]), __uint_as_float(v[q][i + 3]));
           }
@@ -1104,10 +1106,14 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
   DwParams p{};
   p.n_rows = S * L; p.L = L; p.k = k; p.F = F; p.Dpad = Dpad;
   p.n_mt = (F + MT - 1) / MT;
-  p.n_cr = (Dpad + DW_NT - 1) / DW_NT;
   // tiling 2 (CTA = filter M tile x column slice, all window offsets) when the k accumulators fit TMEM; else
   // tiling 1 (CTA = window offset x column slice, all filters).  CLSM_CONV_BWD_DW=1 forces tiling 1.
-  const bool tiling2 = k * DW_NT <= 512 && !(env != nullptr && env[0] == '1');
+  // Slice width of tiling 2: 160 columns when that divides Dpad (D = 300 -> Dpad = 320 = 2 x 160: no padded
+  // columns, against 3 x 128 = 384), else 128.
+  const bool force1 = env != nullptr && env[0] == '1';
+  const int nw = (!force1 && Dpad % 160 == 0 && k * 160 <= 512) ? 160 : DW_NT;
+  const bool tiling2 = k * nw <= 512 && !force1;
+  p.n_cr = tiling2 ? (Dpad + nw - 1) / nw : (Dpad + DW_NT - 1) / DW_NT;
   p.n_slices = (tiling2 ? p.n_mt : k) * p.n_cr;
   if ((!tiling2 && p.n_mt * DW_NT > 512) || p.n_rows + 512 >= (1ll << 31) || L < 16 || F > 512) return CLSM_EUNSUPPORTED;
   int splits = clsm_sm_count() / p.n_slices;
@@ -1119,7 +1125,7 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
   // no empty split: a CTA without chunks would issue no MMA and flush an unwritten accumulator
   splits = static_cast<int>(ceil_div64(p.chunks_total, p.chunks_per_split));
   p.G = G; p.A = A; p.ldp = ldp; p.col0 = col0; p.part = part;
-  const int stage_bytes = tiling2 ? MT_BYTES + ((2 * static_cast<int>(DW2_BOX_BYTES) + 1023) / 1024) * 1024
+  const int stage_bytes = tiling2 ? MT_BYTES + ((((nw + 63) / 64) * static_cast<int>(DW2_BOX_BYTES) + 1023) / 1024) * 1024
                                   : p.n_mt * MT_BYTES + 2 * DW_KT * 128;
   int stages = (SMEM_LIMIT - 2048) / stage_bytes;
   if (stages < (tiling2 ? 4 : 3)) return CLSM_EUNSUPPORTED;
@@ -1146,12 +1152,14 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
     p.prof = static_cast<long long*>(sym);
     CLSM_CUDA(cudaMemsetAsync(sym, 0, sizeof(long long) * 8, st));
   }
-  if (tiling2 && L >= DW_KT) {
-    CLSM_CUDA(cudaFuncSetAttribute(dw2_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    dw2_tc_kernel<2><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
-  } else if (tiling2) {
-    CLSM_CUDA(cudaFuncSetAttribute(dw2_tc_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    dw2_tc_kernel<5><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
+#define DW2_LAUNCH(Q, W)                                                                                          \
+  do {                                                                                                            \
+    CLSM_CUDA(cudaFuncSetAttribute(dw2_tc_kernel<Q, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)); \
+    dw2_tc_kernel<Q, W><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);                             \
+  } while (0)
+  if (tiling2) {
+    if (L >= DW_KT) { if (nw == 160) DW2_LAUNCH(2, 160); else DW2_LAUNCH(2, 128); }
+    else            { if (nw == 160) DW2_LAUNCH(5, 160); else DW2_LAUNCH(5, 128); }
   } else if (L >= DW_KT) {
     CLSM_CUDA(cudaFuncSetAttribute(dw_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     dw_tc_kernel<2><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
