@@ -30,7 +30,7 @@ sys.path.insert(0, ROOT)
 # init: every cosine goes negative, is clipped, and all gradients are zero from then on (measured).
 # A dead backward would be skipped work, so the benchmark trains the reference's ReLU model.
 CFG2 = dict(V=1_000_000, D=300, windows=(3,), F=300, H=128, J=4, Lq=20, Ld=100, B=4096, act="relu")
-DW_SHARE = 0.54        # dw2_tc : (dw2_tc + dx2_tc) device-time ratio from the ncu launch list under profiles/
+DW_SHARE = 0.49        # dw2_tc : (dw2_tc + dx2_tc) device-time ratio from the ncu launch list under profiles/
 WORKLOAD = "cfg2: CLSM bf16 train step, B=4096/GPU, J=4, Lq=20, Ld=100, D=300, window 3, F=300, H=128, V=1M, dense Adam"
 
 
