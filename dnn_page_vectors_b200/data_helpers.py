@@ -28,6 +28,31 @@ from .config import Configuration
 from .data_utils import PAD_WORD, UNK_WORD, DataUtils
 
 
+_PACK = {}
+
+
+def _pack_init(vocab_index_dict, spec):
+    _PACK["vocab"], _PACK["spec"], _PACK["du"] = vocab_index_dict, spec, DataUtils()
+
+
+def _pack_chunk(rows):
+    """rows: JSON lines -> (number of lines, indices of the kept ones, [q, pos, neg_0..] int32 blocks).  Runs in the
+    pretokenize() worker processes (and in-process when workers == 1)."""
+    J, Lq, Ld, level, ng = _PACK["spec"]
+    vocab, du = _PACK["vocab"], _PACK["du"]
+    recs, kept = [], []
+    for k, row in enumerate(rows):
+        d = json.loads(row)
+        if len(d["doc_incorr"]) == J:
+            recs.append(d)
+            kept.append(k)
+    arrays = [du.pack([d["q"] for d in recs], vocab, Lq, level, ng),
+              du.pack([d["doc_corr"] for d in recs], vocab, Ld, level, ng)]
+    for i in range(J):
+        arrays.append(du.pack([d["doc_incorr"][i] for d in recs], vocab, Ld, level, ng))
+    return len(rows), kept, arrays
+
+
 def _mask_tag(masking):
     return "masked" if masking else "non_masked"
 
@@ -126,14 +151,15 @@ class DataHelpers(object):
                     yield [q, pos] + negs, np.ones(len(recs))
 
     # ------------------------------------------------------------------ added
-    def pretokenize(self, vocab_index_dict, mode=None, out_dir=None, chunk_lines=4096):
+    def pretokenize(self, vocab_index_dict, mode=None, out_dir=None, chunk_lines=4096, workers=1):
         """One-off conversion of the JSON-lines file of `mode` into int32 arrays on disk, so that epochs after the
         first never touch JSON, regexes or dict lookups again (the reference's generator redoes all three for
         every line of every epoch, data_helpers.py:148-196).
 
         Writes `<out_dir>/{q,pos,neg0..negJ-1}.npy` (one contiguous (n, L) int32 matrix per model input, rows =
         the records load_data_generator would keep), `line.npy` (int64 source line number of each kept record:
-        batch boundaries of the original generator are reproduced from it) and `meta.json`.  Returns out_dir."""
+        batch boundaries of the original generator are reproduced from it) and `meta.json`.  Returns out_dir.
+        workers > 1 tokenises the chunks in that many processes (the result does not depend on it)."""
         if mode not in ("training", "validation"):
             raise Exception("Please provide mode as either 'training' or 'validation'")
         conf = self.conf
@@ -142,24 +168,37 @@ class DataHelpers(object):
         os.makedirs(out_dir, exist_ok=True)
         J, Lq, Ld = conf.num_negative_examples, conf.query_length, conf.document_length
         level, ng = conf.feature_level, conf.default_ngram
-        parts = {name: [] for name in ["q", "pos"] + ["neg%d" % i for i in range(J)]}
+        names = ["q", "pos"] + ["neg%d" % i for i in range(J)]
+        parts = {name: [] for name in names}
         lines, n_lines = [], 0
-        with open(path, "r", encoding="utf-8") as fin:
-            while True:
-                rows = list(islice(fin, chunk_lines))
-                if not rows:
-                    break
-                recs = []
-                for k, row in enumerate(rows):
-                    d = json.loads(row)
-                    if len(d["doc_incorr"]) == J:
-                        recs.append(d)
-                        lines.append(n_lines + k)
-                n_lines += len(rows)
-                parts["q"].append(self.du.pack([d["q"] for d in recs], vocab_index_dict, Lq, level, ng))
-                parts["pos"].append(self.du.pack([d["doc_corr"] for d in recs], vocab_index_dict, Ld, level, ng))
-                for i in range(J):
-                    parts["neg%d" % i].append(self.du.pack([d["doc_incorr"][i] for d in recs], vocab_index_dict, Ld, level, ng))
+
+        def chunks():
+            with open(path, "r", encoding="utf-8") as fin:
+                while True:
+                    rows = list(islice(fin, chunk_lines))
+                    if not rows:
+                        return
+                    yield rows
+
+        spec = (J, Lq, Ld, level, ng)
+        if workers > 1:
+            import multiprocessing as mp
+            pool = mp.get_context("fork").Pool(workers, initializer=_pack_init, initargs=(vocab_index_dict, spec))
+            results = pool.imap(_pack_chunk, chunks())          # ordered: chunk i's arrays come out i-th
+        else:
+            pool = None
+            _pack_init(vocab_index_dict, spec)
+            results = map(_pack_chunk, chunks())
+        try:
+            for n_rows, kept, arrays in results:
+                lines.extend(n_lines + k for k in kept)
+                n_lines += n_rows
+                for name, arr in zip(names, arrays):
+                    parts[name].append(arr)
+        finally:
+            if pool is not None:
+                pool.close()
+                pool.join()
         for name, blocks in parts.items():
             width = Lq if name == "q" else Ld
             arr = np.concatenate(blocks, axis=0) if blocks else np.empty((0, width), dtype=np.int32)

@@ -20,6 +20,9 @@ with tempfile.TemporaryDirectory() as root:
     _, vocab = dh.generate_vocabulary_set()
     t = time.perf_counter(); cnt = sum(len(y) for _, y in dh.load_data_generator(vocab, "training", 1024, nb_epochs=0)); dt_json = time.perf_counter() - t
     t = time.perf_counter(); packed = dh.pretokenize(vocab, "training"); dt_pack = time.perf_counter() - t
+    nw = os.cpu_count() or 1
+    t = time.perf_counter(); dh.pretokenize(vocab, "training", out_dir=os.path.join(root, "packed_mp"), chunk_lines=256, workers=nw); dt_mp = time.perf_counter() - t
     t = time.perf_counter(); cnt2 = sum(len(y) for _, y in dh.load_packed_generator(packed, 1024, nb_epochs=8)); dt_mm = time.perf_counter() - t
     print(json.dumps({"records": n, "json_generator_pairs_per_s": cnt / dt_json, "pretokenize_pairs_per_s": n / dt_pack,
+                      "pretokenize_%d_workers_pairs_per_s" % nw: n / dt_mp,
                       "packed_generator_pairs_per_s": cnt2 / dt_mm}))

@@ -41,7 +41,7 @@ def test_packed_generator_equals_json_generator(tmp_path, level, n, bs, J, bad_r
     conf = make_corpus(tmp_path, n, J, level, bad_run=bad_run)
     dh = DataHelpers(conf)
     _, vocab = dh.generate_vocabulary_set()
-    packed = dh.pretokenize(vocab, mode="training", chunk_lines=7)
+    packed = dh.pretokenize(vocab, mode="training", chunk_lines=7, workers=3 if level == "word" else 1)
     meta = json.load(open(os.path.join(packed, "meta.json")))
     assert meta["lines"] == n and meta["J"] == J
     ref = list(dh.load_data_generator(vocab, mode="training", batch_size=bs, nb_epochs=1))
