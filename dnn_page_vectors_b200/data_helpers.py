@@ -183,7 +183,12 @@ class DataHelpers(object):
         spec = (J, Lq, Ld, level, ng)
         if workers > 1:
             import multiprocessing as mp
-            pool = mp.get_context("fork").Pool(workers, initializer=_pack_init, initargs=(vocab_index_dict, spec))
+            # fork, not spawn: spawn re-imports the caller's __main__, which a library cannot ask of its callers.  The
+            # workers run only json + NumPy code on their chunk, nothing that needs the parent's threads or CUDA state.
+            import warnings
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore", DeprecationWarning)
+                pool = mp.get_context("fork").Pool(workers, initializer=_pack_init, initargs=(vocab_index_dict, spec))
             results = pool.imap(_pack_chunk, chunks())          # ordered: chunk i's arrays come out i-th
         else:
             pool = None
