@@ -207,8 +207,11 @@ def test_dropout_step_replays_in_the_oracle():
     l, _ = net.train_on_batch(x)
     assert abs(l - ol[0][0]) <= 2e-5 * max(1.0, ol[0][0])
     w = net.get_weights()
-    np.testing.assert_allclose(w["doc"]["E"], od["E"], atol=2e-5)
-    np.testing.assert_allclose(w["query"]["convW0"], oq["convW"][0], atol=2e-5)
+    # one Adam step moves every weight by ~lr * g / (|g| + 3e-7): an element whose gradient is within rounding of zero
+    # can land anywhere inside +-lr, so allow a handful of such elements (any real mask mismatch moves most of them)
+    for got, want in ((w["doc"]["E"], od["E"]), (w["query"]["convW0"], oq["convW"][0])):
+        err = np.abs(got - want)
+        assert (err > 2e-5).mean() < 1e-3 and err.max() < 2.1e-3, ((err > 2e-5).mean(), err.max())
     # evaluation does not drop
     l_eval, _ = net.test_on_batch(x)
     h, _, _, _, _ = O.model_loss_and_grads(x[0].astype(np.int64), np.stack(x[1:], 1).astype(np.int64), oq, od)
