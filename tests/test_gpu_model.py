@@ -68,6 +68,44 @@ def oracle_train(x, pq, pd_, act, steps, masks=None, keep=1.0):
     return losses, pq, pd_
 
 
+
+def decision_flips(tower, b, fw, p, act):
+    """Which pooled columns (window-major, P = |K| F of them) took a different arg-max or ReLU-gate decision on the
+    GPU than in the float64 oracle, and whether any dense-layer gate did.  Every such difference must be a genuine
+    near-tie in the oracle's own numbers (top two accumulators, or a pre-activation, within fp32 noise): anything
+    else is an indexing bug, not rounding."""
+    S = b["S"]
+    am_gpu = b["argmax"].cpu().numpy()
+    pooled_gpu = b["pooled"].cpu().numpy()
+    flagged = np.zeros(tower.P, dtype=bool)
+    X = fw["X"]
+    for i, (W, bias) in enumerate(zip(p["convW"], p["convb"])):
+        k = W.shape[0]
+        T = X.shape[1] - k + 1
+        Y = np.zeros((S, T, tower.F))
+        for j in range(k):
+            Y += X[:, j:j + T, :] @ W[j]
+        sl = slice(i * tower.F, (i + 1) * tower.F)
+        am_o, am_g = fw["argmax"][:, sl], am_gpu[:, sl]
+        live_o, live_g = fw["pooled"][:, sl] > 0, pooled_gpu[:, sl] > 0
+        pre = Y.max(axis=1) + bias[None, :]
+        for s_, f_ in (np.argwhere(live_o != live_g) if act == "relu" else []):     # ReLU gate of the pooled maximum
+            assert abs(pre[s_, f_]) < 1e-5, ("gate flip that is not a near-zero", s_, f_, pre[s_, f_])
+            flagged[i * tower.F + f_] = True
+        both = live_o & live_g if act == "relu" else np.ones_like(live_o)
+        for s_, f_ in np.argwhere((am_o != am_g) & both):
+            assert abs(Y[s_, am_o[s_, f_], f_] - Y[s_, am_g[s_, f_], f_]) < 1e-5, ("arg-max differs without a near-tie", s_, f_)
+            flagged[i * tower.F + f_] = True
+    pre_d = fw["pooled"] @ p["Wd"] + p["bd"][None, :]
+    sem_gpu = b["sem"].cpu().numpy()
+    dense_flip = False
+    if act == "relu":
+        for s_, h_ in np.argwhere((fw["sem"] > 0) != (sem_gpu > 0)):
+            assert abs(pre_d[s_, h_]) < 1e-5, ("dense gate flip that is not a near-zero", s_, h_)
+            dense_flip = True
+    return flagged, dense_flip
+
+
 CFG_SMALL = dict(B=16, J=3, Lq=8, Ld=30, V=200, D=100, windows=(3, 4), F=150, H=150)     # reference literals, short
 CFG_ONE = dict(B=32, J=4, Lq=20, Ld=100, V=500, D=300, windows=(3,), F=300, H=128)        # BASELINE cfg1 shape, B cut
 
@@ -83,33 +121,50 @@ def test_fp32_training_trajectory_matches_oracle(cfg, act):
     l0, a0 = net.test_on_batch(x)
     assert abs(l0 - ol[0][0]) <= 1e-5 * max(1.0, abs(ol[0][0])) and abs(a0 - ol[0][1]) < 1e-6
     q64, d64 = x[0].astype(np.int64), np.stack(x[1:], axis=1).astype(np.int64)
-    _, ogq, ogd, _, _ = O.model_loss_and_grads(q64, d64, pq, pd_, act=act)
+    _, ogq, ogd, ofq, ofd = O.model_loss_and_grads(q64, d64, pq, pd_, act=act)
     for t in range(steps):
         l, a = net.train_on_batch(x, np.ones(cfg["B"]))
         assert abs(l - ol[t][0]) <= 2e-5 * max(1.0, abs(ol[t][0])), (t, l, ol[t])
         if t == 0:
-            # gradients of the first step, tensor by tensor.  One arg-max or ReLU-gate decision that
-            # falls the other way in fp32 changes a whole filter's column, so compare per filter and
-            # allow 1 % of filters to differ; everything else must agree to 1e-4 of the tensor's scale.
-            for tower, og in ((net.query_model, ogq), (net.doc_model, ogd)):
-                def close(got, want, axis_filter=-1):
+            # Gradients of the first step, tensor by tensor, to 1e-4 of the tensor's scale.  One arg-max or ReLU-gate
+            # decision that falls the other way in fp32 changes a whole filter's column; decision_flips() finds those
+            # columns by comparing the GPU's decisions with the oracle's and insists that each one IS a near-tie.
+            # Every other filter must agree with no exceptions -- so a 1-in-100 indexing bug in dW/dX cannot hide
+            # inside a tolerance fraction.
+            for tower, og, fw, op in ((net.query_model, ogq, ofq, pq), (net.doc_model, ogd, ofd, pd_)):
+                b = tower.buffers(cfg["B"] if tower is net.query_model else cfg["B"] * (1 + cfg["J"]), True)
+                flagged, dense_flip = decision_flips(tower, b, fw, op, act)
+                assert flagged.mean() <= 0.01, flagged.mean()
+
+                def close(got, want, cols=None):
+                    """cols: for each index of the last axis, True if that column may differ (a flagged filter)"""
                     got, want = np.asarray(got, dtype=np.float64), np.asarray(want)
                     scale = np.abs(want).max() + 1e-30
                     bad = np.abs(got - want) > 1e-4 * scale
-                    per_filter = bad.reshape(-1, bad.shape[axis_filter]).any(axis=0) if bad.ndim > 1 else bad
-                    assert per_filter.mean() <= 0.01, per_filter.mean()
-                close(tower.g_Wd.cpu().numpy(), og["Wd"])
+                    per_col = bad.reshape(-1, bad.shape[-1]).any(axis=0) if bad.ndim > 1 else bad
+                    if dense_flip:                       # a dense gate flip perturbs G of its whole sequence
+                        assert per_col.mean() <= 0.01, per_col.mean()
+                    elif cols is None:
+                        assert not per_col.any(), (per_col.mean(), np.abs(got - want).max() / scale)
+                    else:
+                        assert not (per_col & ~cols).any(), ((per_col & ~cols).sum(), np.abs(got - want).max() / scale)
+                F_ = tower.F
+                close(tower.g_Wd.cpu().numpy().T, og["Wd"].T, flagged)            # (H, P): pooled column last
                 close(tower.g_bd.cpu().numpy(), og["bd"])
                 for i in range(len(tower.windows)):
-                    close(tower.g_convW[i].cpu().numpy(), og["convW"][i])
-                    close(tower.g_convb[i * tower.F:(i + 1) * tower.F].cpu().numpy(), og["convb"][i])
-                b = tower.buffers(cfg["B"] if tower is net.query_model else cfg["B"] * (1 + cfg["J"]), True)
+                    close(tower.g_convW[i].cpu().numpy(), og["convW"][i], flagged[i * F_:(i + 1) * F_])
+                    close(tower.g_convb[i * F_:(i + 1) * F_].cpu().numpy(), og["convb"][i], flagged[i * F_:(i + 1) * F_])
                 n_u = int(b["n_uniq"].item())
                 ids = b["uniq"][:n_u].cpu().numpy()
                 rows = b["dE_rows"][:n_u, :tower.D].cpu().numpy().astype(np.float64)
                 want = og["E"][ids]
                 scale = np.abs(want).max()
-                assert (np.abs(rows - want) > 1e-4 * scale).any(axis=1).mean() <= 0.02
+                bad_rows = (np.abs(rows - want) > 1e-4 * scale).any(axis=1)
+                if flagged.any() or dense_flip:           # a flipped decision moves gradient between token rows
+                    assert bad_rows.mean() <= 0.02
+                else:
+                    assert not bad_rows.any()
+                np.testing.assert_array_equal(ids, np.unique(q64 if tower is net.query_model else d64))
                 assert np.abs(np.delete(og["E"], ids, axis=0)).max() == 0.0
     w = net.get_weights()
     for tag, op in (("query", oq), ("doc", od)):
@@ -173,21 +228,95 @@ def test_config_shapes_first_step_matches_oracle(cfg, precision):
         assert np.abs(np.delete(og["E"], ids, axis=0)).max() == 0.0
 
 
-def test_bf16_forward_and_loss_within_tolerance():
-    cfg = CFG_ONE
-    net, pq, pd_ = build("bf16", "relu", conv_impl="simt", **cfg)
-    x = synth(2, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"])
-    ol, _, _ = oracle_train(x, pq, pd_, "relu", 2)
-    l0, _ = net.test_on_batch(x)
-    assert abs(l0 - ol[0][0]) <= 2e-2 * max(1.0, abs(ol[0][0]))
-    l1, _ = net.train_on_batch(x)
-    l2, _ = net.train_on_batch(x)
-    assert abs(l1 - ol[0][0]) <= 2e-2 * max(1.0, abs(ol[0][0]))
-    assert abs(l2 - ol[1][0]) <= 2e-2 * max(1.0, abs(ol[1][0]))
-    # page vectors and cosines
+def round_compute_copies(p):
+    """The bf16 mode computes on bf16 copies of the table and the conv kernels (fp32 masters stay exact): the oracle
+    gets the same operands."""
+    q = dict(p)
+    q["E"] = bf16_round(p["E"]).astype(np.float64)
+    q["convW"] = [bf16_round(W).astype(np.float64) for W in p["convW"]]
+    return q
+
+
+def oracle_train_bf16(x, pq, pd_, act, steps):
+    """oracle_train with the library's mixed-precision scheme: gradients are taken at the bf16-rounded compute
+    copies, Adam moves the full-precision masters."""
+    pq, pd_ = copy.deepcopy(pq), copy.deepcopy(pd_)
     q = x[0].astype(np.int64)
-    fq = O.tower_fwd(q, pq, "relu")
-    np.testing.assert_allclose(net.get_weights()["query"]["E"].shape, pq["E"].shape)
+    d = np.stack(x[1:], axis=1).astype(np.int64)
+    st, out = {}, []
+    for t in range(1, steps + 1):
+        head, gq, gd, fq, fd = O.model_loss_and_grads(q, d, round_compute_copies(pq), round_compute_copies(pd_), act=act)
+        out.append((head, fq, fd))
+        for tag, p, g in (("q", pq, gq), ("d", pd_, gd)):
+            for (name, arr), (_, grad) in zip(O.flat_params(p), O.flat_grads(g)):
+                m, v = st.setdefault((tag, name), (np.zeros_like(arr), np.zeros_like(arr)))
+                O.adam_step(arr, m, v, grad, t)
+    return out, pq, pd_
+
+
+@pytest.mark.parametrize("cfg", [CFG_ONE, CFG_SMALL], ids=["cfg1", "ref-literal"])
+def test_bf16_tensor_core_path_vectors_cosines_loss_and_trajectory(cfg):
+    """The production path -- bf16 operands, tcgen05 forward and backward, TF32 dense (conv_impl='auto', what
+    bench.py runs) -- against the oracle at north_star's bf16 tolerance of 2e-2 on semantic VECTORS, COSINES and
+    LOSS, over a 3-step training trajectory."""
+    net, pq, pd_ = build("bf16", "relu", conv_impl="auto", **cfg)
+    B, J = cfg["B"], cfg["J"]
+    x = synth(2, B, J, cfg["Lq"], cfg["Ld"], cfg["V"])
+    steps = 3
+    ref, oq, od = oracle_train_bf16(x, pq, pd_, "relu", steps)
+    tol = 2e-2
+    for t in range(steps):
+        head, fq, fd = ref[t]
+        # evaluation forward on the current weights: vectors, cosines, probabilities, loss
+        l_eval, a_eval = net.test_on_batch(x)
+        bq, bd = net.query_model.buffers(B, False), net.doc_model.buffers(B * (1 + J), False)
+        for got, want in ((bq["sem"], fq["sem"]), (bd["sem"], fd["sem"])):
+            got = got.cpu().numpy().astype(np.float64)
+            assert np.abs(got - want).max() <= tol * np.abs(want).max(), (t, np.abs(got - want).max(), np.abs(want).max())
+        h = net._head_bufs(B)
+        assert np.abs(h["cos"].cpu().numpy() - head["cos"]).max() <= tol
+        assert np.abs(h["prob"].cpu().numpy() - head["prob"]).max() <= tol
+        assert abs(l_eval - head["loss"]) <= tol * max(1.0, abs(head["loss"]))
+        l, a = net.train_on_batch(x)
+        assert abs(l - head["loss"]) <= tol * max(1.0, abs(head["loss"])), (t, l, head["loss"])
+    # Adam normalises every step to ~lr, so after 3 steps the weights agree closely wherever the gradient's sign is
+    # not within rounding of zero; the bulk must sit within 1e-4 of the oracle's masters
+    w = net.get_weights()
+    for tag, op in (("query", oq), ("doc", od)):
+        for got, want in ((w[tag]["Wd"], op["Wd"]), (w[tag]["convW0"], op["convW"][0]), (w[tag]["E"], op["E"])):
+            err = np.abs(got - want)
+            assert err.max() < 7e-3 and (err > 1e-4).mean() < 5e-2, (tag, err.max(), (err > 1e-4).mean())
+
+
+@pytest.mark.parametrize("H", [128, 150])
+def test_bf16_encode_pages_and_topk_against_oracle(H):
+    """encode_pages(dtype=bfloat16) -> topk, the retrieval path INTEGRATION.md presents as production: page vectors
+    within 2e-2 of the oracle's; the scan's ids EXACTLY those of the oracle run on the same bf16 vectors, up to swaps
+    of candidates whose float64 scores differ by less than fp32 accumulation noise.  H = 128 scans on the tensor
+    cores; H = 150 (the reference's own hidden_dims, cnn_dssm_tf.py:38) is not a width that kernel takes and must
+    still work (fp32 scan of the same vectors)."""
+    cfg = dict(CFG_ONE, H=H)
+    net, pq, pd_ = build("bf16", "relu", conv_impl="auto", **cfg)
+    rng = np.random.RandomState(11)
+    pages = synth(5, 700, 0, cfg["Lq"], cfg["Ld"], cfg["V"])[1]
+    queries = synth(6, 40, 0, cfg["Lq"], cfg["Ld"], cfg["V"])[0]
+    vec = net.encode_pages(pages, batch_size=256, dtype=torch.bfloat16)
+    qv = net.encode_queries(queries, dtype=torch.bfloat16)
+    assert vec.dtype == torch.bfloat16 and vec.shape == (700, H)
+    ovec = O.normalise_rows(O.tower_fwd(pages.astype(np.int64), round_compute_copies(pd_), "relu")["sem"])
+    oq = O.normalise_rows(O.tower_fwd(queries.astype(np.int64), round_compute_copies(pq), "relu")["sem"])
+    v, q = vec.float().cpu().numpy().astype(np.float64), qv.float().cpu().numpy().astype(np.float64)
+    assert np.abs(v - ovec).max() <= 2e-2 and np.abs(q - oq).max() <= 2e-2
+    k = 10
+    sc, ids = net.topk(qv, vec, k=k, id_base=5)
+    osc, oid = O.cos_topk(q, v, k, id_base=5)                 # oracle on the very vectors the scan read
+    got_s, got_i = sc.cpu().numpy(), ids.cpu().numpy()
+    np.testing.assert_allclose(got_s, osc, rtol=2e-5, atol=2e-6)
+    for r, j in np.argwhere(got_i != oid):                       # only near-ties may swap
+        assert abs(got_s[r, j] - osc[r, j]) < 1e-5
+    # and end to end against the oracle's own vectors: cosines within 2e-2, so the best page's score is too
+    osc2, _ = O.cos_topk(oq, ovec, k)
+    assert np.abs(got_s[:, 0] - osc2[:, 0]).max() <= 2e-2
 
 
 def test_dropout_step_replays_in_the_oracle():
