@@ -221,8 +221,30 @@ __global__ void topk_decode_kernel(const u64* __restrict__ keys, int64_t n, int6
   id[i] = id_base + static_cast<int64_t>(0xFFFFFFFFu - static_cast<uint32_t>(key & 0xFFFFFFFFull));
 }
 
+// Merge keys carry 32 bits of id, the lists carry int64 ids (shard row + id_base, and id_base is unrestricted):
+// keys hold id - lo, lo = the smallest valid id of the call (found by the pass below), and the decode adds lo back.
+// ctl[0] = lo (starts at ~0), ctl[1] = 1 if some id lies 2^32 - 1 or more above lo (the call then reports failure
+// in its outputs, see clsm_b200.h).
+__global__ void __launch_bounds__(256)
+topk_min_id_kernel(const int64_t* __restrict__ id, int64_t n, u64* __restrict__ ctl) {
+  __shared__ u64 s_min[8];
+  u64 m = ~0ull;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t v = id[i];
+    if (v >= 0 && static_cast<u64>(v) < m) m = static_cast<u64>(v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { const u64 n2 = __shfl_xor_sync(0xffffffffu, m, o); m = n2 < m ? n2 : m; }
+  if ((threadIdx.x & 31) == 0) s_min[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) m = s_min[w] < m ? s_min[w] : m;
+    if (m != ~0ull) atomicMin(ctl, m);
+  }
+}
+
 __global__ void topk_encode_kernel(const float* __restrict__ score, const int64_t* __restrict__ id,
-                                   int n_parts, int64_t nQ, int k, u64* __restrict__ keys) {
+                                   int n_parts, int64_t nQ, int k, u64* __restrict__ keys, u64* __restrict__ ctl) {
   const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const int64_t n = static_cast<int64_t>(n_parts) * nQ * k;
   if (i >= n) return;
@@ -231,8 +253,24 @@ __global__ void topk_encode_kernel(const float* __restrict__ score, const int64_
   const int64_t q = rem / k;
   const int j = static_cast<int>(rem - q * k);
   const int64_t idv = id[i];
-  keys[q * (static_cast<int64_t>(n_parts) * k) + part * k + j] =
-      idv < 0 ? 0ull : make_key(score[i], static_cast<uint32_t>(idv));
+  u64 key = 0ull;
+  if (idv >= 0) {
+    const u64 rel = static_cast<u64>(idv) - ctl[0];
+    if (rel >= 0xFFFFFFFFull) ctl[1] = 1ull;                    // benign race: every writer stores the same value
+    else key = make_key(score[i], static_cast<uint32_t>(rel));
+  }
+  keys[q * (static_cast<int64_t>(n_parts) * k) + part * k + j] = key;
+}
+
+__global__ void topk_decode_merge_kernel(const u64* __restrict__ keys, int64_t n, const u64* __restrict__ ctl,
+                                         float* __restrict__ score, int64_t* __restrict__ id) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (ctl[1] != 0ull) { score[i] = __uint_as_float(0x7fc00000u); id[i] = -2; return; }      // id span too wide: refuse loudly
+  const u64 key = keys[i];
+  if (key == 0) { score[i] = -INFINITY; id[i] = -1; return; }
+  score[i] = ordered_to_f32(static_cast<uint32_t>(key >> 32));
+  id[i] = static_cast<int64_t>(ctl[0]) + static_cast<int64_t>(0xFFFFFFFFu - static_cast<uint32_t>(key & 0xFFFFFFFFull));
 }
 
 // runs merge levels on keys (nQ, n_in) in buf[src] until one list of k per query is left;
@@ -291,7 +329,7 @@ int clsm_cos_topk(const float* Qn, int64_t nQ, const float* Cn, int64_t N, int H
 
 size_t clsm_topk_merge_workspace_bytes(int n_parts, int64_t nQ, int k) {
   const int64_t c1 = ceil_div64(static_cast<int64_t>(n_parts) * k, R);
-  return level_bytes(nQ, n_parts, k) + level_bytes(nQ, c1 > 1 ? c1 : 1, k);
+  return level_bytes(nQ, n_parts, k) + level_bytes(nQ, c1 > 1 ? c1 : 1, k) + 256 /* id base + range flag */;
 }
 
 int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_t nQ, int k,
@@ -302,16 +340,23 @@ int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_
     return CLSM_EWORKSPACE;
   }
   cudaStream_t st = as_stream(stream);
+  const int64_t c1 = ceil_div64(static_cast<int64_t>(n_parts) * k, R);
   u64* buf[2];
   buf[0] = static_cast<u64*>(ws);
   buf[1] = reinterpret_cast<u64*>(static_cast<char*>(ws) + level_bytes(nQ, n_parts, k));
+  u64* ctl = reinterpret_cast<u64*>(static_cast<char*>(ws) + level_bytes(nQ, n_parts, k) + level_bytes(nQ, c1 > 1 ? c1 : 1, k));
   const int64_t n_in = static_cast<int64_t>(n_parts) * nQ * k;
-  topk_encode_kernel<<<static_cast<unsigned>(ceil_div64(n_in, 256)), 256, 0, st>>>(scores, ids, n_parts, nQ, k, buf[0]);
+  CLSM_CUDA(cudaMemsetAsync(ctl, 0xFF, 8, st));
+  CLSM_CUDA(cudaMemsetAsync(ctl + 1, 0, 8, st));
+  const int64_t min_blocks = ceil_div64(n_in, 256);
+  topk_min_id_kernel<<<static_cast<unsigned>(min_blocks < 1024 ? min_blocks : 1024), 256, 0, st>>>(ids, n_in, ctl);
+  CLSM_LAUNCH_CHECK();
+  topk_encode_kernel<<<static_cast<unsigned>(ceil_div64(n_in, 256)), 256, 0, st>>>(scores, ids, n_parts, nQ, k, buf[0], ctl);
   CLSM_LAUNCH_CHECK();
   const int src = run_merge_levels(buf, 0, nQ, static_cast<int64_t>(n_parts) * k, k, st);
   CLSM_LAUNCH_CHECK();
   const int64_t n = nQ * k;
-  topk_decode_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(buf[src], n, 0, out_score, out_id);
+  topk_decode_merge_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(buf[src], n, ctl, out_score, out_id);
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
 }
@@ -530,9 +575,9 @@ int clsm_topk_merge_static(const float* scores, const int64_t* ids, int n_parts,
   void* scratch = nullptr;
   const int rc = topk_merge_static_setup(&scratch);
   if (rc != CLSM_OK) return rc;
-  // Every byte the merge kernels read from the scratch is written earlier in the same call (the key
-  // encoding pass fills level 0 completely, each level fills the next), so nothing has to start at zero
-  // even though the array still holds the previous call's keys.
+  // Every byte the merge kernels read from the scratch is written earlier in the same call (the two control
+  // words are re-initialised first, the key encoding pass fills level 0 completely, each level fills the next),
+  // so the previous call's contents never matter.
   return clsm_topk_merge(scores, ids, n_parts, nQ, k, out_score, out_id, scratch,
                          static_cast<size_t>(CLSM_TOPK_MERGE_STATIC_MAX_BYTES), stream);
 }

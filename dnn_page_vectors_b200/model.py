@@ -314,6 +314,9 @@ class CLSM(object):
         self.iterations = 0
         self.compiled = False
         self.dp = None                 # set by parallel.DataParallel
+        import os
+        self.overlap = os.environ.get("CLSM_OVERLAP", "1") != "0"      # two-stream step, see step_resident
+        self._side = None
         self._head = {}
         self._pinned = {}
 
@@ -395,20 +398,41 @@ class CLSM(object):
 
     # ---- device-resident step (bench `value`): tokens already staged in the tower buffers
     def step_resident(self, B, bq, bd):
+        """One training step.  After the loss kernel the two towers are independent: the query tower's backward,
+        scatter and table Adam (HBM-bound: a 1.2 GB table and its Adam state) run on a second stream underneath the
+        document tower's tensor-bound conv gradients, and the streams join before the step returns.  Every kernel is
+        deterministic and the towers share no buffer, so the weights are bit-identical to the one-stream order
+        (CLSM_OVERLAP=0 selects it; tests/test_gpu_model.py compares the two)."""
         sq, sd = self._seeds()
         self.query_model.forward(bq, True, sq)
         self.doc_model.forward(bd, True, sd)
         bt = B * (self.dp.world if self.dp is not None else 1)
         h = self._forward_head(B, bq, bd, True, bt)
-        self.query_model.backward(bq)
-        self.doc_model.backward(bd)
         self.iterations += 1
         if self.dp is not None:
+            self.query_model.backward(bq)
+            self.doc_model.backward(bd)
             gq, gd = self.dp.exchange(self, bq, bd)
             self.query_model.adam(bq, self.iterations, gq)
             self.doc_model.adam(bd, self.iterations, gd)
             self.dp.after_adam(self)
+        elif self.overlap:
+            main = torch.cuda.current_stream()
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=self.device)
+                self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
+            self._ev_fork.record(main)
+            self._side.wait_event(self._ev_fork)
+            with torch.cuda.stream(self._side):
+                self.query_model.backward(bq)
+                self.query_model.adam(bq, self.iterations)
+                self._ev_join.record(self._side)
+            self.doc_model.backward(bd)
+            self.doc_model.adam(bd, self.iterations)
+            main.wait_event(self._ev_join)
         else:
+            self.query_model.backward(bq)
+            self.doc_model.backward(bd)
             self.query_model.adam(bq, self.iterations)
             self.doc_model.adam(bd, self.iterations)
         return h
@@ -516,7 +540,7 @@ class CLSM(object):
         Q, H = query_vecs.shape
         N = corpus_vecs.shape[0]
         k = int(k)
-        if corpus_vecs.dtype == torch.bfloat16:
+        if corpus_vecs.dtype == torch.bfloat16 and H in (64, 128):
             # tensor-core scan of a bf16 corpus (queries are rounded to bf16 too)
             qv = query_vecs if query_vecs.dtype == torch.bfloat16 else query_vecs.to(torch.bfloat16)
             qv = qv.contiguous()
@@ -527,6 +551,17 @@ class CLSM(object):
             call("clsm_cos_topk_bf16", _ptr(qv), Q, _ptr(corpus_vecs), N, H, k, int(id_base), _ptr(sc), _ptr(ids),
                  _ptr(ws), ws_bytes, _stream())
             return sc, ids
+        if corpus_vecs.dtype == torch.bfloat16:
+            # a width the tensor-core scan does not take (it wants H = 64 or 128; the reference's own hidden_dims is
+            # 150, cnn_dssm_tf.py:38): the exact fp32 scan over fp32 views of the SAME bf16 vectors, one bounded slice
+            # of the corpus at a time, merged in (score desc, id asc) order -- same answer, CUDA-core speed.
+            qf = query_vecs.to(torch.bfloat16).float().contiguous()
+            step = 1 << 20
+            if N <= step:
+                return self.topk(qf, corpus_vecs.float(), k=k, id_base=id_base)
+            parts = [self.topk(qf, corpus_vecs[s:s + step].float(), k=k, id_base=id_base + s) for s in range(0, N, step)]
+            return self.topk_merge(torch.stack([p_[0] for p_ in parts]), torch.stack([p_[1] for p_ in parts]))
+        query_vecs = query_vecs.float().contiguous()
         ws_bytes = lib.clsm_cos_topk_workspace_bytes(Q, N, k)
         ws = self._scratch("topk", ws_bytes)
         sc = torch.empty((Q, k), dtype=torch.float32, device=self.device)

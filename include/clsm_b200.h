@@ -188,7 +188,10 @@ int clsm_adam_table_dp(float* p, float* m, float* v, int64_t n_rows, int D, int 
  * clsm_normalize_rows: vec (N, H) = sem / sqrt(max(|sem|^2, FLT_MIN))   (RTF's norm, :63-72)
  * clsm_cos_topk: scores = Qn . Cn^T over corpus rows [0, N), top-k per query ordered by
  *   (score desc, id asc); ids are id_base + row.  out_score (nQ, k) fp32, out_id (nQ, k) int64.
- * clsm_topk_merge: merge n_parts lists (n_parts, nQ, k) -> (nQ, k), same order. */
+ * clsm_topk_merge: merge n_parts lists (n_parts, nQ, k) -> (nQ, k), same order.  ids are int64; any negative id
+ *   marks an empty slot.  The valid ids of ONE call must span less than 2^32 - 1 (max - min): the merge keys carry
+ *   32 bits of id relative to the smallest one.  A wider span cannot be merged exactly; the call then fills
+ *   out_id with -2 and out_score with NaN instead of returning truncated ids. */
 int clsm_normalize_rows(const float* sem, int64_t N, int H, float* vec, void* stream);
 size_t clsm_cos_topk_workspace_bytes(int64_t nQ, int64_t N, int k);
 int clsm_cos_topk(const float* Qn, int64_t nQ, const float* Cn, int64_t N, int H, int k,

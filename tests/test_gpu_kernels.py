@@ -489,6 +489,34 @@ def test_topk_merge_equals_single_pass():
     assert torch.equal(mi, full_i) and torch.equal(ms, full_s)     # independent of the sharding
 
 
+def test_topk_merge_ids_beyond_32_bits_and_span_check():
+    """Merged ids are int64: shards of a corpus whose ids start past 2^32 merge exactly (keys hold id - smallest id);
+    a call whose ids span 2^32 - 1 or more cannot be merged exactly and says so in its outputs."""
+    rng = np.random.RandomState(15)
+    parts, Q, k = 3, 5, 20
+    base = 6_000_000_000
+    sc = np.sort(rng.rand(parts, Q, k).astype(np.float32), axis=2)[:, :, ::-1].copy()
+    sc[1, 2, :4] = sc[0, 2, :4]                                   # cross-shard score ties -> lowest id first
+    ids = np.stack([np.stack([np.sort(rng.choice(1000, size=k, replace=False)) for _ in range(Q)]) + base + p_ * 1000
+                    for p_ in range(parts)])
+    ids[2, 0, -3:] = -1; sc[2, 0, -3:] = -np.inf                  # short list
+    S_, I_ = dev(sc), dev(ids.astype(np.int64))
+    wsb = lib.clsm_topk_merge_workspace_bytes(parts, Q, k)
+    ws = torch.full((wsb,), 0xA5, dtype=torch.uint8, device=DEV)
+    ms = torch.empty((Q, k), dtype=torch.float32, device=DEV)
+    mi = torch.empty((Q, k), dtype=torch.int64, device=DEV)
+    call("clsm_topk_merge", P(S_), P(I_), parts, Q, k, P(ms), P(mi), P(ws), wsb, ST())
+    for q in range(Q):
+        valid = [(s, i) for s, i in zip(sc[:, q].ravel(), ids[:, q].ravel()) if i >= 0]
+        want = sorted(valid, key=lambda t: (-t[0], t[1]))[:k]
+        np.testing.assert_array_equal(mi[q].cpu().numpy(), [w[1] for w in want])
+        np.testing.assert_array_equal(ms[q].cpu().numpy(), np.array([w[0] for w in want], dtype=np.float32))
+    ids[0, 0, 0] = 5                                              # 6e9 below the others: the span is not representable
+    I2 = dev(ids.astype(np.int64))
+    call("clsm_topk_merge", P(S_), P(I2), parts, Q, k, P(ms), P(mi), P(ws), wsb, ST())
+    assert (mi.cpu().numpy() == -2).all() and np.isnan(ms.cpu().numpy()).all()
+
+
 def test_normalize_rows():
     rng = np.random.RandomState(12)
     z = np.maximum(rng.randn(100, 128), 0).astype(np.float32); z[3] = 0

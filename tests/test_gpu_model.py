@@ -446,3 +446,26 @@ def test_pinned_tensor_batches_equal_numpy_batches():
     assert net_a.test_on_batch(x) == net_b.test_on_batch([t.to(DEV) for t in xt])
     with pytest.raises(ValueError):
         net_b.train_on_batch([t.long() for t in xt])
+
+
+def test_two_stream_step_is_bit_identical_to_one_stream():
+    """step_resident runs the query tower's backward / scatter / Adam on a second stream under the document tower's
+    conv gradients.  Every kernel is deterministic and the towers share no buffer, so three steps (dropout on, bf16
+    tensor-core path) must leave exactly the same weights, optimizer state and losses as the one-stream order."""
+    cfg = dict(CFG_ONE, B=64, V=3000)
+    x = synth(12, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"])
+    runs = []
+    for overlap in (True, False):
+        net, _, _ = build("bf16", "relu", dropout=0.25, conv_impl="auto", **cfg)
+        net.overlap = overlap
+        losses = [net.train_on_batch(x) for _ in range(3)]
+        torch.cuda.synchronize()
+        runs.append((losses, {k: v.clone() for k, v in net.query_model.state().items()},
+                     {k: v.clone() for k, v in net.doc_model.state().items()},
+                     net.query_model.E_c.clone(), net.doc_model.E_c.clone()))
+    a, b_ = runs
+    assert a[0] == b_[0]
+    for i in (1, 2):
+        for k in a[i]:
+            assert torch.equal(a[i][k], b_[i][k]), k
+    assert torch.equal(a[3], b_[3]) and torch.equal(a[4], b_[4])
