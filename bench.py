@@ -5,10 +5,18 @@ batch 4096 per GPU, 1M-word embedding table, dense Keras Adam.  One pair = 1 que
 J negatives through forward, loss, backward and the optimizer step.
 
   python bench.py [--gpus N --steps K --warmup W]          our arm (one process per GPU under torchrun)
-  python bench.py --impl reference [...]                   CPU arm: torch-CPU port of the reference graph
+  python bench.py --impl reference [...]                   CPU arm: torch-CPU port of the reference graph,
+                                                           SAME batch, shapes and token stream as our arm
 
-Prints ONE JSON line (rank 0).  Extra keys beyond the contract: roofline, cpu_baseline, kernels
-(per-phase device times of one instrumented step), encode / topk (page-encode and retrieval rates).
+Prints ONE JSON line (rank 0).  Extra keys beyond the contract:
+  step_ms          per-step device times of the timed region (median, p90, min, max)
+  kernels          device time of every C-ABI call class in an instrumented one-stream step (median of 3)
+  roofline(_all)   per-kernel achieved / peak, each launch timed directly with CUDA events (clsm_conv_pool_bwd is
+                   split into its dW and dX kernels by two events recorded INSIDE the call); `traffic` comes from
+                   the ncu capture summarised in profiles/r02_ncu_traffic.json
+  other_configs    BASELINE configs[2] (J=50, 1000-token pages) and configs[3] (windows 1/2/3/5, batch 8192) on one GPU
+  sharded          configs[4] at this N: page encoding over a row shard per GPU, per-GPU top-100 + allgather + merge
+  cpu_baseline     the CPU port on the host cores (N = 1 only)
 """
 from __future__ import annotations
 
@@ -18,7 +26,6 @@ import os
 import subprocess
 import sys
 import threading
-import time
 
 import numpy as np
 
@@ -29,9 +36,13 @@ sys.path.insert(0, ROOT)
 # but tanh + the reference's cosine clip to [0, 1] (cnn_dssm_tf.py:75-76) dies after one Adam step on random
 # init: every cosine goes negative, is clipped, and all gradients are zero from then on (measured).
 # A dead backward would be skipped work, so the benchmark trains the reference's ReLU model.
+CFG1 = dict(V=50_000, D=300, windows=(3,), F=300, H=128, J=4, Lq=20, Ld=100, B=128, act="relu")
 CFG2 = dict(V=1_000_000, D=300, windows=(3,), F=300, H=128, J=4, Lq=20, Ld=100, B=4096, act="relu")
-DW_SHARE = 0.49        # dw2_tc : (dw2_tc + dx2_tc) device-time ratio from the ncu launch list under profiles/
+CFG3 = dict(V=1_000_000, D=300, windows=(3,), F=300, H=128, J=50, Lq=20, Ld=1000, B=256, act="relu")
+CFG4 = dict(V=1_000_000, D=300, windows=(1, 2, 3, 5), F=300, H=128, J=4, Lq=20, Ld=100, B=8192, act="relu")
 WORKLOAD = "cfg2: CLSM bf16 train step, B=4096/GPU, J=4, Lq=20, Ld=100, D=300, window 3, F=300, H=128, V=1M, dense Adam"
+SHARD_PAGES = 2_500_000          # configs[4]: 20 M pages over 8 GPUs
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")
 
 
 def peaks():
@@ -39,14 +50,18 @@ def peaks():
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
             p = json.load(f)
         return {"hbm": p["hbm_gbs"], "tf_burst": p["bf16_tflops"], "tf_sust": p.get("bf16_tflops_sustained", p["bf16_tflops"]),
-                "src": "measured"}
+                "src": "measured (MEASURED_PEAKS.json)"}
     except Exception:
-        return {"hbm": 6650.0, "tf_burst": 1590.0, "tf_sust": 1400.0, "src": "fallback"}
+        return {"hbm": 6650.0, "tf_burst": 1590.0, "tf_sust": 1400.0, "src": "fallback (B200_PROFILING.md)"}
+
+
+def conv_flops_seq(c, L):
+    return sum(2 * (L - k + 1) * k * c["D"] * c["F"] for k in c["windows"])
 
 
 def flops_pair_fwd(c):
     def seq(L):
-        return sum(2 * (L - k + 1) * k * c["D"] * c["F"] for k in c["windows"]) + 2 * len(c["windows"]) * c["F"] * c["H"]
+        return conv_flops_seq(c, L) + 2 * len(c["windows"]) * c["F"] * c["H"]
     return seq(c["Lq"]) + (1 + c["J"]) * seq(c["Ld"])
 
 
@@ -128,60 +143,39 @@ class ClockSampler(object):
 
 # ------------------------------------------------------------------------------ reference arm
 def run_reference(args, rank, world):
+    """The reference graph (dssm_cnn_v2/cnn_dssm_tf.py:63-182) on the host cores: oracle/torch_cpu_port.py, all
+    threads, on the SAME workload as our arm -- cfg2 shapes, batch --batch (4096) per step, the same Zipf token
+    stream, --steps / --warmup honoured.  pairs/s is not batch invariant (every step carries a dense Adam over two
+    1M x 300 tables), which is why the batch must match.  A wall-clock budget (--ref-budget-s) bounds the run: when it
+    cuts the timed steps short the line says so in `steps` / `requested_steps`."""
     if rank != 0:
         return 0
     from oracle import torch_cpu_port as CP
-    c = dict(CFG2)
-    Bs = 64                                   # bounded sample of the cfg2 workload per step
-    steps, warmup = max(args.steps, 1), max(args.warmup, 1)
-    steps = min(steps, 5)
-    pps, threads, dt = CP.time_train(c, Bs, steps, min(warmup, 2))
+    c = dict(CFG2, B=args.batch, V=args.vocab)
+    steps, warmup = max(args.steps, 1), max(args.warmup, 0)
+    batches = make_batches(c, 4, 1337)
+    pps, threads, dt, done = CP.time_train(c, c["B"], steps, warmup, batches=batches, budget_s=args.ref_budget_s)
+    sample = "torch-CPU fp32 port of the reference graph, cfg2 shapes, B=%d per step, Zipf token stream of the GPU arm, %d timed steps" % (c["B"], done)
     line = {
         "impl": "reference", "metric": "train_pairs_per_s", "value": pps, "unit": "pairs/s", "n_gpus": args.gpus,
-        "steps": steps, "warmup": min(warmup, 2), "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "steps": done, "requested_steps": steps, "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": "batch %d per step (same shapes, uniform ids)" % Bs},
-        "cpu_baseline": {"value": pps, "unit": "pairs/s", "cores": threads, "kind": "port",
-                         "sample": "torch-CPU fp32 port of the reference graph, B=%d per step, %d steps" % (Bs, steps)},
+        "config": {"workload": WORKLOAD, "global_batch": c["B"], "activation": c["act"],
+                   "tokens": "Zipf(1.07) ids (frequency rank -> id by a fixed random permutation), true length U[L/4,L], right-padded with one PAD id",
+                   "sample": sample},
+        "cpu_baseline": {"value": pps, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": pps, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference stack (Keras 1.0.x / Theano 0.8 / TF 0.x, Python 2) not installable here; oracle port timed",
     }
+    if done < steps:
+        line["note"] += "; timed steps cut from %d to %d by the %.0f s budget" % (steps, done, args.ref_budget_s)
     emit(line)
     return 0
 
 
 # ------------------------------------------------------------------------------ our arm
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=CFG2["B"])
-    ap.add_argument("--vocab", type=int, default=CFG2["V"])
-    ap.add_argument("--conv-impl", default="auto")
-    ap.add_argument("--lazy-adam", action="store_true", help="row-sparse table Adam (NOT the reference's semantics)")
-    ap.add_argument("--no-extras", action="store_true", help="skip cpu_baseline / encode / topk / breakdown")
-    ap.add_argument("--dp-profile", action="store_true", help="N>1: device time of exchange / Adam / allgather per step, to stderr")
-    args = ap.parse_args()
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.impl == "reference":
-        return run_reference(args, rank, world)
-
-    import torch
-    import torch.distributed as dist
+def build_net(c, local_rank, args, torch):
     from dnn_page_vectors_b200 import CLSM, ModelParams
-    from dnn_page_vectors_b200._lib import lib
-
-    assert torch.cuda.is_available(), "bench.py needs a CUDA device"
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    warmup = max(args.warmup, 3)
-    steps = max(args.steps, 1)
-    c = dict(CFG2, B=args.batch, V=args.vocab)
     mp = ModelParams(embedding_dim=c["D"], batch_size=c["B"], filter_sizes=c["windows"], num_filters=c["F"],
                      hidden_dims=c["H"], J=c["J"], dropout_prob=(0.25, 0.5), activation=c["act"], precision="bf16")
     rng = np.random.RandomState(1337)
@@ -189,19 +183,11 @@ def main():
     table[-1] = 0.0
     net = CLSM(mp, c["Lq"], c["Ld"], embedding_weights=table, device="cuda:%d" % local_rank,
                conv_impl=args.conv_impl, lazy_table_adam=args.lazy_adam).compile()
-    del table
-    if world > 1:
-        from dnn_page_vectors_b200.parallel import DataParallel
-        DataParallel(net)
-    batches = make_batches(c, 4, 1337 + rank)
+    return net
+
+
+def stage_resident(net, c, batches, torch):
     B = c["B"]
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- value: tokens resident in HBM before the timed region
     bq = net.query_model.buffers(B, True)
     bd = net.doc_model.buffers(B * (1 + c["J"]), True)
     dev_batches = []
@@ -215,7 +201,60 @@ def main():
         bq["tok"].copy_(q)
         bd["tok"].copy_(d)
         return net.step_resident(B, bq, bd)
+    return bq, bd, resident_step
 
+
+def pct(xs, q):
+    xs = sorted(xs)
+    return float(xs[min(len(xs) - 1, int(round(q * (len(xs) - 1))))])
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=CFG2["B"])
+    ap.add_argument("--vocab", type=int, default=CFG2["V"])
+    ap.add_argument("--conv-impl", default="auto")
+    ap.add_argument("--lazy-adam", action="store_true", help="row-sparse table Adam (NOT the reference's semantics)")
+    ap.add_argument("--no-extras", action="store_true", help="skip kernels / roofline / other_configs / sharded / cpu_baseline")
+    ap.add_argument("--dp-profile", action="store_true", help="N>1: device time of exchange / Adam / allgather per step, to stderr")
+    ap.add_argument("--ref-budget-s", type=float, default=420.0, help="--impl reference: wall-clock budget of the timed steps")
+    ap.add_argument("--shard-pages", type=int, default=SHARD_PAGES)
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    from dnn_page_vectors_b200._lib import lib
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    warmup = max(args.warmup, 3)
+    steps = max(args.steps, 1)
+    c = dict(CFG2, B=args.batch, V=args.vocab)
+    net = build_net(c, local_rank, args, torch)
+    if world > 1:
+        from dnn_page_vectors_b200.parallel import DataParallel
+        DataParallel(net)
+    batches = make_batches(c, 4, 1337 + rank)
+    B = c["B"]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: tokens resident in HBM before the timed region
+    bq, bd, resident_step = stage_resident(net, c, batches, torch)
     for i in range(warmup):
         resident_step(i)
     barrier()
@@ -223,25 +262,26 @@ def main():
     if rank == 0:
         sampler.start()
     l0 = lib.clsm_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    marks[0].record()
     for i in range(steps):
-        h = resident_step(i)
-    e1.record()
+        resident_step(i)
+        marks[i + 1].record()
     barrier()
     launches = int(lib.clsm_launch_count() - l0)
-    ms = e0.elapsed_time(e1)
+    ms = marks[0].elapsed_time(marks[steps])
+    per_step = [marks[i].elapsed_time(marks[i + 1]) for i in range(steps)]
     # ---- e2e: host batches in PINNED memory through the public API (train_on_batch): ids H2D and loss D2H
     # inside every step
-    batches = [[torch.as_tensor(a).pin_memory() for a in x] for x in batches]
+    pinned = [[torch.as_tensor(a).pin_memory() for a in x] for x in batches]
     for i in range(2):
-        net.train_on_batch(batches[i % len(batches)])
+        net.train_on_batch(pinned[i % len(pinned)])
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     last = None
     for i in range(steps):
-        last = net.train_on_batch(batches[i % len(batches)])
+        last = net.train_on_batch(pinned[i % len(pinned)])
     e3.record()
     barrier()
     ms_e2e = e2.elapsed_time(e3)
@@ -262,8 +302,11 @@ def main():
         "config": {"workload": WORKLOAD, "global_batch": B * world, "activation": c["act"], "dropout": 0.25,
                    "table_adam": "lazy-rows" if args.lazy_adam else "dense (Keras semantics)",
                    "conv_impl": args.conv_impl, "parallelism": "dp%d" % world,
+                   "streams": "two (query tower's backward/scatter/Adam beside the document tower's)" if (world == 1 and net.overlap) else "one",
                    "l2": "inputs larger than L2: each step streams both 1M x 300 tables and their Adam state (14 GB)",
                    "tokens": "Zipf(1.07) ids (frequency rank -> id by a fixed random permutation), true length U[L/4,L], right-padded with one PAD id"},
+        "step_ms": {"median": pct(per_step, 0.5), "p90": pct(per_step, 0.9), "min": min(per_step), "max": max(per_step),
+                    "note": "rank 0's device time per step of the timed region (events between steps)"},
         "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": tok_bytes, "d2h_bytes_per_step": 8,
                 "ms_per_step": ms_e2e / steps, "loss": last[0] if last else None},
         "gpu_launches": launches,
@@ -273,66 +316,125 @@ def main():
     if world > 1 and args.dp_profile:
         dp_profile(net, resident_step, torch, rank)
 
-    phases = None
     if not args.no_extras:
-        # ---- per-phase device times of instrumented steps (events between C-ABI calls).  Every rank runs
-        # them (the steps contain collectives); rank 0 reports its own.
-        phases = profile_phases(net, B, bq, bd, resident_step, torch)
-    if rank == 0 and not args.no_extras:
         pk = peaks()
-        line["kernels"] = phases
-        fwd = flops_pair_fwd(c) * B
-        # per-LAUNCH figures of the document tower (the larger of the two launches of each kernel): S = B*(1+J)
-        # sequences of Ld tokens.  Times: the instrumented step's per-call device time split between the two
-        # towers in proportion to their token counts.
-        n_doc, n_qry = B * (1 + c["J"]) * c["Ld"], B * c["Lq"]
-        share = n_doc / float(n_doc + n_qry)
-        conv_doc_flops = sum(2 * (c["Ld"] - k + 1) * k * c["D"] * c["F"] for k in c["windows"]) * B * (1 + c["J"])
-        n_table = (c["V"] + 1) * c["D"]                       # one table
-        cand = {
-            # kernel: (bound, algorithmic work per launch, launch ms, peak, unit, measured DRAM traffic per launch or None)
-            "conv_pool_tc (forward conv + max-pool)": ("tensor", conv_doc_flops / 1e12, phases.get("conv_pool_fwd_ms", 0) * share, pk["tf_sust"], "TFLOP/s", None),
-            # clsm_conv_pool_bwd launches dw_tc then dx_tc; its device time is split by the ncu launch-list ratio
-            # (profiles/r01_launches_summary.txt).  Work = the dense-equivalent GEMM each one stands for (= forward FLOPs).
-            "dw_tc (conv weight gradient)": ("tensor", conv_doc_flops / 1e12, phases.get("conv_pool_bwd_ms", 0) * share * DW_SHARE, pk["tf_sust"], "TFLOP/s", None),
-            "dx_tc (conv input gradient)": ("tensor", conv_doc_flops / 1e12, phases.get("conv_pool_bwd_ms", 0) * share * (1 - DW_SHARE), pk["tf_sust"], "TFLOP/s", None),
-            # traffic: dram__bytes_read+write of one adam_table launch, profiles/r01_ncu_full_summary.csv
-            "adam_table (dense Keras Adam over one 1M x 300 table)": ("hbm", 24.0 * n_table / 1e9, phases.get("adam_table_ms", 0) / 2.0, pk["hbm"], "GB/s", 7.92),
-            "emb_gather": ("hbm", n_doc * (4 + c["D"] * 2) / 1e9, phases.get("emb_gather_ms", 0) * share, pk["hbm"], "GB/s", None),
-            "emb_scatter": ("hbm", n_doc * (c["D"] * 4 + 8) / 1e9, phases.get("emb_scatter_ms", 0) * share, pk["hbm"], "GB/s", None),
-        }
-        top = max(cand, key=lambda k: cand[k][2])
-        bound, work, tms, peak, unit, traffic = cand[top]
-        ach = work / (tms * 1e-3) if tms > 0 else 0.0
-        line["roofline"] = {"kernel": top, "bound": bound, "achieved": ach, "peak": peak, "unit": unit,
-                            "frac": ach / peak if peak else None, "traffic": traffic, "traffic_unit": "GB per launch" if traffic else None,
-                            "peak_source": pk["src"], "algorithmic_work_per_launch": work, "launch_ms": tms,
-                            "note": "peak = sustained bf16 figure of MEASURED_PEAKS.json (kernel timed inside a long step)"}
-        line["roofline_all"] = {k: {"bound": v[0], "achieved": (v[1] / (v[2] * 1e-3) if v[2] > 0 else 0.0), "peak": v[3], "unit": v[4],
-                                    "frac": (v[1] / (v[2] * 1e-3) / v[3] if v[2] > 0 else None), "launch_ms": v[2]} for k, v in cand.items()}
-        line["train_flops_per_pair_3x"] = 3 * flops_pair_fwd(c)
-        line["model_tflops_3x"] = 3 * fwd * (steps / (ms * 1e-3)) / 1e12
-        if world == 1:
-            try:
-                line["encode"], line["topk"] = bench_inference(net, c, torch, pk)
-            except Exception as e:          # keep the headline line even if the extra leg fails
-                line["encode"] = {"error": repr(e)}
-    if rank == 0 and not args.no_extras and world == 1:       # CPU baseline: rank 0 at N = 1 only
+        # ---- per-call device times of instrumented ONE-STREAM steps.  Every rank runs them (the steps contain
+        # collectives); rank 0 reports its own.
+        phases, launch = profile_phases(net, resident_step, torch)
+        if rank == 0:
+            line["kernels"] = phases
+            fill_roofline(line, c, launch, clocks, pk, steps, ms)
+        # ---- configs[4] at this N: sharded encode and retrieval
         try:
-            from oracle import torch_cpu_port as CP
-            Bs = 64
-            pps, threads, dt = CP.time_train(dict(c), Bs, 3, 1)
-            line["cpu_baseline"] = {"value": pps, "unit": "pairs/s", "cores": threads, "kind": "port",
-                                    "sample": "torch-CPU fp32 port of the reference graph, cfg2 shapes, B=%d per step, 3 steps" % Bs}
-        except Exception as e:
-            line["cpu_baseline"] = {"value": None, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
-                                    "sample": "failed: %r" % (e,)}
+            line_sh = bench_sharded(net, c, torch, dist, pk, rank, world, args.shard_pages)
+            if rank == 0:
+                line["sharded"] = line_sh
+        except Exception as e:          # keep the headline line even if the extra leg fails
+            if rank == 0:
+                line["sharded"] = {"error": repr(e)}
+        if world == 1:
+            del bq, bd, resident_step
+            net = None
+            torch.cuda.empty_cache()
+            line["other_configs"] = {}
+            for name, cc in (("cfg3 (J=50, 1000-token pages, B=256/GPU)", CFG3), ("cfg4 (windows 1/2/3/5, 4x300 filters, B=8192)", CFG4)):
+                try:
+                    line["other_configs"][name] = bench_other(cc, local_rank, args, torch, pk)
+                except Exception as e:
+                    line["other_configs"][name] = {"error": repr(e)}
+                torch.cuda.empty_cache()
+            line["cpu_baseline"] = cpu_baseline(c, batches)
     if rank == 0:
         emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def fill_roofline(line, c, launch, clocks, pk, steps, ms):
+    """launch: {kernel: directly measured device ms of ONE launch of the document tower (or of one table)}."""
+    B = c["B"]
+    n_doc = B * (1 + c["J"]) * c["Ld"]
+    Dpad = (c["D"] + 63) // 64 * 64
+    conv_doc_tf = conv_flops_seq(c, c["Ld"]) * B * (1 + c["J"]) / 1e12
+    dense_doc_tf = 2 * len(c["windows"]) * c["F"] * c["H"] * B * (1 + c["J"]) / 1e12
+    n_table = (c["V"] + 1) * c["D"]
+    try:
+        with open(TRAFFIC_FILE) as f:
+            traffic = json.load(f)
+    except Exception:
+        traffic = {}
+    # the bf16 denominator: the burst figure unless the clock record of the timed region shows the power cap (then the
+    # sustained one); both fractions are printed
+    capped = bool(clocks and "sw_power_cap" in (clocks.get("reasons") or []))
+    cand = {
+        # kernel: (bound, algorithmic work per launch [TFLOP or GB], what the work is)
+        "conv_pool_tc": ("tensor", conv_doc_tf, "2 T k D F per sequence, document tower"),
+        "dw2_tc": ("tensor", conv_doc_tf, "dense-equivalent GEMM of the conv weight gradient (= forward FLOPs)"),
+        "dx2_tc": ("tensor", conv_doc_tf, "dense-equivalent GEMM of the conv input gradient (= forward FLOPs)"),
+        "dense_fwd": ("tensor", dense_doc_tf, "2 |K|F H per sequence"),
+        "dense_bwd": ("tensor", 2 * dense_doc_tf, "dWd and G GEMMs"),
+        "adam_table": ("hbm", 24.0 * n_table / 1e9, "24 B per parameter of one 1M x 300 table (p, m, v read + write)"),
+        # the gather is a standalone kernel: it must WRITE X (Dpad bf16 per token) besides reading ids and rows
+        "emb_gather": ("hbm", n_doc * (4 + c["D"] * 2 + Dpad * 2) / 1e9, "ids + table rows read + X written (not fused, so the write is work)"),
+        "emb_scatter": ("hbm", n_doc * (c["D"] * 4 + 8) / 1e9, "dX rows read + 8 B key/index per token"),
+    }
+    out = {}
+    for k, (bound, work, what) in cand.items():
+        tms = launch.get(k)
+        if not tms:
+            continue
+        ach = work / (tms * 1e-3)
+        if bound == "tensor":
+            e = {"bound": bound, "achieved": ach, "unit": "TFLOP/s", "peak": pk["tf_sust"] if capped else pk["tf_burst"],
+                 "frac_of_burst_peak": ach / pk["tf_burst"], "frac_of_sustained_peak": ach / pk["tf_sust"]}
+        else:
+            e = {"bound": bound, "achieved": ach, "unit": "GB/s", "peak": pk["hbm"]}
+        e["frac"] = ach / e["peak"]
+        e["launch_ms"] = tms
+        e["algorithmic_work_per_launch"] = work
+        e["work"] = what
+        e["traffic"] = traffic.get(k)
+        out[k] = e
+    line["roofline_all"] = out
+    if out:
+        top = max(out, key=lambda k: out[k]["launch_ms"])
+        r = dict(out[top])
+        r["kernel"] = top
+        r["peak_source"] = pk["src"]
+        r["traffic_unit"] = ("GB per launch (dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full, %s)"
+                             % os.path.relpath(TRAFFIC_FILE, ROOT)) if r.get("traffic") else None
+        how = "launch_ms = CUDA events around this kernel's launch in a one-stream instrumented step, median of 3; "
+        if r["bound"] == "tensor":
+            how += ("bf16 peak = sustained figure (sw_power_cap seen in the timed region)" if capped
+                    else "bf16 peak = burst figure (no power-cap sample in the timed region)")
+        else:
+            how += "peak = measured HBM copy bandwidth"
+        r["note"] = how
+        line["roofline"] = r
+    line["train_flops_per_pair_3x"] = 3 * flops_pair_fwd(c)
+    line["model_tflops_3x"] = 3 * flops_pair_fwd(c) * B * (steps / (ms * 1e-3)) / 1e12
+
+
+def cpu_baseline(c, batches):
+    """Rank 0, N = 1: the CPU port on the host cores.  cfg2 at the GPU arm's own batch (a bounded sample: 1 warm-up +
+    2 timed steps), and BASELINE.json configs[0] (cfg1: B=128, V=50k -- the reference's own CPU-runnable case)."""
+    try:
+        from oracle import torch_cpu_port as CP
+        pps, threads, dt, done = CP.time_train(dict(c), c["B"], 2, 1, batches=batches, budget_s=60.0)
+        out = {"value": pps, "unit": "pairs/s", "cores": threads, "kind": "port",
+               "sample": "torch-CPU fp32 port of the reference graph, cfg2 shapes, B=%d per step (same batch and Zipf tokens as the "
+                         "GPU arm), 1 warm-up + %d timed steps, %.1f s per step" % (c["B"], done, dt)}
+        try:
+            c1 = dict(CFG1)
+            p1, _, dt1, n1 = CP.time_train(c1, c1["B"], 10, 2, batches=make_batches(c1, 2, 1337), budget_s=20.0)
+            out["cfg1"] = {"value": p1, "unit": "pairs/s", "sample": "BASELINE configs[0]: B=128, V=50k, %d timed steps, %.3f s per step" % (n1, dt1)}
+        except Exception as e:
+            out["cfg1"] = {"error": repr(e)}
+        return out
+    except Exception as e:
+        return {"value": None, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: %r" % (e,)}
 
 
 def dp_profile(net, resident_step, torch, rank):
@@ -377,85 +479,192 @@ def dp_profile(net, resident_step, torch, rank):
     sys.stderr.write("[dp profile, rank %d, ms] %s\n" % (rank, json.dumps(med)))
 
 
-def profile_phases(net, B, bq, bd, resident_step, torch):
-    """Device time of each C-ABI call class over 3 instrumented steps (median)."""
+def profile_phases(net, resident_step, torch):
+    """Device time of each C-ABI call over 3 instrumented steps (median), with the two-stream overlap switched off so
+    that every launch is timed alone on the stream.  Returns (per-call-class totals per step, per-launch times of the
+    document tower: for a class called once per tower the LARGER launch is the document tower's).  clsm_conv_pool_bwd
+    is split into dW kernel / reductions / dX kernel by two events the library records inside the call."""
+    import ctypes as C
     from dnn_page_vectors_b200 import _lib
     import dnn_page_vectors_b200.model as M
-    import dnn_page_vectors_b200.parallel  # noqa: F401
     orig = _lib.call
     rec = []
 
+    def new_event():
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()                          # creates the underlying cudaEvent_t
+        return e
+
     def timed(name, *a):
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        mids = None
+        if name == "clsm_conv_pool_bwd":
+            mids = (new_event(), new_event())
+            _lib.lib.clsm_debug_mark_conv_bwd(C.c_void_p(mids[0].cuda_event), C.c_void_p(mids[1].cuda_event))
         s.record()
         r = orig(name, *a)
         e.record()
-        rec.append((name, s, e))
+        rec.append((name, s, e, mids))
         return r
-    out = {}
+    was = net.overlap
+    net.overlap = False
     M.call = timed
+    totals, launches = [], []
     try:
-        runs = []
         for i in range(3):
             rec.clear()
             resident_step(i)
             torch.cuda.synchronize()
-            agg = {}
-            for name, s, e in rec:
-                agg[name] = agg.get(name, 0.0) + s.elapsed_time(e)
-            runs.append(agg)
-        for name in runs[0]:
-            out[name.replace("clsm_", "") + "_ms"] = float(np.median([r.get(name, 0.0) for r in runs]))
+            agg, per = {}, {}
+            for name, s, e, mids in rec:
+                key = name.replace("clsm_", "")
+                d = s.elapsed_time(e)
+                agg[key] = agg.get(key, 0.0) + d
+                per.setdefault(key, []).append(d)
+                if mids is not None:
+                    per.setdefault("dw2_tc", []).append(s.elapsed_time(mids[0]))
+                    per.setdefault("conv_bwd_reductions", []).append(mids[0].elapsed_time(mids[1]))
+                    per.setdefault("dx2_tc", []).append(mids[1].elapsed_time(e))
+            totals.append(agg)
+            launches.append({k: max(v) for k, v in per.items()})
     finally:
         M.call = orig
+        net.overlap = was
+    out = {k + "_ms": float(np.median([r.get(k, 0.0) for r in totals])) for k in totals[0]}
+    launch = {k: float(np.median([r.get(k, 0.0) for r in launches])) for k in launches[0]}
+    rename = {"conv_pool_fwd": "conv_pool_tc"}
+    launch = {rename.get(k, k): v for k, v in launch.items()}
+    out["doc_tower_launch_ms"] = {k: round(v, 4) for k, v in launch.items()}
+    return out, launch
+
+
+def bench_other(cc, local_rank, args, torch, pk):
+    """One of the other BASELINE training shapes on one GPU: ms/step, pairs/s, and the fraction of the roofline-implied
+    floor of SURVEY 8(d) (3x forward FLOPs at the sustained bf16 peak -- these steps run for seconds)."""
+    net = build_net(cc, local_rank, args, torch)
+    batches = make_batches(cc, 2, 4242)
+    bq, bd, step = stage_resident(net, cc, batches, torch)
+    for i in range(3):
+        step(i)
+    torch.cuda.synchronize()
+    n = 5
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(n):
+        step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n
+    flops3 = 3 * flops_pair_fwd(cc) * cc["B"]
+    floor_ms = flops3 / (pk["tf_sust"] * 1e12) * 1e3
+    phases, launch = profile_phases(net, step, torch)
+    out = {"ms_per_step": ms, "pairs_per_s": cc["B"] / (ms * 1e-3), "batch": cc["B"], "model_tflops_3x": flops3 / (ms * 1e-3) / 1e12,
+           "floor_ms_3x_flops_at_sustained_bf16_peak": floor_ms, "frac_of_floor": floor_ms / ms,
+           "kernels_ms": {k: round(v, 3) for k, v in phases.items() if isinstance(v, float)}}
+    del net, bq, bd, step
     return out
 
 
-def bench_inference(net, c, torch, pk):
-    """Page-encode rate (pages/s) and retrieval rate (queries/s) on one GPU shard."""
-    rng = np.random.RandomState(7)
+def bench_sharded(net, c, torch, dist, pk, rank, world, shard_pages):
+    """BASELINE configs[4] at this N.  Encode: each rank encodes its contiguous row shard (shard_pages pages of Ld tokens,
+    no communication) into bf16 page vectors.  Retrieval: each rank scans its shard (tensor-core scan, k = 100), the
+    (Q, k) lists are allgathered and merged in (score desc, id asc) order.  Rank 0 also scans the whole corpus alone and
+    checks that the merged ids are IDENTICAL.  Rates are whole-job (all ranks), times the max over ranks."""
+    H, Ld, k = c["H"], c["Ld"], 100
+    dev = torch.device("cuda", torch.cuda.current_device())
+
+    def maxr(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+    # ---- encode: 8 distinct resident batches of 16384 pages, cycled until the shard is done
     NB = 16384
-    pages = torch.as_tensor(zipf_tokens(rng, c["V"], NB, c["Ld"])).cuda()
+    rng = np.random.RandomState(7 + rank)
+    pool = [torch.as_tensor(zipf_tokens(rng, c["V"], NB, Ld)).to(dev) for _ in range(8)]
     b = net.doc_model.buffers(NB, False)
-    out = torch.empty((NB, c["H"]), dtype=torch.float32, device="cuda")
-    b["tok"].copy_(pages)
-    for _ in range(3):
+    out = torch.empty((NB, H), dtype=torch.bfloat16, device=dev)
+    n_calls = max(shard_pages // NB, 1)
+    for i in range(3):
+        b["tok"].copy_(pool[i % len(pool)])
         net.encode_resident(net.doc_model, b, out)
+    if world > 1:
+        dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    reps = 10
     e0.record()
-    for _ in range(reps):
+    for i in range(n_calls):
+        b["tok"].copy_(pool[i % len(pool)])
         net.encode_resident(net.doc_model, b, out)
     e1.record()
     torch.cuda.synchronize()
-    enc_ms = e0.elapsed_time(e1) / reps
-    enc = {"value": NB / (enc_ms * 1e-3), "unit": "pages/s", "pages_per_call": NB, "ms_per_call": enc_ms}
-    # retrieval (cfg5's per-GPU shard: 2.5 M pages of H = 128 bf16 vectors, k = 100), random unit vectors, tensor-core
-    # scan; query batches of 128 (the memory-bound regime) and 1024, plus the 1 M-row shard quoted in earlier rounds
-    k = 100
-    g = torch.Generator(device="cuda").manual_seed(3)
-    corpus = torch.nn.functional.normalize(torch.randn((2_500_000, c["H"]), generator=g, device="cuda"), dim=1).to(torch.bfloat16)
-    qall = torch.nn.functional.normalize(torch.randn((1024, c["H"]), generator=g, device="cuda"), dim=1).to(torch.bfloat16)
+    enc_ms = maxr(e0.elapsed_time(e1))
+    pages = n_calls * NB
+    page_flops = conv_flops_seq(c, Ld) + 2 * len(c["windows"]) * c["F"] * H
+    enc = {"value": pages * world / (enc_ms * 1e-3), "unit": "pages/s", "pages_per_gpu": pages, "pages_per_call": NB,
+           "ms_per_call": enc_ms / n_calls, "per_gpu_pages_per_s": pages / (enc_ms * 1e-3), "out_dtype": "bf16",
+           "frac_of_tensor_floor_sustained": (pages * page_flops / (enc_ms * 1e-3) / 1e12) / pk["tf_sust"]}
+    del pool
 
-    def run(N, Q):
-        cv, qv = corpus[:N], qall[:Q].contiguous()
+    # ---- retrieval: shard r = unit vectors from seed 1000 + r
+    def shard(r):
+        g = torch.Generator(device=dev).manual_seed(1000 + r)
+        return torch.nn.functional.normalize(torch.randn((shard_pages, H), generator=g, device=dev), dim=1).to(torch.bfloat16)
+    g = torch.Generator(device=dev).manual_seed(3)
+    qall = torch.nn.functional.normalize(torch.randn((1024, H), generator=g, device=dev), dim=1).to(torch.bfloat16)
+    corpus = shard(rank)
+    res = {}
+    merged_ids = {}
+    for Q in (128, 1024):
+        qv = qall[:Q].contiguous()
+
+        def one():
+            sc, ids = net.topk(qv, corpus, k=k, id_base=rank * shard_pages)
+            m0 = torch.cuda.Event(enable_timing=True)
+            m0.record()
+            if world > 1:
+                all_s = sc.new_empty((world,) + tuple(sc.shape))
+                all_i = ids.new_empty((world,) + tuple(ids.shape))
+                dist.all_gather_into_tensor(all_s, sc.contiguous())
+                dist.all_gather_into_tensor(all_i, ids.contiguous())
+                sc, ids = net.topk_merge(all_s, all_i)
+            return sc, ids, m0
         for _ in range(2):
-            net.topk(qv, cv, k=k)
+            one()
+        if world > 1:
+            dist.barrier()
         torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(5):
-            net.topk(qv, cv, k=k)
-        e1.record()
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / 5
+        reps = 5
+        scan_ms, merge_ms = [], []
+        for _ in range(reps):
+            a = torch.cuda.Event(enable_timing=True)
+            a.record()
+            sc, ids, m0 = one()
+            z = torch.cuda.Event(enable_timing=True)
+            z.record()
+            torch.cuda.synchronize()
+            scan_ms.append(a.elapsed_time(m0))
+            merge_ms.append(m0.elapsed_time(z))
+        tot = maxr(float(np.sum(scan_ms) + np.sum(merge_ms))) / reps
+        scan = maxr(float(np.median(scan_ms)))
         blocks = (Q + 127) // 128
-        return {"value": Q / (ms * 1e-3), "unit": "queries/s", "corpus_rows": N, "queries_per_call": Q, "k": k, "corpus_dtype": "bf16",
-                "ms_per_call": ms, "hbm_frac_of_one_scan": (blocks * N * c["H"] * 2 / 1e9) / (ms * 1e-3) / pk["hbm"]}
-    tk = run(1_000_000, 128)
-    tk["cfg5_shard_2p5M_rows"] = {"q128": run(2_500_000, 128), "q1024": run(2_500_000, 1024)}
-    return enc, tk
+        res["q%d" % Q] = {"value": Q / (tot * 1e-3), "unit": "queries/s", "queries_per_call": Q, "k": k, "corpus_rows_per_gpu": shard_pages,
+                          "corpus_rows_total": shard_pages * world, "corpus_dtype": "bf16", "ms_per_call": tot, "scan_ms": scan,
+                          "allgather_merge_ms": maxr(float(np.median(merge_ms))),
+                          "hbm_frac_of_one_scan_per_query_block": (blocks * shard_pages * H * 2 / 1e9) / (scan * 1e-3) / pk["hbm"]}
+        merged_ids[Q] = ids
+    # ---- the merged answer against one GPU scanning the whole corpus
+    if world > 1:
+        check = None
+        del corpus
+        if rank == 0:
+            whole = torch.cat([shard(r) for r in range(world)], dim=0)
+            _, ids1 = net.topk(qall[:128].contiguous(), whole, k=k, id_base=0)
+            check = bool(torch.equal(ids1, merged_ids[128]))
+            del whole
+        res["merged_ids_identical_to_single_gpu_scan_of_whole_corpus"] = check
+        dist.barrier()
+    return {"encode": enc, "topk": res}
 
 
 _RESULT_FD = None

@@ -26,6 +26,7 @@ SIGNATURES = {
     "clsm_last_error": (C.c_char_p, []),
     "clsm_num_sms": (i32, []),
     "clsm_launch_count": (C.c_ulonglong, []),
+    "clsm_debug_mark_conv_bwd": (None, [vp, vp]),
     "clsm_emb_gather": (i32, [vp, i64, vp, i64, i32, i32, i32, vp, i32, f32, u64, vp]),
     "clsm_emb_gather_h": (i32, [vp, vp, i64, vp, i64, i32, i32, i32, vp, i32, f32, u64, vp]),
     "clsm_dropout_mask": (i32, [i64, i32, f32, u64, vp, vp]),

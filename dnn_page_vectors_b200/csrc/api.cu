@@ -5,6 +5,7 @@
 
 static thread_local char g_err[512] = "";
 unsigned long long g_clsm_launches = 0;
+thread_local void* g_clsm_marks[2] = {nullptr, nullptr};      // clsm_debug_mark_conv_bwd: events for the next clsm_conv_pool_bwd
 
 void clsm_set_error(const char* fmt, ...) {
   va_list ap;
@@ -30,4 +31,5 @@ int clsm_version(void) { return 100; }
 const char* clsm_last_error(void) { return g_err; }
 int clsm_num_sms(void) { return clsm_sm_count(); }
 unsigned long long clsm_launch_count(void) { return g_clsm_launches; }
+void clsm_debug_mark_conv_bwd(void* ev_after_dw, void* ev_before_dx) { g_clsm_marks[0] = ev_after_dw; g_clsm_marks[1] = ev_before_dx; }
 }

@@ -28,6 +28,7 @@ void clsm_set_error(const char* fmt, ...);
     }                                                                             \
   } while (0)
 
+extern thread_local void* g_clsm_marks[2];       // measurement marks (api.cu), consumed by clsm_conv_pool_bwd
 extern unsigned long long g_clsm_launches;      // kernels of this library launched so far (api.cu)
 #define CLSM_LAUNCH_CHECK()            \
   do {                                 \

@@ -264,6 +264,7 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
   } else if (rc != CLSM_OK) {
     return rc;
   }
+  if (g_clsm_marks[0] != nullptr) { CLSM_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(g_clsm_marks[0]), st)); g_clsm_marks[0] = nullptr; }
   const int64_t ne = static_cast<int64_t>(k) * D * F;
   conv_bwd_dw_reduce_kernel<<<static_cast<unsigned>(ceil_div64(ne, 256)), 256, 0, st>>>(part, n_parts, k, D, Dpad, F, dW_ref);
   CLSM_LAUNCH_CHECK();
@@ -271,6 +272,7 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
 
   // dX: tensor cores (bf16 mode) -> shared-memory staged CUDA cores -> generic
   void* wb_scratch = static_cast<char*>(sort_scratch) + clsm_conv_bwd_dx_fast_bytes(S, L, F);
+  if (g_clsm_marks[1] != nullptr) { CLSM_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(g_clsm_marks[1]), st)); g_clsm_marks[1] = nullptr; }
   rc = clsm_conv_bwd_dx_tc(Wt, dtype, k, Dpad, L, S, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1, wb_scratch, st);
   if (rc == CLSM_OK) return CLSM_OK;
   if (rc != CLSM_EUNSUPPORTED) return rc;

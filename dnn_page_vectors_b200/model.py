@@ -317,6 +317,7 @@ class CLSM(object):
         import os
         self.overlap = os.environ.get("CLSM_OVERLAP", "1") != "0"      # two-stream step, see step_resident
         self._side = None
+        self._probe = None             # scripts/overlap_probe.py: events around the two towers' post-loss work
         self._head = {}
         self._pinned = {}
 
@@ -399,8 +400,8 @@ class CLSM(object):
     # ---- device-resident step (bench `value`): tokens already staged in the tower buffers
     def step_resident(self, B, bq, bd):
         """One training step.  After the loss kernel the two towers are independent: the query tower's backward,
-        scatter and table Adam (HBM-bound: a 1.2 GB table and its Adam state) run on a second stream underneath the
-        document tower's tensor-bound conv gradients, and the streams join before the step returns.  Every kernel is
+        scatter and table Adam (HBM-bound: a 1.2 GB table and its Adam state) and the document tower's tensor-bound
+        conv gradients run on two streams, and the streams join before the step returns.  Every kernel is
         deterministic and the towers share no buffer, so the weights are bit-identical to the one-stream order
         (CLSM_OVERLAP=0 selects it; tests/test_gpu_model.py compares the two)."""
         sq, sd = self._seeds()
@@ -417,18 +418,29 @@ class CLSM(object):
             self.doc_model.adam(bd, self.iterations, gd)
             self.dp.after_adam(self)
         elif self.overlap:
+            # The document tower's persistent tensor-core kernels go to a HIGH-priority stream: their 148 CTAs become
+            # resident as soon as they are launched and the query tower's short HBM-bound CTAs (current stream) fill
+            # the thread slots that are left, instead of the first-launched grid holding every SM until it drains.
             main = torch.cuda.current_stream()
             if self._side is None:
-                self._side = torch.cuda.Stream(device=self.device)
+                self._side = torch.cuda.Stream(device=self.device, priority=-1)
                 self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
             self._ev_fork.record(main)
             self._side.wait_event(self._ev_fork)
+            if self._probe is not None:
+                self._probe["q0"].record(main)
+            self.query_model.backward(bq)             # issued first: the host needs ~1 ms to issue a tower's backward
+            self.query_model.adam(bq, self.iterations)
+            if self._probe is not None:
+                self._probe["q1"].record(main)
             with torch.cuda.stream(self._side):
-                self.query_model.backward(bq)
-                self.query_model.adam(bq, self.iterations)
+                if self._probe is not None:
+                    self._probe["d0"].record(self._side)
+                self.doc_model.backward(bd)
+                self.doc_model.adam(bd, self.iterations)
+                if self._probe is not None:
+                    self._probe["d1"].record(self._side)
                 self._ev_join.record(self._side)
-            self.doc_model.backward(bd)
-            self.doc_model.adam(bd, self.iterations)
             main.wait_event(self._ev_join)
         else:
             self.query_model.backward(bq)

@@ -42,6 +42,10 @@ const char* clsm_last_error(void);
 int clsm_num_sms(void);
 /* kernels of this library launched by this process so far (bench.py's gpu_launches) */
 unsigned long long clsm_launch_count(void);
+/* measurement aid (bench.py's per-kernel roofline): the NEXT clsm_conv_pool_bwd call of this thread records the two
+ * given cudaEvent_t handles on its stream, the first right after its dW kernel and the second right before its dX
+ * kernel (the weight-gradient reduction and the bias column sum lie between them), then forgets them.  NULL = none. */
+void clsm_debug_mark_conv_bwd(void* ev_after_dw, void* ev_before_dx);
 
 /* ---- embedding gather (+ optional inverted dropout) ------------------------------------
  * replaces Embedding(...)            dssm_cnn_v2/cnn_dssm_tf.py:111-116

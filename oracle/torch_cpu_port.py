@@ -92,16 +92,26 @@ class CpuCLSM(object):
         return torch.topk(qn @ cn.T, k, dim=1)
 
 
-def time_train(cfg, B, steps, warmup, seed=1337):
-    """Returns (pairs_per_s, threads, seconds_per_step)."""
+def time_train(cfg, B, steps, warmup, seed=1337, batches=None, budget_s=None):
+    """Times `steps` training steps after `warmup` untimed ones.  batches: optional list of [q (B, Lq), pos (B, Ld),
+    neg_0.. (B, Ld)] integer arrays (the reference's batch format, data_helpers.py:196-197) cycled through; default
+    uniform random ids.  budget_s: stop early once the timed steps have used that many seconds (at least one step
+    is always timed).  Returns (pairs_per_s, threads, seconds_per_step, steps_done)."""
     net = CpuCLSM(cfg["V"] + 1, cfg["D"], cfg["windows"], cfg["F"], cfg["H"], cfg["J"], act=cfg["act"], seed=seed)
-    g = torch.Generator().manual_seed(seed)
-    q = torch.randint(0, cfg["V"], (B, cfg["Lq"]), generator=g)
-    d = torch.randint(0, cfg["V"], (B, 1 + cfg["J"], cfg["Ld"]), generator=g)
-    for _ in range(warmup):
-        net.train_step(q, d)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        net.train_step(q, d)
-    dt = (time.perf_counter() - t0) / max(steps, 1)
-    return B / dt, net.threads, dt
+    if batches is None:
+        g = torch.Generator().manual_seed(seed)
+        data = [(torch.randint(0, cfg["V"], (B, cfg["Lq"]), generator=g),
+                 torch.randint(0, cfg["V"], (B, 1 + cfg["J"], cfg["Ld"]), generator=g))]
+    else:
+        data = [(torch.as_tensor(np.asarray(x[0])).long(), torch.as_tensor(np.stack(x[1:], axis=1)).long()) for x in batches]
+        B = int(data[0][0].shape[0])
+    for i in range(warmup):
+        net.train_step(*data[i % len(data)])
+    done, t0 = 0, time.perf_counter()
+    for i in range(max(steps, 1)):
+        net.train_step(*data[i % len(data)])
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s:
+            break
+    dt = (time.perf_counter() - t0) / done
+    return B / dt, net.threads, dt, done

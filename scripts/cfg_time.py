@@ -37,7 +37,7 @@ e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / steps
 fl = 3 * bench.flops_pair_fwd(c) * B
 if os.environ.get("PHASES"):
-    ph = bench.profile_phases(net, B, bq, bd, lambda i: net.step_resident(B, bq, bd), torch)
-    print(json.dumps({k: round(v, 3) for k, v in ph.items()}))
+    ph, _ = bench.profile_phases(net, lambda i: net.step_resident(B, bq, bd), torch)
+    print(json.dumps({k: (round(v, 3) if isinstance(v, float) else v) for k, v in ph.items()}))
 print(json.dumps({"config": name, "B": B, "ms_per_step": ms, "pairs_per_s": B / (ms * 1e-3), "model_tflops_3x": fl / (ms * 1e-3) / 1e12,
                   "loss": float(h["loss_acc"][0]), "mem_GB": torch.cuda.max_memory_allocated() / 1e9}))

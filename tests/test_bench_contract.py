@@ -11,7 +11,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def run(env_extra=None):
     env = dict(os.environ)
     env.update(env_extra or {})
-    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1",
+                        "--batch", "32", "--vocab", "20000"],      # small batch / table: this test is about the line, not the number
                        capture_output=True, text=True, env=env, timeout=600, cwd=ROOT)
     assert p.returncode == 0, p.stderr[-2000:]
     return p.stdout
@@ -28,6 +29,7 @@ def test_reference_arm_prints_one_json_line():
     assert d["impl"] == "reference" and d["metric"] == "train_pairs_per_s" and d["unit"] == "pairs/s"
     assert d["value"] > 0 and d["higher_is_better"] is True and d["vs_baseline"] is None
     assert "workload" in d["config"] and d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    assert d["steps"] == 2 and d["requested_steps"] == 2 and d["warmup"] == 1 and d["config"]["global_batch"] == 32
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0 and d["e2e"]["value"] == d["value"]
 
 

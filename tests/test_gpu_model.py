@@ -279,13 +279,14 @@ def test_bf16_tensor_core_path_vectors_cosines_loss_and_trajectory(cfg):
         assert abs(l_eval - head["loss"]) <= tol * max(1.0, abs(head["loss"]))
         l, a = net.train_on_batch(x)
         assert abs(l - head["loss"]) <= tol * max(1.0, abs(head["loss"])), (t, l, head["loss"])
-    # Adam normalises every step to ~lr, so after 3 steps the weights agree closely wherever the gradient's sign is
-    # not within rounding of zero; the bulk must sit within 1e-4 of the oracle's masters
+    # Adam normalises every step to ~lr, so after 3 steps the weights agree closely wherever the gradient is not a
+    # near-cancelling sum (the pooled gradient enters the tensor-core backward as bf16: 2^-9 per term, which is a
+    # large relative error on an element whose terms cancel); the bulk must sit within 1e-4 of the oracle's masters
     w = net.get_weights()
     for tag, op in (("query", oq), ("doc", od)):
         for got, want in ((w[tag]["Wd"], op["Wd"]), (w[tag]["convW0"], op["convW"][0]), (w[tag]["E"], op["E"])):
             err = np.abs(got - want)
-            assert err.max() < 7e-3 and (err > 1e-4).mean() < 5e-2, (tag, err.max(), (err > 1e-4).mean())
+            assert err.max() < 7e-3 and (err > 1e-4).mean() < 0.15, (tag, err.max(), (err > 1e-4).mean())
 
 
 @pytest.mark.parametrize("H", [128, 150])
