@@ -30,6 +30,14 @@ SIGNATURES = {
     "clsm_emb_gather": (i32, [vp, i64, vp, i64, i32, i32, i32, vp, i32, f32, u64, vp]),
     "clsm_emb_gather_h": (i32, [vp, vp, i64, vp, i64, i32, i32, i32, vp, i32, f32, u64, vp]),
     "clsm_dropout_mask": (i32, [i64, i32, f32, u64, vp, vp]),
+    "clsm_emb_gather_mask": (i32, [vp, i64, vp, i64, i32, i32, i32, vp, i32, f32, u64, vp, vp]),
+    "clsm_dropout_scale": (f32, [f32]),
+    "clsm_check_token_ids": (i32, [vp, i64, i64, vp, vp]),
+    "clsm_conv_bwd_dx_bf16_ok": (i32, [i64, i32, i32, i32, i32]),
+    "clsm_conv_pool_bwd_ex": (i32, [vp, i32, i64, i32, i32, i32, vp, i32, i32, i32, vp, vp, i32, i32,
+                                    vp, vp, vp, i32, i32, vp, sz, vp]),
+    "clsm_emb_scatter_plan": (i32, [vp, i64, i32, i32, i64, vp, vp, vp, vp, sz, vp]),
+    "clsm_emb_scatter_reduce": (i32, [i64, vp, i32, i32, i32, f32, u64, vp, vp, vp, sz, vp]),
     "clsm_pack_conv_w": (i32, [vp, i32, i32, i32, i32, i32, i32, vp, vp]),
     "clsm_conv_pool_fwd": (i32, [vp, i32, i64, i32, i32, vp, i32, i32, i32, vp, i32, i32, i32, vp]),
     "clsm_pool_finalize": (i32, [vp, i64, i32, i32, vp, i32, vp, vp, i32, vp]),

@@ -106,6 +106,11 @@ __host__ __device__ __forceinline__ uint32_t keep_threshold(float keep) {
   int t = static_cast<int>(keep * 256.0f + 0.5f);
   return t < 0 ? 0u : (t > 256 ? 256u : static_cast<uint32_t>(t));
 }
+// inverted-dropout scale = 1 / the realised keep probability (thr / 256), so E[X] is unbiased for every keep
+__host__ __device__ __forceinline__ float dropout_scale(float keep) {
+  const uint32_t t = keep_threshold(keep);
+  return t == 0 ? 0.0f : 256.0f / static_cast<float>(t);
+}
 // 16 decision bytes for (row, block of 16 columns)
 __host__ __device__ __forceinline__ void dropout_bytes16(uint64_t seed, uint64_t row, uint32_t cblk,
                                                          uint32_t out[4]) {

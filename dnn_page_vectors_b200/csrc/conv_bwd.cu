@@ -20,8 +20,9 @@ int clsm_conv_bwd_dx_fast(const void* Wt, int dtype, int k, int Dpad, int L, int
 int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, int max_splits, const float* G,
                         const int32_t* A, int ldp, int col0, int F, int k, float* part, cudaStream_t st);          // conv_bwd_tc.cu
 size_t clsm_conv_bwd_dx_tc_bytes(int k, int Dpad, int F);                                               // conv_bwd_tc.cu
+int clsm_conv_bwd_dx_tc_tiling2_ok(int k, int Dpad, int F, int64_t n_rows);
 int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64_t S, const float* G, const int32_t* A,
-                        int ldp, int col0, int F, float* dX, int accumulate, void* scratch, cudaStream_t st);
+                        int ldp, int col0, int F, float* dX, int accumulate, int dx_bf16, void* scratch, cudaStream_t st);
 
 namespace {
 
@@ -225,12 +226,34 @@ size_t clsm_conv_bwd_workspace_bytes(int64_t S, int L, int k, int D, int F) {
   return part + cs + clsm_conv_bwd_dx_fast_bytes(S, L, F) + clsm_conv_bwd_dx_tc_bytes(k, Dpad, F);
 }
 
+int clsm_conv_bwd_dx_bf16_ok(int64_t S, int L, int k, int D, int F) {
+  const int Dpad = (D + 63) / 64 * 64;
+  return (k >= 1 && k <= 7 && Dpad <= 512) ? clsm_conv_bwd_dx_tc_tiling2_ok(k, Dpad, F, S * L) : 0;
+}
+
 int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
                        const void* Wt, int k, int F, int Fpad,
                        const float* G, const int32_t* argmax, int ldp, int col0,
                        float* dW_ref, float* db, float* dX, int first_window,
                        void* ws, size_t ws_bytes, void* stream) {
+  return clsm_conv_pool_bwd_ex(X, dtype, S, L, D, Dpad, Wt, k, F, Fpad, G, argmax, ldp, col0, dW_ref, db, dX, CLSM_F32,
+                               first_window, ws, ws_bytes, stream);
+}
+
+int clsm_conv_pool_bwd_ex(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
+                          const void* Wt, int k, int F, int Fpad,
+                          const float* G, const int32_t* argmax, int ldp, int col0,
+                          float* dW_ref, float* db, void* dX_any, int dx_dtype, int first_window,
+                          void* ws, size_t ws_bytes, void* stream) {
   CLSM_REQUIRE(dtype == CLSM_BF16 || dtype == CLSM_F32, "conv_pool_bwd: bad dtype");
+  CLSM_REQUIRE(dx_dtype == CLSM_F32 || dx_dtype == CLSM_BF16, "conv_pool_bwd: dX must be fp32 or bf16");
+  const int dx_bf16 = dx_dtype == CLSM_BF16 ? 1 : 0;
+  if (dx_bf16 && !(dtype == CLSM_BF16 && first_window != 0 && clsm_conv_bwd_dx_bf16_ok(S, L, k, D, F))) {
+    clsm_set_error("conv_pool_bwd: bf16 dX rows need the bf16 tensor-core path, first_window = 1 and a shape "
+                   "clsm_conv_bwd_dx_bf16_ok() accepts");
+    return CLSM_EUNSUPPORTED;
+  }
+  float* dX = static_cast<float*>(dX_any);
   CLSM_REQUIRE(S > 0 && L >= k && k >= 1 && k <= 7 && F >= 1 && Fpad >= F && F <= DX_MAXF, "conv_pool_bwd: bad sizes (k must be 1..7, F <= 512)");
   CLSM_REQUIRE(S * ((L + DX_ROWS - 1) / DX_ROWS) < (1ll << 31), "conv_pool_bwd: too many sequences for one launch");
   CLSM_REQUIRE(Dpad == (D + 63) / 64 * 64 && Dpad <= 512, "conv_pool_bwd: Dpad must be D rounded up to 64 and <= 512");
@@ -273,7 +296,8 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
   // dX: tensor cores (bf16 mode) -> shared-memory staged CUDA cores -> generic
   void* wb_scratch = static_cast<char*>(sort_scratch) + clsm_conv_bwd_dx_fast_bytes(S, L, F);
   if (g_clsm_marks[1] != nullptr) { CLSM_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(g_clsm_marks[1]), st)); g_clsm_marks[1] = nullptr; }
-  rc = clsm_conv_bwd_dx_tc(Wt, dtype, k, Dpad, L, S, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1, wb_scratch, st);
+  rc = clsm_conv_bwd_dx_tc(Wt, dtype, k, Dpad, L, S, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1, dx_bf16, wb_scratch, st);
+  if (dx_bf16 && rc == CLSM_EUNSUPPORTED) { clsm_set_error("conv_pool_bwd: bf16 dX rows requested but the tensor-core dX kernel refused the shape"); return rc; }
   if (rc == CLSM_OK) return CLSM_OK;
   if (rc != CLSM_EUNSUPPORTED) return rc;
   rc = clsm_conv_bwd_dx_fast(Wt, dtype, k, Dpad, L, S, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1, sort_scratch, st);

@@ -305,6 +305,7 @@ struct Dx2Params {
   int n_mt, NT, n_tiles, fblocks;
   const float* G; const int32_t* A; int ldp, col0;
   float* dX; int accumulate;
+  int dx_bf16;                 // dX rows are bf16 (overwrite mode only: the single-window case); halves the largest stream of the step
   int wstages, xrows, nreg;
   long long* prof;
 };
@@ -432,6 +433,16 @@ dx2_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const Dx2Params p) {
               for (int i = 0; i < 16; ++i) {
                 const int n = q * 16 + i;
                 if (rbeg + n < p.n_rows) atomicAdd(dst + static_cast<int64_t>(n) * p.Dpad, __uint_as_float(v[q][i]));
+              }
+            }
+          } else if (p.dx_bf16) {
+            __nv_bfloat16* dst16 = reinterpret_cast<__nv_bfloat16*>(p.dX) + rbeg * p.Dpad + c;
+#pragma unroll
+            for (int q = 0; q < NCH; ++q) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const int n = q * 16 + i;
+                if (rbeg + n < p.n_rows) dst16[static_cast<int64_t>(n) * p.Dpad] = __float2bfloat16_rn(__uint_as_float(v[q][i]));
               }
             }
           } else {
@@ -977,11 +988,25 @@ size_t clsm_conv_bwd_dx_tc_bytes(int k, int Dpad, int F) {
   return align_up(static_cast<size_t>(Dpad) * k * Fk * 2, 256);
 }
 
+// 1 when the resident-tile dX kernel (the only one that can write bf16 dX rows) takes this shape
+int clsm_conv_bwd_dx_tc_tiling2_ok(int k, int Dpad, int F, int64_t n_rows) {
+  const char* env = getenv("CLSM_CONV_BWD_DX");
+  if (env != nullptr && (env[0] == 's' || env[0] == '1')) return 0;
+  if ((Dpad + MT - 1) / MT > 4 || n_rows + 512 >= (1ll << 31)) return 0;
+  int nt = 224;
+  while (nt > 64 && nt + k - 1 > 256) nt -= 32;
+  const int xrows = (nt + k - 1 + 7) / 8 * 8;
+  const int x_slot = (xrows * 128 + 1023) / 1024 * 1024;
+  const int wstages = (SMEM_LIMIT - 2048 - ((F + 63) / 64) * x_slot) / MT_BYTES;
+  return wstages >= 3 ? 1 : 0;
+}
+
 int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64_t S, const float* G, const int32_t* A,
-                        int ldp, int col0, int F, float* dX, int accumulate, void* scratch, cudaStream_t st) {
+                        int ldp, int col0, int F, float* dX, int accumulate, int dx_bf16, void* scratch, cudaStream_t st) {
   if (dtype != CLSM_BF16) return CLSM_EUNSUPPORTED;
   const char* env = getenv("CLSM_CONV_BWD_DX");
   if (env != nullptr && env[0] == 's') return CLSM_EUNSUPPORTED;       // force the CUDA-core path
+  if (dx_bf16 && (accumulate || !clsm_conv_bwd_dx_tc_tiling2_ok(k, Dpad, F, S * L))) return CLSM_EUNSUPPORTED;
   DxParams p{};
   p.n_rows = S * L; p.L = L; p.k = k; p.F = F; p.Dpad = Dpad;
   p.n_mt = (Dpad + MT - 1) / MT;
@@ -1011,7 +1036,7 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
     while (nt > 64 && nt + k - 1 > 256) nt -= 32;
     q.n_rows = p.n_rows; q.L = L; q.k = k; q.F = F; q.Dpad = Dpad; q.n_mt = p.n_mt; q.NT = nt; q.fblocks = p.fblocks;
     q.n_tiles = static_cast<int>(ceil_div64(p.n_rows, nt));
-    q.G = G; q.A = A; q.ldp = ldp; q.col0 = col0; q.dX = dX; q.accumulate = accumulate;
+    q.G = G; q.A = A; q.ldp = ldp; q.col0 = col0; q.dX = dX; q.accumulate = accumulate; q.dx_bf16 = dx_bf16;
     q.xrows = (nt + k - 1 + 7) / 8 * 8;
     q.nreg = 512 / nt; if (q.nreg > 4) q.nreg = 4;
     const int x_slot = (q.xrows * 128 + 1023) / 1024 * 1024;

@@ -15,7 +15,8 @@ emb_gather_kernel(const int32_t* __restrict__ tok, int64_t n_tok, const uint4* _
                   int ld_table_v,         // table row pitch in uint4
                   int in_vec_valid,       // valid uint4 per table row (ld_table*esize/16)
                   uint4* __restrict__ X, int out_blocks, int ldx_v,
-                  float inv_keep, uint32_t thr, uint64_t seed) {
+                  float inv_keep, uint32_t thr, uint64_t seed,
+                  uint16_t* __restrict__ mask_bits) {    // optional (n_tok, out_blocks): bit c = column 16*blk + c kept
   constexpr int VPB = BF16 ? 2 : 4;       // uint4 per 16-column block
   const int64_t item = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const int64_t total = n_tok * out_blocks;
@@ -33,6 +34,12 @@ emb_gather_kernel(const int32_t* __restrict__ tok, int64_t n_tok, const uint4* _
   if (DROPOUT) {
     uint32_t bytes[4];
     dropout_bytes16(seed, static_cast<uint64_t>(r), static_cast<uint32_t>(blk), bytes);
+    if (mask_bits != nullptr) {              // the backward reads these bits instead of regenerating the stream
+      uint32_t w = 0;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) w |= dropout_keep(bytes, c, thr) ? (1u << c) : 0u;
+      mask_bits[item] = static_cast<uint16_t>(w);
+    }
     if (BF16) {
       __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(v);
 #pragma unroll
@@ -50,6 +57,13 @@ emb_gather_kernel(const int32_t* __restrict__ tok, int64_t n_tok, const uint4* _
   uint4* dst = X + r * ldx_v + blk * VPB;
 #pragma unroll
   for (int i = 0; i < VPB; ++i) dst[i] = v[i];
+}
+
+__global__ void check_ids_kernel(const int32_t* __restrict__ tok, int64_t n, int64_t n_rows, int32_t* __restrict__ n_bad) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const bool bad = i < n && (tok[i] < 0 || tok[i] >= n_rows);
+  const unsigned m = __ballot_sync(0xffffffffu, bad);
+  if ((threadIdx.x & 31) == 0 && m != 0) atomicAdd(n_bad, __popc(m));
 }
 
 __global__ void dropout_mask_kernel(int64_t n_tok, int D, uint32_t thr, uint64_t seed, uint8_t* mask) {
@@ -93,9 +107,9 @@ __global__ void pack_conv_w_kernel(const float* __restrict__ W, int k, int D, in
 
 extern "C" {
 
-int clsm_emb_gather(const int32_t* tok, int64_t n_tok, const void* table, int64_t n_rows,
-                    int D, int ld_table, int dtype, void* X, int ldx,
-                    float keep, uint64_t seed, void* stream) {
+static int emb_gather_impl(const int32_t* tok, int64_t n_tok, const void* table, int64_t n_rows,
+                           int D, int ld_table, int dtype, void* X, int ldx,
+                           float keep, uint64_t seed, uint16_t* mask_bits, void* stream) {
   CLSM_REQUIRE(dtype == CLSM_BF16 || dtype == CLSM_F32, "emb_gather: bad dtype %d", dtype);
   CLSM_REQUIRE(n_tok >= 0 && n_rows > 0 && D > 0 && ld_table >= D && ldx >= D, "emb_gather: bad sizes");
   const int es = dtype == CLSM_BF16 ? 2 : 4;
@@ -109,21 +123,46 @@ int clsm_emb_gather(const int32_t* tok, int64_t n_tok, const void* table, int64_
   const int64_t total = n_tok * out_blocks;
   const unsigned grid = static_cast<unsigned>(ceil_div64(total, 256));
   const bool drop = keep < 1.0f;
-  const float inv_keep = 1.0f / keep;
   const uint32_t thr = keep_threshold(keep);
+  CLSM_REQUIRE(!drop || thr > 0, "emb_gather: keep %g rounds to a keep probability of 0/256", keep);
+  const float inv_keep = drop ? dropout_scale(keep) : 1.0f;          // 1 / the REALISED keep probability thr/256
   const uint4* t = static_cast<const uint4*>(table);
   uint4* x = static_cast<uint4*>(X);
   cudaStream_t st = as_stream(stream);
   if (dtype == CLSM_BF16) {
-    if (drop) emb_gather_kernel<true, true><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed);
-    else      emb_gather_kernel<true, false><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed);
+    if (drop) emb_gather_kernel<true, true><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed, mask_bits);
+    else      emb_gather_kernel<true, false><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed, nullptr);
   } else {
-    if (drop) emb_gather_kernel<false, true><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed);
-    else      emb_gather_kernel<false, false><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed);
+    if (drop) emb_gather_kernel<false, true><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed, mask_bits);
+    else      emb_gather_kernel<false, false><<<grid, 256, 0, st>>>(tok, n_tok, t, in_blocks, vec_per_row_in, vec_per_row_in, x, out_blocks, ldx * es / 16, inv_keep, thr, seed, nullptr);
   }
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
 }
+
+int clsm_emb_gather(const int32_t* tok, int64_t n_tok, const void* table, int64_t n_rows,
+                    int D, int ld_table, int dtype, void* X, int ldx,
+                    float keep, uint64_t seed, void* stream) {
+  return emb_gather_impl(tok, n_tok, table, n_rows, D, ld_table, dtype, X, ldx, keep, seed, nullptr, stream);
+}
+
+int clsm_emb_gather_mask(const int32_t* tok, int64_t n_tok, const void* table, int64_t n_rows,
+                         int D, int ld_table, int dtype, void* X, int ldx,
+                         float keep, uint64_t seed, uint16_t* mask_bits, void* stream) {
+  return emb_gather_impl(tok, n_tok, table, n_rows, D, ld_table, dtype, X, ldx, keep, seed, mask_bits, stream);
+}
+
+int clsm_check_token_ids(const int32_t* tok, int64_t n_tok, int64_t n_rows, int32_t* n_bad, void* stream) {
+  CLSM_REQUIRE(n_tok >= 0 && n_rows > 0 && n_bad != nullptr, "check_token_ids: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  CLSM_CUDA(cudaMemsetAsync(n_bad, 0, sizeof(int32_t), st));
+  if (n_tok == 0) return CLSM_OK;
+  check_ids_kernel<<<static_cast<unsigned>(ceil_div64(n_tok, 256)), 256, 0, st>>>(tok, n_tok, n_rows, n_bad);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+float clsm_dropout_scale(float keep) { return keep < 1.0f ? dropout_scale(keep) : 1.0f; }
 
 int clsm_emb_gather_h(const int32_t* tok_h, int32_t* tok_d, int64_t n_tok, const void* table,
                       int64_t n_rows, int D, int ld_table, int dtype, void* X, int ldx,

@@ -42,12 +42,15 @@ __global__ void segments_kernel(const int32_t* __restrict__ st, const int32_t* _
 }
 
 // level 0: one CTA per chunk of CH sorted entries; thread = one float4 column of the row.
-template <bool DROPOUT>
+// MASK: 0 = no dropout, 1 = regenerate the Philox stream of the forward, 2 = read the 1-bit-per-element mask the
+// forward gather stored (mask_bits (n_tok, ncol4 / 4) uint16, bit c of word (row, blk) = column 16 blk + c kept).
+// DXBF16: dX rows are bf16 (the single-window tensor-core backward writes them so); sums stay fp32.
+template <int MASK, bool DXBF16>
 __global__ void __launch_bounds__(128)
 seg_reduce_l0_kernel(const int32_t* __restrict__ spos, const int32_t* __restrict__ seg,
                      const int32_t* __restrict__ seg_start, int64_t n,
-                     const float4* __restrict__ dX, int ldx4, int ncol4,
-                     float inv_keep, uint32_t thr, uint64_t seed,
+                     const void* __restrict__ dXv, int ldx4, int ncol4,
+                     float inv_keep, uint32_t thr, uint64_t seed, const uint16_t* __restrict__ mask_bits,
                      float4* __restrict__ dE, int lde4,
                      int32_t* __restrict__ slot_key, float4* __restrict__ slot_rows) {
   __shared__ int32_t s_pos[CH], s_seg[CH];
@@ -63,6 +66,7 @@ seg_reduce_l0_kernel(const int32_t* __restrict__ spos, const int32_t* __restrict
   __syncthreads();
   const int col = threadIdx.x;
   const bool active = col < ncol4;
+  const int nblk = ncol4 >> 2;
   int e = 0;
   while (e < cnt) {
     const int g = s_seg[e];
@@ -70,30 +74,42 @@ seg_reduce_l0_kernel(const int32_t* __restrict__ spos, const int32_t* __restrict
     while (e1 < cnt && s_seg[e1] == g) ++e1;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     {
-      // Dropout mask: one Philox call yields the 16 decision bytes of a (row, 16-column block); the 4 lanes
-      // that own that block's 4 float4 columns would each recompute it.  Instead lane (4b + j) computes the
-      // block for row q + j of the 4 rows in flight and the words are exchanged with shuffles: 1 call per
-      // lane per 4 rows instead of 4.  (All 32 lanes take part in the shuffles, active or not.)
       const int lane = threadIdx.x & 31;
       const int sub = lane & 3;                       // which float4 of the 16-column block this lane owns
       auto load_row = [&](int q) {
-        return active ? __ldg(dX + static_cast<int64_t>(s_pos[q]) * ldx4 + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!active) return make_float4(0.f, 0.f, 0.f, 0.f);
+        if (DXBF16) {
+          const uint2 u = __ldcs(reinterpret_cast<const uint2*>(dXv) + static_cast<int64_t>(s_pos[q]) * ldx4 + col);
+          return make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u),
+                             __uint_as_float(u.y << 16), __uint_as_float(u.y & 0xffff0000u));
+        }
+        return __ldcs(reinterpret_cast<const float4*>(dXv) + static_cast<int64_t>(s_pos[q]) * ldx4 + col);
       };
-      auto apply = [&](float4 v, uint32_t word) {
+      auto apply = [&](float4 v, uint32_t word) {                 // Philox decision bytes
         v.x = ((word & 0xffu) < thr) ? v.x * inv_keep : 0.f;
         v.y = (((word >> 8) & 0xffu) < thr) ? v.y * inv_keep : 0.f;
         v.z = (((word >> 16) & 0xffu) < thr) ? v.z * inv_keep : 0.f;
         v.w = ((word >> 24) < thr) ? v.w * inv_keep : 0.f;
         return v;
       };
+      auto apply_bits = [&](float4 v, int q) {                    // stored mask bits
+        const uint32_t w = active ? static_cast<uint32_t>(__ldg(mask_bits + static_cast<int64_t>(s_pos[q]) * nblk + (col >> 2))) >> (4 * sub) : 0u;
+        v.x = (w & 1u) ? v.x * inv_keep : 0.f;
+        v.y = (w & 2u) ? v.y * inv_keep : 0.f;
+        v.z = (w & 4u) ? v.z * inv_keep : 0.f;
+        v.w = (w & 8u) ? v.w * inv_keep : 0.f;
+        return v;
+      };
       int q = e;
       for (; q + 4 <= e1; q += 4) {            // 4 independent row loads in flight, added in order
         float4 v0 = load_row(q), v1 = load_row(q + 1), v2 = load_row(q + 2), v3 = load_row(q + 3);
-        if (DROPOUT) {
+        if (MASK == 1) {
+          // One Philox call yields the 16 decision bytes of a (row, 16-column block); the 4 lanes that own that
+          // block's 4 float4 columns would each recompute it.  Instead lane (4b + j) computes the block for row
+          // q + j of the 4 rows in flight and the words are exchanged with shuffles: 1 call per lane per 4 rows.
           uint32_t bytes[4];
           dropout_bytes16(seed, static_cast<uint64_t>(s_pos[q + sub]), static_cast<uint32_t>(col >> 2), bytes);
           const int base = lane & ~3;
-          // row q+j's bytes live in lane base+j; this lane needs word `sub` of each
           uint32_t w[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -102,6 +118,8 @@ seg_reduce_l0_kernel(const int32_t* __restrict__ spos, const int32_t* __restrict
             w[j] = sub == 0 ? b0 : sub == 1 ? b1 : sub == 2 ? b2 : b3;
           }
           v0 = apply(v0, w[0]); v1 = apply(v1, w[1]); v2 = apply(v2, w[2]); v3 = apply(v3, w[3]);
+        } else if (MASK == 2) {
+          v0 = apply_bits(v0, q); v1 = apply_bits(v1, q + 1); v2 = apply_bits(v2, q + 2); v3 = apply_bits(v3, q + 3);
         }
         acc.x += v0.x; acc.y += v0.y; acc.z += v0.z; acc.w += v0.w;
         acc.x += v1.x; acc.y += v1.y; acc.z += v1.z; acc.w += v1.w;
@@ -110,10 +128,12 @@ seg_reduce_l0_kernel(const int32_t* __restrict__ spos, const int32_t* __restrict
       }
       for (; q < e1; ++q) {
         float4 v = load_row(q);
-        if (DROPOUT) {
+        if (MASK == 1) {
           uint32_t bytes[4];
           dropout_bytes16(seed, static_cast<uint64_t>(s_pos[q]), static_cast<uint32_t>(col >> 2), bytes);
           v = apply(v, bytes[sub]);
+        } else if (MASK == 2) {
+          v = apply_bits(v, q);
         }
         acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       }
@@ -225,13 +245,14 @@ size_t clsm_emb_scatter_workspace_bytes(int64_t n_tok, int D) {
   return make_plan(n_tok, Dpad / 4).total;
 }
 
-int clsm_emb_scatter(const int32_t* tok, int64_t n_tok, const float* dX, int Dpad, int D,
-                     float keep, uint64_t seed, int64_t n_rows,
-                     int32_t* uniq_ids, int32_t* n_uniq_out, float* dE_rows, int32_t* row_of_id,
-                     void* ws, size_t ws_bytes, void* stream) {
+// plan: everything that depends on the token ids alone (sort, segments, unique ids, row_of_id).  It does not need
+// dX, so a host can run it at the START of the step on another stream, underneath the forward pass.
+int clsm_emb_scatter_plan(const int32_t* tok, int64_t n_tok, int Dpad, int D, int64_t n_rows,
+                          int32_t* uniq_ids, int32_t* n_uniq_out, int32_t* row_of_id,
+                          void* ws, size_t ws_bytes, void* stream) {
   CLSM_REQUIRE(n_tok > 0 && n_tok < (1ll << 31), "emb_scatter: n_tok out of range");
   CLSM_REQUIRE(Dpad == (D + 63) / 64 * 64 && Dpad <= 512, "emb_scatter: Dpad must be D rounded up to 64 (<= 512)");
-  CLSM_REQUIRE(keep > 0.0f && n_rows > 0, "emb_scatter: bad keep / n_rows");
+  CLSM_REQUIRE(n_rows > 0, "emb_scatter: bad n_rows");
   const int ncol4 = Dpad / 4;
   const ScatterPlan p = make_plan(n_tok, ncol4);
   if (ws_bytes < p.total) {
@@ -264,20 +285,44 @@ int clsm_emb_scatter(const int32_t* tok, int64_t n_tok, const float* dX, int Dpa
   CLSM_CUDA(cub::DeviceScan::InclusiveSum(cub_ws, cb, head, seg, n, st));
   segments_kernel<<<g256, 256, 0, st>>>(keys_out, head, seg, n_tok, uniq_ids, seg_start, row_of_id, n_uniq_out);
   CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+// reduce: the segmented sum over dX, on the plan left in `ws` by clsm_emb_scatter_plan for the same tokens.
+int clsm_emb_scatter_reduce(int64_t n_tok, const void* dX, int dx_dtype, int Dpad, int D,
+                            float keep, uint64_t seed, const uint16_t* mask_bits, float* dE_rows,
+                            void* ws, size_t ws_bytes, void* stream) {
+  CLSM_REQUIRE(n_tok > 0 && n_tok < (1ll << 31), "emb_scatter: n_tok out of range");
+  CLSM_REQUIRE(Dpad == (D + 63) / 64 * 64 && Dpad <= 512, "emb_scatter: Dpad must be D rounded up to 64 (<= 512)");
+  CLSM_REQUIRE(dx_dtype == CLSM_F32 || dx_dtype == CLSM_BF16, "emb_scatter: dX must be fp32 or bf16");
+  CLSM_REQUIRE(keep > 0.0f, "emb_scatter: bad keep");
+  const int ncol4 = Dpad / 4;
+  const ScatterPlan p = make_plan(n_tok, ncol4);
+  if (ws_bytes < p.total) {
+    clsm_set_error("emb_scatter: workspace too small (%zu < %zu)", ws_bytes, p.total);
+    return CLSM_EWORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  char* w = static_cast<char*>(ws);
+  const int32_t* vals_out = reinterpret_cast<const int32_t*>(w + p.off_vals_out);
+  const int32_t* seg = reinterpret_cast<const int32_t*>(w + p.off_seg);
+  const int32_t* seg_start = reinterpret_cast<const int32_t*>(w + p.off_seg_start);
 
   const int threads = (ncol4 + 31) / 32 * 32 < 64 ? 64 : (ncol4 + 31) / 32 * 32;
   int32_t* skey[2] = {reinterpret_cast<int32_t*>(w + p.off_slot_key[0]), reinterpret_cast<int32_t*>(w + p.off_slot_key[1])};
   float4* srow[2] = {reinterpret_cast<float4*>(w + p.off_slot_rows[0]), reinterpret_cast<float4*>(w + p.off_slot_rows[1])};
   const int64_t chunks0 = ceil_div64(n_tok, CH);
   const bool drop = keep < 1.0f;
-  const float4* dX4 = reinterpret_cast<const float4*>(dX);
+  const int mask = !drop ? 0 : (mask_bits != nullptr ? 2 : 1);
+  const float inv_keep = drop ? dropout_scale(keep) : 1.0f;
+  const uint32_t thr = drop ? keep_threshold(keep) : 256u;
   float4* dE4 = reinterpret_cast<float4*>(dE_rows);
-  if (drop)
-    seg_reduce_l0_kernel<true><<<static_cast<unsigned>(chunks0), threads, 0, st>>>(vals_out, seg, seg_start, n_tok, dX4, ncol4, ncol4,
-        1.0f / keep, keep_threshold(keep), seed, dE4, ncol4, skey[0], srow[0]);
-  else
-    seg_reduce_l0_kernel<false><<<static_cast<unsigned>(chunks0), threads, 0, st>>>(vals_out, seg, seg_start, n_tok, dX4, ncol4, ncol4,
-        1.0f, 256u, seed, dE4, ncol4, skey[0], srow[0]);
+  const unsigned g0 = static_cast<unsigned>(chunks0);
+#define L0(M, B) seg_reduce_l0_kernel<M, B><<<g0, threads, 0, st>>>(vals_out, seg, seg_start, n_tok, dX, ncol4, ncol4, \
+        inv_keep, thr, seed, mask_bits, dE4, ncol4, skey[0], srow[0])
+  if (dx_dtype == CLSM_BF16) { if (mask == 0) L0(0, true); else if (mask == 1) L0(1, true); else L0(2, true); }
+  else { if (mask == 0) L0(0, false); else if (mask == 1) L0(1, false); else L0(2, false); }
+#undef L0
   CLSM_LAUNCH_CHECK();
   // higher levels ping-pong between the two slot buffers
   int64_t n_chunks_prev = chunks0;
@@ -295,6 +340,16 @@ int clsm_emb_scatter(const int32_t* tok, int64_t n_tok, const float* dX, int Dpa
     src = dst;
   }
   return CLSM_OK;
+}
+
+int clsm_emb_scatter(const int32_t* tok, int64_t n_tok, const float* dX, int Dpad, int D,
+                     float keep, uint64_t seed, int64_t n_rows,
+                     int32_t* uniq_ids, int32_t* n_uniq_out, float* dE_rows, int32_t* row_of_id,
+                     void* ws, size_t ws_bytes, void* stream) {
+  CLSM_REQUIRE(keep > 0.0f && n_rows > 0, "emb_scatter: bad keep / n_rows");
+  const int rc = clsm_emb_scatter_plan(tok, n_tok, Dpad, D, n_rows, uniq_ids, n_uniq_out, row_of_id, ws, ws_bytes, stream);
+  if (rc != CLSM_OK) return rc;
+  return clsm_emb_scatter_reduce(n_tok, dX, CLSM_F32, Dpad, D, keep, seed, nullptr, dE_rows, ws, ws_bytes, stream);
 }
 
 }  // extern "C"

@@ -164,7 +164,13 @@ class Tower(object):
         if train:
             b["dsem"] = torch.empty((S, self.H), dtype=torch.float32, device=dev)
             b["G"] = torch.empty((S, self.P), dtype=torch.float32, device=dev)
-            b["dX"] = torch.empty((n_tok, self.Dpad), dtype=torch.float32, device=dev)
+            # dX rows: bf16 when ONE window size writes them from the tensor-core kernel (the largest stream of the step,
+            # halved); fp32 when several windows accumulate into them or the CUDA-core kernels run
+            dx16 = (self.bf16 and len(self.windows) == 1 and self.net.conv_impl != "simt" and
+                    lib.clsm_conv_bwd_dx_bf16_ok(S, self.L, self.windows[0], self.D, self.F) == 1)
+            b["dx_dtype"] = BF16 if dx16 else F32
+            b["dX"] = torch.empty((n_tok, self.Dpad), dtype=torch.bfloat16 if dx16 else torch.float32, device=dev)
+            b["mask"] = torch.empty((n_tok, self.Dpad // 16), dtype=torch.int16, device=dev)       # 1 keep bit per element
             max_u = min(n_tok, self.V1)
             b["uniq"] = torch.empty(n_tok, dtype=torch.int32, device=dev)
             b["n_uniq"] = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -172,10 +178,13 @@ class Tower(object):
             b["row_of_id"] = torch.empty(self.V1, dtype=torch.int32, device=dev)
             ws = max(
                 lib.clsm_dense_bwd_workspace_bytes(S, self.P, self.H),
-                max(lib.clsm_conv_bwd_workspace_bytes(S, self.L, k, self.D, self.F) for k in self.windows),
-                lib.clsm_emb_scatter_workspace_bytes(n_tok, self.D))
+                max(lib.clsm_conv_bwd_workspace_bytes(S, self.L, k, self.D, self.F) for k in self.windows))
             b["ws"] = torch.empty(ws, dtype=torch.uint8, device=dev)
             b["ws_bytes"] = ws
+            # the scatter's plan (sort + segments) is made early in the step and must survive until its reduce
+            b["ws_sc_bytes"] = lib.clsm_emb_scatter_workspace_bytes(n_tok, self.D)
+            b["ws_sc"] = torch.empty(b["ws_sc_bytes"], dtype=torch.uint8, device=dev)
+            b["planned"] = False
         self._bufs[key] = b
         return b
 
@@ -187,8 +196,8 @@ class Tower(object):
         keep = 1.0 - net.params.dropout_prob[0] if train else 1.0
         table = self.E_c if self.bf16 else self.E
         ld_table = self.Dpad if self.bf16 else self.D
-        call("clsm_emb_gather", _ptr(b["tok"]), n_tok, _ptr(table), self.V1, self.D, ld_table,
-             self.dtype_code, _ptr(b["X"]), self.Dpad, keep, seed, st)
+        call("clsm_emb_gather_mask", _ptr(b["tok"]), n_tok, _ptr(table), self.V1, self.D, ld_table,
+             self.dtype_code, _ptr(b["X"]), self.Dpad, keep, seed, _ptr(b["mask"]) if (train and keep < 1.0) else C.c_void_p(0), st)
         for i, k in enumerate(self.windows):
             call("clsm_conv_pool_fwd", _ptr(b["X"]), self.dtype_code, S, self.L, self.Dpad, _ptr(self.Wt[i]),
                  k, self.F, self.Fpad, _ptr(b["keys"]), self.P, i * self.F, IMPL[net.conv_impl], st)
@@ -210,13 +219,23 @@ class Tower(object):
              _ptr(b["ws"]), b["ws_bytes"], st)
         for i, k in enumerate(self.windows):
             gb = self.g_convb[i * self.F:(i + 1) * self.F]
-            call("clsm_conv_pool_bwd", _ptr(b["X"]), self.dtype_code, S, self.L, self.D, self.Dpad, _ptr(self.Wt[i]),
+            call("clsm_conv_pool_bwd_ex", _ptr(b["X"]), self.dtype_code, S, self.L, self.D, self.Dpad, _ptr(self.Wt[i]),
                  k, self.F, self.Fpad, _ptr(b["G"]), _ptr(b["argmax"]), self.P, i * self.F,
-                 _ptr(self.g_convW[i]), _ptr(gb), _ptr(b["dX"]), 1 if i == 0 else 0,
+                 _ptr(self.g_convW[i]), _ptr(gb), _ptr(b["dX"]), b["dx_dtype"], 1 if i == 0 else 0,
                  _ptr(b["ws"]), b["ws_bytes"], st)
-        call("clsm_emb_scatter", _ptr(b["tok"]), n_tok, _ptr(b["dX"]), self.Dpad, self.D, b["keep"], b["seed"],
-             self.V1, _ptr(b["uniq"]), _ptr(b["n_uniq"]), _ptr(b["dE_rows"]), _ptr(b["row_of_id"]),
-             _ptr(b["ws"]), b["ws_bytes"], st)
+        if not b["planned"]:
+            self.plan_scatter(b)
+        b["planned"] = False
+        use_bits = b["keep"] < 1.0
+        call("clsm_emb_scatter_reduce", n_tok, _ptr(b["dX"]), b["dx_dtype"], self.Dpad, self.D, b["keep"], b["seed"],
+             _ptr(b["mask"]) if use_bits else C.c_void_p(0), _ptr(b["dE_rows"]), _ptr(b["ws_sc"]), b["ws_sc_bytes"], st)
+
+    def plan_scatter(self, b):
+        """The id-only half of the embedding-gradient scatter (sort, segments, unique ids): needs no gradient, so
+        step_resident issues it at the start of the step on its own stream, underneath the forward pass."""
+        call("clsm_emb_scatter_plan", _ptr(b["tok"]), b["n_tok"], self.Dpad, self.D, self.V1, _ptr(b["uniq"]),
+             _ptr(b["n_uniq"]), _ptr(b["row_of_id"]), _ptr(b["ws_sc"]), b["ws_sc_bytes"], _stream())
+        b["planned"] = True
 
     def adam(self, b, step, sparse_grad=None):
         """sparse_grad: optional (row_of_id, dE_rows, uniq, n_uniq) replacing this rank's own
@@ -317,6 +336,7 @@ class CLSM(object):
         import os
         self.overlap = os.environ.get("CLSM_OVERLAP", "1") != "0"      # two-stream step, see step_resident
         self._side = None
+        self._plan_stream = None
         self._probe = None             # scripts/overlap_probe.py: events around the two towers' post-loss work
         self._head = {}
         self._pinned = {}
@@ -405,11 +425,25 @@ class CLSM(object):
         deterministic and the towers share no buffer, so the weights are bit-identical to the one-stream order
         (CLSM_OVERLAP=0 selects it; tests/test_gpu_model.py compares the two)."""
         sq, sd = self._seeds()
+        if self.overlap:
+            # the scatters' plans (sort of the token ids, segments) on their own stream, under the forward pass
+            main = torch.cuda.current_stream()
+            if self._plan_stream is None:
+                self._plan_stream = torch.cuda.Stream(device=self.device)
+                self._ev_tok, self._ev_plan = torch.cuda.Event(), torch.cuda.Event()
+            self._ev_tok.record(main)
+            self._plan_stream.wait_event(self._ev_tok)
+            with torch.cuda.stream(self._plan_stream):
+                self.doc_model.plan_scatter(bd)
+                self.query_model.plan_scatter(bq)
+                self._ev_plan.record(self._plan_stream)
         self.query_model.forward(bq, True, sq)
         self.doc_model.forward(bd, True, sd)
         bt = B * (self.dp.world if self.dp is not None else 1)
         h = self._forward_head(B, bq, bd, True, bt)
         self.iterations += 1
+        if self.overlap:
+            main.wait_event(self._ev_plan)
         if self.dp is not None:
             self.query_model.backward(bq)
             self.doc_model.backward(bd)

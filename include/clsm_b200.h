@@ -54,12 +54,25 @@ void clsm_debug_mark_conv_bwd(void* ev_after_dw, void* ev_before_dx);
  * keep >= 1 disables dropout.  mask(r, c) is a counter-based Bernoulli(keep) bit that is a
  * pure function of (seed, r, c) -- clsm_dropout_mask exports it for the oracle.
  * dtype: CLSM_BF16 (table and X bf16) or CLSM_F32 (both fp32).  Rows must be 16-byte aligned
- * (ld_table*esize and ldx*esize multiples of 16).  Returns CLSM_EINVAL for a token id outside
- * [0, n_rows) only in debug builds; ids are trusted otherwise, as Keras trusts them. */
+ * (ld_table*esize and ldx*esize multiples of 16).  Token ids are trusted to lie in [0, n_rows), as Keras
+ * trusts them (an id outside is an out-of-bounds read); clsm_check_token_ids validates a batch when the feeder is
+ * not trusted. */
 int clsm_emb_gather(const int32_t* tok, int64_t n_tok, const void* table, int64_t n_rows,
                     int D, int ld_table, int dtype, void* X, int ldx,
                     float keep, uint64_t seed, void* stream);
 int clsm_dropout_mask(int64_t n_tok, int D, float keep, uint64_t seed, uint8_t* mask, void* stream);
+/* n_bad[0] (device) <- how many of tok[0:n_tok] lie outside [0, n_rows).  Asynchronous; the caller reads the count. */
+int clsm_check_token_ids(const int32_t* tok, int64_t n_tok, int64_t n_rows, int32_t* n_bad, void* stream);
+/* clsm_emb_gather that also stores the keep decisions it applied, 1 bit per element: mask_bits (n_tok, ldx / 16)
+ * uint16, bit c of word (r, b) = column 16 b + c of row r kept.  clsm_emb_scatter_reduce reads them back, so the
+ * backward pass does not regenerate the random stream.  mask_bits may be NULL (then identical to clsm_emb_gather).
+ * The keep probability is realised in steps of 1/256 (threshold t = round(256 keep), P(keep) = t / 256) and kept
+ * values are scaled by 256 / t = clsm_dropout_scale(keep), the inverse of the REALISED probability, so the expectation
+ * is exact for every keep; the reference's 0.75 (cnn_dssm_tf.py:37) is t = 192, scale 4/3. */
+int clsm_emb_gather_mask(const int32_t* tok, int64_t n_tok, const void* table, int64_t n_rows,
+                         int D, int ld_table, int dtype, void* X, int ldx,
+                         float keep, uint64_t seed, uint16_t* mask_bits, void* stream);
+float clsm_dropout_scale(float keep);
 
 /* ---- conv weights: reference layout -> compute layout ------------------------------------
  * W_ref fp32 (k, D, F)  [Keras-1 Convolution1D kernel (k,1,D,F), cnn_dssm_tf.py:85-91]
@@ -126,6 +139,19 @@ int clsm_conv_pool_bwd(const void* X, int dtype, int64_t S, int L, int D, int Dp
                        float* dW_ref, float* db, float* dX, int first_window,
                        void* ws, size_t ws_bytes, void* stream);
 
+/* Same, with a choice of dX format.  dx_dtype CLSM_BF16 stores dX rows as bf16 (S*L, Dpad): the tensor-core dX
+ * kernel rounds its fp32 accumulators once on the way out, which halves the largest memory stream of a training step
+ * (written here, read once by clsm_emb_scatter_reduce, which still sums in fp32).  Only with dtype CLSM_BF16,
+ * first_window = 1 (one window size: later windows ADD into dX and need fp32) and a shape for which
+ * clsm_conv_bwd_dx_bf16_ok() returns 1; CLSM_EUNSUPPORTED otherwise.  (No counterpart in the reference: Keras keeps
+ * every gradient in the model's float type.) */
+int clsm_conv_bwd_dx_bf16_ok(int64_t S, int L, int k, int D, int F);
+int clsm_conv_pool_bwd_ex(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
+                          const void* Wt, int k, int F, int Fpad,
+                          const float* G, const int32_t* argmax, int ldp, int col0,
+                          float* dW_ref, float* db, void* dX, int dx_dtype, int first_window,
+                          void* ws, size_t ws_bytes, void* stream);
+
 /* ---- embedding gradient: deterministic sort + segmented reduce -------------------------------
  * replaces the gradient of Embedding (AdvancedIncSubtensor1 / UnsortedSegmentSum).
  * dX (n_tok, Dpad) fp32; if keep < 1 the dropout mask of the forward is re-applied.
@@ -138,6 +164,20 @@ int clsm_emb_scatter(const int32_t* tok, int64_t n_tok, const float* dX, int Dpa
                      float keep, uint64_t seed, int64_t n_rows,
                      int32_t* uniq_ids, int32_t* n_uniq_out, float* dE_rows, int32_t* row_of_id,
                      void* ws, size_t ws_bytes, void* stream);
+
+/* The same in two halves, for hosts that overlap them with other work.
+ * clsm_emb_scatter_plan: everything that depends on the token ids alone (stable sort, segments, uniq_ids, n_uniq_out,
+ *   row_of_id); it needs no gradient, so it can run at the start of the step on another stream, under the forward pass.
+ * clsm_emb_scatter_reduce: the segmented sum over dX (dx_dtype CLSM_F32 or CLSM_BF16 rows, fp32 sums) into dE_rows, on
+ *   the plan that the SAME workspace holds for the same tokens.  Dropout (keep < 1): mask_bits != NULL reads the
+ *   1-bit-per-element mask clsm_emb_gather_mask stored in the forward, NULL regenerates the stream from seed.
+ * clsm_emb_scatter == plan + reduce(fp32 dX, regenerated mask): bit-identical results. */
+int clsm_emb_scatter_plan(const int32_t* tok, int64_t n_tok, int Dpad, int D, int64_t n_rows,
+                          int32_t* uniq_ids, int32_t* n_uniq_out, int32_t* row_of_id,
+                          void* ws, size_t ws_bytes, void* stream);
+int clsm_emb_scatter_reduce(int64_t n_tok, const void* dX, int dx_dtype, int Dpad, int D,
+                            float keep, uint64_t seed, const uint16_t* mask_bits, float* dE_rows,
+                            void* ws, size_t ws_bytes, void* stream);
 
 /* ---- optimizer -----------------------------------------------------------------------------
  * replaces optimizer="adam" (Keras-1 Adam, cnn_dssm_tf.py:182):

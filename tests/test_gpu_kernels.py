@@ -385,6 +385,108 @@ def test_emb_scatter_reapplies_dropout_mask():
     np.testing.assert_allclose(r[:, :D], want[u], rtol=2e-5, atol=2e-5)
 
 
+def test_mask_bits_bf16_dx_and_split_scatter_equal_the_one_call_path():
+    """The training path's variants: clsm_emb_gather_mask stores the keep decisions as bits, clsm_emb_scatter_plan /
+    _reduce split the scatter and read those bits (no Philox in the backward), dX may arrive as bf16.  With fp32 dX
+    the split path must be BIT-IDENTICAL to clsm_emb_scatter (same tree, same order); with bf16 dX it must equal the
+    one-call path fed the bf16-rounded dX."""
+    rng = np.random.RandomState(8)
+    n_tok, V1, D, keep, seed = 70001, 300, 100, 0.75, 4242
+    Dpad = rup(D, 64)
+    E = rng.uniform(-0.25, 0.25, size=(V1, D)).astype(np.float32)
+    tok = rng.randint(0, V1, size=n_tok).astype(np.int32)
+    tok[rng.rand(n_tok) < 0.4] = 7
+    tok_d, E_d = dev(tok), dev(E)
+    table = torch.zeros((V1, Dpad), dtype=torch.bfloat16, device=DEV)
+    call("clsm_table_to_bf16", P(E_d), V1, D, P(table), Dpad, ST())
+    X1 = torch.empty((n_tok, Dpad), dtype=torch.bfloat16, device=DEV)
+    X2 = torch.empty_like(X1)
+    bits = torch.zeros((n_tok, Dpad // 16), dtype=torch.int16, device=DEV)
+    call("clsm_emb_gather", P(tok_d), n_tok, P(table), V1, D, Dpad, BF16, P(X1), Dpad, keep, seed, ST())
+    call("clsm_emb_gather_mask", P(tok_d), n_tok, P(table), V1, D, Dpad, BF16, P(X2), Dpad, keep, seed, P(bits), ST())
+    assert torch.equal(X1, X2)
+    mask = torch.empty((n_tok, D), dtype=torch.uint8, device=DEV)
+    call("clsm_dropout_mask", n_tok, D, keep, seed, P(mask), ST())
+    b = bits.cpu().numpy().view(np.uint16)
+    unpacked = ((b[:, :, None] >> np.arange(16, dtype=np.uint16)[None, None, :]) & 1).reshape(n_tok, Dpad)[:, :D]
+    np.testing.assert_array_equal(unpacked, mask.cpu().numpy())
+    assert abs(lib.clsm_dropout_scale(0.75) - 4.0 / 3.0) < 1e-7 and abs(lib.clsm_dropout_scale(0.9) - 256.0 / 230.0) < 1e-7
+    # scatter: one call (Philox regenerated) vs plan + reduce (stored bits)
+    dXn = np.zeros((n_tok, Dpad), dtype=np.float32); dXn[:, :D] = rng.randn(n_tok, D)
+    dX_d = dev(dXn)
+    u1, r1, roi1 = run_scatter(tok_d, dX_d, D, V1, keep, seed)
+
+    def split(dX_t, code):
+        wsb = lib.clsm_emb_scatter_workspace_bytes(n_tok, D)
+        ws = torch.full((wsb,), 0xA5, dtype=torch.uint8, device=DEV)
+        uniq = torch.full((n_tok,), -7, dtype=torch.int32, device=DEV)
+        nu = torch.zeros(1, dtype=torch.int32, device=DEV)
+        rows = torch.full((min(n_tok, V1), Dpad), 9.0, dtype=torch.float32, device=DEV)
+        roi = torch.empty(V1, dtype=torch.int32, device=DEV)
+        call("clsm_emb_scatter_plan", P(tok_d), n_tok, Dpad, D, V1, P(uniq), P(nu), P(roi), P(ws), wsb, ST())
+        call("clsm_emb_scatter_reduce", n_tok, P(dX_t), code, Dpad, D, keep, seed, P(bits), P(rows), P(ws), wsb, ST())
+        n = int(nu.item())
+        return uniq[:n].cpu().numpy(), rows[:n].cpu().numpy(), roi.cpu().numpy()
+    u2, r2, roi2 = split(dX_d, F32)
+    assert np.array_equal(u1, u2) and np.array_equal(roi1, roi2) and np.array_equal(r1, r2)
+    dX16 = dX_d.to(torch.bfloat16)
+    u3, r3, _ = split(dX16, BF16)
+    _, r4, _ = run_scatter(tok_d, dX16.float(), D, V1, keep, seed)
+    assert np.array_equal(u1, u3) and np.array_equal(r3, r4)
+    # id validation
+    bad = torch.zeros(1, dtype=torch.int32, device=DEV)
+    call("clsm_check_token_ids", P(tok_d), n_tok, V1, P(bad), ST())
+    assert int(bad.item()) == 0
+    tok2 = tok.copy(); tok2[5] = V1; tok2[77] = -1; tok2[n_tok - 1] = 1 << 30
+    call("clsm_check_token_ids", P(dev(tok2)), n_tok, V1, P(bad), ST())
+    assert int(bad.item()) == 3
+
+
+def test_gather_scales_by_the_realised_keep_probability():
+    """keep is realised in steps of 1/256: 0.9 -> 230/256.  Kept values are scaled by 256/230, not 1/0.9."""
+    rng = np.random.RandomState(9)
+    V1, D, n_tok, keep, seed = 50, 64, 2000, 0.9, 5
+    E = rng.uniform(-1, 1, size=(V1, D)).astype(np.float32)
+    tok = rng.randint(0, V1, size=n_tok).astype(np.int32)
+    X = torch.empty((n_tok, 64), dtype=torch.float32, device=DEV)
+    mask = torch.empty((n_tok, D), dtype=torch.uint8, device=DEV)
+    E_d, tok_d = dev(E), dev(tok)
+    call("clsm_emb_gather", P(tok_d), n_tok, P(E_d), V1, D, D, F32, P(X), 64, keep, seed, ST())
+    call("clsm_dropout_mask", n_tok, D, keep, seed, P(mask), ST())
+    m = mask.cpu().numpy().astype(np.float32)
+    assert abs(m.mean() - 230.0 / 256.0) < 0.01
+    np.testing.assert_array_equal(X.cpu().numpy(), E[tok] * m * np.float32(256.0 / 230.0))
+
+
+@pytest.mark.parametrize("shape", [(70, 100, 300, 3, 300), (5, 1000, 100, 4, 150), (9, 12, 64, 2, 20)])
+def test_conv_bwd_bf16_dx_rows_are_the_rounded_fp32_rows(shape):
+    """clsm_conv_pool_bwd_ex with dx_dtype = bf16: the same accumulators, rounded once on the way out."""
+    S, L, D, k, F = shape
+    assert lib.clsm_conv_bwd_dx_bf16_ok(S, L, k, D, F) == 1
+    rng = np.random.RandomState(16)
+    X, W = conv_case(17, S, L, D, k, F, exact=False)
+    Dpad, Fpad = rup(D, 64), rup(F, 16)
+    G = (rng.randn(S, F) * (rng.rand(S, F) > 0.4)).astype(np.float32)
+    A = rng.randint(0, L - k + 1, size=(S, F)).astype(np.int32)
+    Xd, Wt = make_X(X, Dpad, True), pack_w(W, Dpad, Fpad, True)
+    ws_bytes = lib.clsm_conv_bwd_workspace_bytes(S, L, k, D, F)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    G_d, A_d = dev(G), dev(A)
+    outs = []
+    for code, dt in ((F32, torch.float32), (BF16, torch.bfloat16)):
+        dW = torch.empty((k, D, F), dtype=torch.float32, device=DEV)
+        db = torch.empty(F, dtype=torch.float32, device=DEV)
+        dX = torch.full((S * L, Dpad), 3.0, dtype=dt, device=DEV)
+        call("clsm_conv_pool_bwd_ex", P(Xd), BF16, S, L, D, Dpad, P(Wt), k, F, Fpad, P(G_d), P(A_d), F, 0,
+             P(dW), P(db), P(dX), code, 1, P(ws), ws_bytes, ST())
+        outs.append((dW, dX))
+    assert torch.equal(outs[0][0], outs[1][0])
+    assert torch.equal(outs[0][1].to(torch.bfloat16), outs[1][1])
+    with pytest.raises(_lib.ClsmError):                     # accumulating windows need fp32 rows
+        call("clsm_conv_pool_bwd_ex", P(Xd), BF16, S, L, D, Dpad, P(Wt), k, F, Fpad, P(G_d), P(A_d), F, 0,
+             P(outs[1][0]), P(db), P(outs[1][1]), BF16, 0, P(ws), ws_bytes, ST())
+
+
 # ------------------------------------------------------------------ Adam
 def test_adam_dense_and_table():
     rng = np.random.RandomState(9)
