@@ -323,7 +323,8 @@ def main():
         phases, launch = profile_phases(net, resident_step, torch)
         if rank == 0:
             line["kernels"] = phases
-            fill_roofline(line, c, launch, clocks, pk, steps, ms)
+            from dnn_page_vectors_b200._lib import BF16 as _BF16
+            fill_roofline(line, c, launch, clocks, pk, steps, ms, dx_bytes=2 if bd.get("dx_dtype") == _BF16 else 4)
         # ---- configs[4] at this N: sharded encode and retrieval
         try:
             line_sh = bench_sharded(net, c, torch, dist, pk, rank, world, args.shard_pages)
@@ -352,8 +353,9 @@ def main():
     return 0
 
 
-def fill_roofline(line, c, launch, clocks, pk, steps, ms):
-    """launch: {kernel: directly measured device ms of ONE launch of the document tower (or of one table)}."""
+def fill_roofline(line, c, launch, clocks, pk, steps, ms, dx_bytes=4):
+    """launch: {kernel: directly measured device ms of ONE launch of the document tower (or of one table)}.
+    dx_bytes: element size of the dX rows the scatter reads (2 when the tensor-core backward writes them as bf16)."""
     B = c["B"]
     n_doc = B * (1 + c["J"]) * c["Ld"]
     Dpad = (c["D"] + 63) // 64 * 64
@@ -376,9 +378,12 @@ def fill_roofline(line, c, launch, clocks, pk, steps, ms):
         "dense_fwd": ("tensor", dense_doc_tf, "2 |K|F H per sequence"),
         "dense_bwd": ("tensor", 2 * dense_doc_tf, "dWd and G GEMMs"),
         "adam_table": ("hbm", 24.0 * n_table / 1e9, "24 B per parameter of one 1M x 300 table (p, m, v read + write)"),
-        # the gather is a standalone kernel: it must WRITE X (Dpad bf16 per token) besides reading ids and rows
-        "emb_gather": ("hbm", n_doc * (4 + c["D"] * 2 + Dpad * 2) / 1e9, "ids + table rows read + X written (not fused, so the write is work)"),
-        "emb_scatter": ("hbm", n_doc * (c["D"] * 4 + 8) / 1e9, "dX rows read + 8 B key/index per token"),
+        # SURVEY 8(d) figures.  gather: ids + table rows read; "the write is not counted when fused" -- it is NOT fused
+        # here (the kernel must write X, Dpad bf16 per token), so both accountings are printed (frac_with_write below).
+        "emb_gather": ("hbm", n_doc * (4 + c["D"] * 2) / 1e9, "SURVEY 8(d): ids + table rows read (the X write, which this standalone kernel also does, is not counted)"),
+        # scatter: SURVEY 8(d) counts dX as D*4 bytes per token (+ 8 B key/index); this build's single-window backward
+        # hands the rows over as bf16 (dx_bytes = 2), i.e. it moves LESS than the algorithmic figure
+        "emb_scatter": ("hbm", n_doc * (c["D"] * 4 + 8) / 1e9, "SURVEY 8(d): tokens x (D x 4 + 8) B; rows actually read with %d B per element (clsm_emb_scatter_reduce; the id-only plan runs under the forward)" % dx_bytes),
     }
     out = {}
     for k, (bound, work, what) in cand.items():
@@ -396,6 +401,10 @@ def fill_roofline(line, c, launch, clocks, pk, steps, ms):
         e["algorithmic_work_per_launch"] = work
         e["work"] = what
         e["traffic"] = traffic.get(k)
+        if k == "emb_gather":
+            e["frac_with_write"] = (n_doc * (4 + c["D"] * 2 + Dpad * 2) / 1e9) / (tms * 1e-3) / pk["hbm"]
+        if k == "emb_scatter":
+            e["frac_of_bytes_actually_read"] = (n_doc * (c["D"] * dx_bytes + 8) / 1e9) / (tms * 1e-3) / pk["hbm"]
         out[k] = e
     line["roofline_all"] = out
     if out:
@@ -498,7 +507,7 @@ def profile_phases(net, resident_step, torch):
     def timed(name, *a):
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         mids = None
-        if name == "clsm_conv_pool_bwd":
+        if name in ("clsm_conv_pool_bwd", "clsm_conv_pool_bwd_ex"):
             mids = (new_event(), new_event())
             _lib.lib.clsm_debug_mark_conv_bwd(C.c_void_p(mids[0].cuda_event), C.c_void_p(mids[1].cuda_event))
         s.record()
@@ -532,7 +541,8 @@ def profile_phases(net, resident_step, torch):
         net.overlap = was
     out = {k + "_ms": float(np.median([r.get(k, 0.0) for r in totals])) for k in totals[0]}
     launch = {k: float(np.median([r.get(k, 0.0) for r in launches])) for k in launches[0]}
-    rename = {"conv_pool_fwd": "conv_pool_tc"}
+    rename = {"conv_pool_fwd": "conv_pool_tc", "emb_gather_mask": "emb_gather", "conv_pool_bwd_ex": "conv_pool_bwd",
+              "emb_scatter_reduce": "emb_scatter"}
     launch = {rename.get(k, k): v for k, v in launch.items()}
     out["doc_tower_launch_ms"] = {k: round(v, 4) for k, v in launch.items()}
     return out, launch

@@ -41,170 +41,247 @@ __global__ void segments_kernel(const int32_t* __restrict__ st, const int32_t* _
   if (i == n - 1) { seg_start[g + 1] = static_cast<int32_t>(n); n_uniq[0] = g + 1; }
 }
 
-// level 0: one CTA per chunk of CH sorted entries; thread = one float4 column of the row.
+// ---- the whole reduction tree in ONE launch -------------------------------------------------------------------
+// Level 0 sums CH consecutive sorted entries per chunk, level l + 1 the two slots of FAN chunks of level l.  A thread
+// GROUP (64 or 128 threads of a 128-thread CTA) owns one level-0 chunk; when it is done it counts itself in at the
+// chunk's parent, and the group that arrives LAST at a parent goes on to reduce that parent (and so on up), so the
+// upper levels need no launches of their own and overlap the rest of level 0.  The tree's shape and every addition
+// order depend on n only -- which group happens to execute a chunk does not change a bit of the result.
+constexpr int MAXLV = 8;
+struct TreeParams {
+  const int32_t* spos; const int32_t* seg; const int32_t* seg_start; int64_t n;
+  const void* dX; int ncol4;
+  float inv_keep; uint32_t thr; uint64_t seed; const uint16_t* mask_bits;
+  float4* dE;
+  int n_levels;                       // level l has n_chunks[l] chunks; n_chunks[n_levels - 1] == 1
+  int64_t n_chunks[MAXLV];
+  int32_t* slot_key[MAXLV];           // outputs of level l: 2 slots per chunk
+  float4* slot_rows[MAXLV];
+  int* counters[MAXLV];               // counters[l][c]: children of chunk c of level l that have finished (self-resetting)
+};
+
+__device__ __forceinline__ void group_sync(int grp, int gthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(gthreads) : "memory");
+}
+__device__ __forceinline__ float4 f4add(float4 a, const float4& b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; return a; }
+
 // MASK: 0 = no dropout, 1 = regenerate the Philox stream of the forward, 2 = read the 1-bit-per-element mask the
 // forward gather stored (mask_bits (n_tok, ncol4 / 4) uint16, bit c of word (row, blk) = column 16 blk + c kept).
-// DXBF16: dX rows are bf16 (the single-window tensor-core backward writes them so); sums stay fp32.
+// DXBF16: dX rows are bf16 (the single-window tensor-core backward writes them so), thread = 8 columns (one 16-byte
+// load per row), 64 threads per group; otherwise fp32 rows, thread = one float4 column, 128 threads per group.
 template <int MASK, bool DXBF16>
 __global__ void __launch_bounds__(128)
-seg_reduce_l0_kernel(const int32_t* __restrict__ spos, const int32_t* __restrict__ seg,
-                     const int32_t* __restrict__ seg_start, int64_t n,
-                     const void* __restrict__ dXv, int ldx4, int ncol4,
-                     float inv_keep, uint32_t thr, uint64_t seed, const uint16_t* __restrict__ mask_bits,
-                     float4* __restrict__ dE, int lde4,
-                     int32_t* __restrict__ slot_key, float4* __restrict__ slot_rows) {
-  __shared__ int32_t s_pos[CH], s_seg[CH];
-  const int64_t c = blockIdx.x;
-  const int64_t i0 = c * CH;
-  const int cnt = static_cast<int>((i0 + CH <= n) ? CH : n - i0);
-  if (threadIdx.x < CH) {
-    const bool ok = threadIdx.x < cnt;
-    s_pos[threadIdx.x] = ok ? spos[i0 + threadIdx.x] : 0;
-    s_seg[threadIdx.x] = ok ? seg[i0 + threadIdx.x] : -1;
-  }
-  if (threadIdx.x == 0) { slot_key[2 * c] = -1; slot_key[2 * c + 1] = -1; }
-  __syncthreads();
-  const int col = threadIdx.x;
-  const bool active = col < ncol4;
+seg_reduce_tree_kernel(const TreeParams p) {
+  constexpr int GT = DXBF16 ? 64 : 128;                 // threads per group
+  constexpr int NG = 128 / GT;                          // groups per CTA
+  constexpr int NF4 = DXBF16 ? 2 : 1;                   // float4 accumulators per thread
+  constexpr int DEPTH = 16;                             // dX rows in flight per thread (shared-memory ring)
+  extern __shared__ __align__(128) uint8_t s_rows_all[];   // NG x DEPTH staged dX rows
+  __shared__ int32_t s_pos[NG][CH], s_seg[NG][CH];
+  __shared__ uint16_t s_bits[NG][CH * 32];              // keep bits of the staged rows (MASK == 2), nblk <= 32 words per row
+  __shared__ int s_edge[NG][2];                         // [0]: the chunk's first run starts its segment; [1]: its last run ends it
+  __shared__ int s_last[NG];
+  const int grp = threadIdx.x / GT, gt = threadIdx.x % GT;
+  int64_t c = static_cast<int64_t>(blockIdx.x) * NG + grp;
+  if (c >= p.n_chunks[0]) return;
+  const int ncol = DXBF16 ? p.ncol4 / 2 : p.ncol4;      // 16-byte thread columns per row
+  const bool active = gt < ncol;
+  const int ncol4 = p.ncol4;
   const int nblk = ncol4 >> 2;
-  int e = 0;
-  while (e < cnt) {
-    const int g = s_seg[e];
-    int e1 = e + 1;
-    while (e1 < cnt && s_seg[e1] == g) ++e1;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    {
-      const int lane = threadIdx.x & 31;
-      const int sub = lane & 3;                       // which float4 of the 16-column block this lane owns
-      auto load_row = [&](int q) {
-        if (!active) return make_float4(0.f, 0.f, 0.f, 0.f);
-        if (DXBF16) {
-          const uint2 u = __ldcs(reinterpret_cast<const uint2*>(dXv) + static_cast<int64_t>(s_pos[q]) * ldx4 + col);
-          return make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u),
-                             __uint_as_float(u.y << 16), __uint_as_float(u.y & 0xffff0000u));
-        }
-        return __ldcs(reinterpret_cast<const float4*>(dXv) + static_cast<int64_t>(s_pos[q]) * ldx4 + col);
-      };
-      auto apply = [&](float4 v, uint32_t word) {                 // Philox decision bytes
-        v.x = ((word & 0xffu) < thr) ? v.x * inv_keep : 0.f;
-        v.y = (((word >> 8) & 0xffu) < thr) ? v.y * inv_keep : 0.f;
-        v.z = (((word >> 16) & 0xffu) < thr) ? v.z * inv_keep : 0.f;
-        v.w = ((word >> 24) < thr) ? v.w * inv_keep : 0.f;
-        return v;
-      };
-      auto apply_bits = [&](float4 v, int q) {                    // stored mask bits
-        const uint32_t w = active ? static_cast<uint32_t>(__ldg(mask_bits + static_cast<int64_t>(s_pos[q]) * nblk + (col >> 2))) >> (4 * sub) : 0u;
-        v.x = (w & 1u) ? v.x * inv_keep : 0.f;
-        v.y = (w & 2u) ? v.y * inv_keep : 0.f;
-        v.z = (w & 4u) ? v.z * inv_keep : 0.f;
-        v.w = (w & 8u) ? v.w * inv_keep : 0.f;
-        return v;
-      };
-      int q = e;
-      for (; q + 4 <= e1; q += 4) {            // 4 independent row loads in flight, added in order
-        float4 v0 = load_row(q), v1 = load_row(q + 1), v2 = load_row(q + 2), v3 = load_row(q + 3);
-        if (MASK == 1) {
-          // One Philox call yields the 16 decision bytes of a (row, 16-column block); the 4 lanes that own that
-          // block's 4 float4 columns would each recompute it.  Instead lane (4b + j) computes the block for row
-          // q + j of the 4 rows in flight and the words are exchanged with shuffles: 1 call per lane per 4 rows.
-          uint32_t bytes[4];
-          dropout_bytes16(seed, static_cast<uint64_t>(s_pos[q + sub]), static_cast<uint32_t>(col >> 2), bytes);
-          const int base = lane & ~3;
-          uint32_t w[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const uint32_t b0 = __shfl_sync(0xffffffffu, bytes[0], base + j), b1 = __shfl_sync(0xffffffffu, bytes[1], base + j);
-            const uint32_t b2 = __shfl_sync(0xffffffffu, bytes[2], base + j), b3 = __shfl_sync(0xffffffffu, bytes[3], base + j);
-            w[j] = sub == 0 ? b0 : sub == 1 ? b1 : sub == 2 ? b2 : b3;
-          }
-          v0 = apply(v0, w[0]); v1 = apply(v1, w[1]); v2 = apply(v2, w[2]); v3 = apply(v3, w[3]);
-        } else if (MASK == 2) {
-          v0 = apply_bits(v0, q); v1 = apply_bits(v1, q + 1); v2 = apply_bits(v2, q + 2); v3 = apply_bits(v3, q + 3);
-        }
-        acc.x += v0.x; acc.y += v0.y; acc.z += v0.z; acc.w += v0.w;
-        acc.x += v1.x; acc.y += v1.y; acc.z += v1.z; acc.w += v1.w;
-        acc.x += v2.x; acc.y += v2.y; acc.z += v2.z; acc.w += v2.w;
-        acc.x += v3.x; acc.y += v3.y; acc.z += v3.z; acc.w += v3.w;
-      }
-      for (; q < e1; ++q) {
-        float4 v = load_row(q);
-        if (MASK == 1) {
-          uint32_t bytes[4];
-          dropout_bytes16(seed, static_cast<uint64_t>(s_pos[q]), static_cast<uint32_t>(col >> 2), bytes);
-          v = apply(v, bytes[sub]);
-        } else if (MASK == 2) {
-          v = apply_bits(v, q);
-        }
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-      }
-    }
-    const bool final_run = (seg_start[g] == i0 + e) && (seg_start[g + 1] == i0 + e1);
-    if (final_run) {
-      if (active) dE[static_cast<int64_t>(g) * lde4 + col] = acc;
-    } else {
-      const int64_t slot = 2 * c + (e == 0 ? 0 : 1);
-      if (active) slot_rows[slot * ncol4 + col] = acc;
-      if (threadIdx.x == 0) slot_key[slot] = g;
-    }
-    e = e1;
-  }
-}
+  const uint32_t row_bytes = static_cast<uint32_t>(ncol) * 16u;
 
-// level >= 1: chunk c covers slots [c*CH, c*CH+CH) = level-0 entries [c*R, (c+1)*R)
-__global__ void __launch_bounds__(128)
-seg_reduce_ln_kernel(const int32_t* __restrict__ in_key, const float4* __restrict__ in_rows, int64_t n_slots,
-                     const int32_t* __restrict__ seg_start, int64_t n, int64_t R, int ncol4,
-                     float4* __restrict__ dE, int lde4,
-                     int32_t* __restrict__ out_key, float4* __restrict__ out_rows) {
-  __shared__ int32_t s_key[CH];
-  const int64_t c = blockIdx.x;
-  const int64_t b0 = c * CH;
-  if (threadIdx.x < CH) s_key[threadIdx.x] = (b0 + threadIdx.x < n_slots) ? in_key[b0 + threadIdx.x] : -1;
-  if (threadIdx.x == 0) { out_key[2 * c] = -1; out_key[2 * c + 1] = -1; }
-  __syncthreads();
-  const int64_t lo = c * R;
-  const int64_t hi = ((c + 1) * R < n) ? (c + 1) * R : n;
-  const int col = threadIdx.x;
-  const bool active = col < ncol4;
-  int e = 0;
-  bool first = true;
-  while (e < CH) {
-    const int g = s_key[e];
-    if (g < 0) { ++e; continue; }
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    int e1 = e;
-    // up to four partial rows of the run in flight at a time, added left to right (same order as one by one)
-    while (e1 < CH && (s_key[e1] == g || s_key[e1] < 0)) {
-      int idx[4], n = 0;
-      while (n < 4 && e1 < CH && (s_key[e1] == g || s_key[e1] < 0)) {
-        if (s_key[e1] == g) idx[n++] = e1;
-        ++e1;
+  // =============================== level 0: chunk c of the sorted (id, position) list
+  // The chunk's CH rows of dX sit at CH unrelated addresses.  They are staged through shared memory with cp.async (16
+  // bytes per thread and row): a register-staged loop with 8 rows in flight spent two thirds of its time waiting for
+  // them (ncu: stall_long_scoreboard) and more rows in flight cost registers, i.e. occupancy.
+  {
+    const int64_t i0 = c * CH;
+    const int cnt = static_cast<int>((i0 + CH <= p.n) ? CH : p.n - i0);
+    uint8_t* rows = s_rows_all + static_cast<size_t>(grp) * DEPTH * row_bytes;
+    if (gt < CH) {
+      const bool ok = gt < cnt;
+      s_pos[grp][gt] = ok ? p.spos[i0 + gt] : 0;
+      s_seg[grp][gt] = ok ? p.seg[i0 + gt] : -1;
+    }
+    if (gt == 0) { p.slot_key[0][2 * c] = -1; p.slot_key[0][2 * c + 1] = -1; }
+    group_sync(grp, GT);
+    const int32_t* pos = s_pos[grp];
+    const int32_t* sg = s_seg[grp];
+    // Each thread owns the same 16 bytes of every row: it copies them and it alone reads them, so the staging needs
+    // no barrier -- a private ring of DEPTH slots, refilled one row at a time as rows are consumed, keeps DEPTH rows
+    // in flight for the whole chunk (a register-staged loop drains to zero after every batch).
+    const uint32_t ring = static_cast<uint32_t>(__cvta_generic_to_shared(rows)) + gt * 16;
+    const uint8_t* src0 = static_cast<const uint8_t*>(p.dX) + gt * 16;
+    auto issue = [&](int q) {                           // one commit group per row, empty past the end (uniform counting)
+      if (active && q < cnt)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring + (q % DEPTH) * row_bytes), "l"(src0 + static_cast<int64_t>(pos[q]) * row_bytes) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if constexpr (MASK == 2) {
+      // the rows' keep bits (nblk 16-bit words per row, a multiple of 8 bytes) go first, as the OLDEST commit group:
+      // 8-byte cp.async pieces, all in flight at once (plain loads through registers were 4 deep and a third of the kernel)
+      const int ppr = nblk >> 2;                        // 8-byte pieces per row
+      const uint32_t sb = static_cast<uint32_t>(__cvta_generic_to_shared(&s_bits[grp][0]));
+      for (int i = gt; i < cnt * ppr; i += GT) {
+        const int q = i / ppr, pc = i - q * ppr;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sb + q * 64 + pc * 8),
+                     "l"(reinterpret_cast<const uint8_t*>(p.mask_bits) + (static_cast<int64_t>(pos[q]) * nblk) * 2 + pc * 8) : "memory");
       }
-      float4 v[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        v[i] = (i < n && active) ? in_rows[(b0 + idx[i]) * ncol4 + col] : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        if (i < n) { acc.x += v[i].x; acc.y += v[i].y; acc.z += v[i].z; acc.w += v[i].w; }
     }
-    const bool final_run = (seg_start[g] >= lo) && (seg_start[g + 1] <= hi);
-    if (final_run) {
-      if (active) dE[static_cast<int64_t>(g) * lde4 + col] = acc;
-    } else {
-      const int64_t slot = 2 * c + (first ? 0 : 1);
-      if (active) out_rows[slot * ncol4 + col] = acc;
-      if (threadIdx.x == 0) out_key[slot] = g;
+    asm volatile("cp.async.commit_group;" ::: "memory");
+#pragma unroll
+    for (int q = 0; q < DEPTH; ++q) issue(q);
+    if (gt == 0) {
+      s_edge[grp][0] = p.seg_start[sg[0]] == i0 ? 1 : 0;
+      s_edge[grp][1] = p.seg_start[sg[cnt - 1] + 1] == i0 + cnt ? 1 : 0;
     }
-    first = false;
-    e = e1;
+    asm volatile("cp.async.wait_group %0;" ::"n"(DEPTH) : "memory");      // this thread's pieces of the keep bits have landed
+    group_sync(grp, GT);
+    const int sub = gt & 3;
+    struct Row { float4 v[NF4]; };
+    auto load_row = [&](int q) {                        // from the staged copy
+      Row r;
+      asm volatile("cp.async.wait_group %0;" ::"n"(DEPTH - 1) : "memory");      // the oldest row in flight has landed
+      if constexpr (DXBF16) {
+        const uint4 u = active ? *reinterpret_cast<const uint4*>(rows + static_cast<size_t>(q % DEPTH) * row_bytes + gt * 16) : make_uint4(0u, 0u, 0u, 0u);
+        r.v[0] = make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u), __uint_as_float(u.y << 16), __uint_as_float(u.y & 0xffff0000u));
+        r.v[1] = make_float4(__uint_as_float(u.z << 16), __uint_as_float(u.z & 0xffff0000u), __uint_as_float(u.w << 16), __uint_as_float(u.w & 0xffff0000u));
+      } else {
+        r.v[0] = active ? *reinterpret_cast<const float4*>(rows + static_cast<size_t>(q % DEPTH) * row_bytes + gt * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      issue(q + DEPTH);                                 // refill the slot just read
+      return r;
+    };
+    auto keep4 = [&](float4 v, uint32_t w) {                    // low 4 bits of w: keep decisions of the 4 columns
+      v.x = (w & 1u) ? v.x * p.inv_keep : 0.f;
+      v.y = (w & 2u) ? v.y * p.inv_keep : 0.f;
+      v.z = (w & 4u) ? v.z * p.inv_keep : 0.f;
+      v.w = (w & 8u) ? v.w * p.inv_keep : 0.f;
+      return v;
+    };
+    auto bytes_to_nibble = [&](uint32_t word) -> uint32_t {     // 4 Philox decision bytes -> 4 keep bits
+      return ((word & 0xffu) < p.thr ? 1u : 0u) | (((word >> 8) & 0xffu) < p.thr ? 2u : 0u) |
+             (((word >> 16) & 0xffu) < p.thr ? 4u : 0u) | ((word >> 24) < p.thr ? 8u : 0u);
+    };
+    // keep bits of this thread's columns of row q: NF4 nibbles, lowest first
+    auto row_bits = [&](int q) -> uint32_t {
+      if (!active) return 0u;
+      if constexpr (MASK == 2) {
+        if constexpr (DXBF16) return (static_cast<uint32_t>(s_bits[grp][q * 32 + (gt >> 1)]) >> (8 * (gt & 1))) & 0xFFu;
+        else return (static_cast<uint32_t>(s_bits[grp][q * 32 + (gt >> 2)]) >> (4 * sub)) & 0xFu;
+      } else {
+        uint32_t b[4];
+        if constexpr (DXBF16) {
+          dropout_bytes16(p.seed, static_cast<uint64_t>(pos[q]), static_cast<uint32_t>(gt >> 1), b);
+          return bytes_to_nibble(b[2 * (gt & 1)]) | (bytes_to_nibble(b[2 * (gt & 1) + 1]) << 4);
+        } else {
+          dropout_bytes16(p.seed, static_cast<uint64_t>(pos[q]), static_cast<uint32_t>(gt >> 2), b);
+          return bytes_to_nibble(sub == 0 ? b[0] : sub == 1 ? b[1] : sub == 2 ? b[2] : b[3]);
+        }
+      }
+    };
+    // A run of equal ids that lies wholly inside the chunk is final; a run cut by a chunk edge leaves a partial row
+    // in one of the chunk's two slots.  Only the first and the last run can be cut (s_edge).
+    auto flush = [&](int g, int rs, int re, const Row& acc) {
+      const bool final_run = (rs > 0 || s_edge[grp][0] != 0) && (re < cnt || s_edge[grp][1] != 0);
+      float4* dst = final_run ? p.dE + static_cast<int64_t>(g) * ncol4 : p.slot_rows[0] + (2 * c + (rs == 0 ? 0 : 1)) * ncol4;
+      if (active) {
+#pragma unroll
+        for (int i = 0; i < NF4; ++i) dst[gt * NF4 + i] = acc.v[i];
+      }
+      if (!final_run && gt == 0) p.slot_key[0][2 * c + (rs == 0 ? 0 : 1)] = g;
+    };
+    // rows are added strictly left to right within a run: the same bits whatever the staging
+    int g = sg[0], rs = 0;
+    Row acc;
+#pragma unroll
+    for (int i = 0; i < NF4; ++i) acc.v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int idx = 0; idx < cnt; ++idx) {
+      Row v = load_row(idx);
+      if constexpr (MASK != 0) {
+        const uint32_t w = row_bits(idx);
+#pragma unroll
+        for (int j = 0; j < NF4; ++j) v.v[j] = keep4(v.v[j], w >> (4 * j));
+      }
+      const int gi = sg[idx];
+      if (gi != g) {
+        flush(g, rs, idx, acc);
+        g = gi; rs = idx;
+#pragma unroll
+        for (int j = 0; j < NF4; ++j) acc.v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int j = 0; j < NF4; ++j) acc.v[j] = f4add(acc.v[j], v.v[j]);
+    }
+    flush(g, rs, cnt, acc);
+  }
+
+  // =============================== levels >= 1: whoever arrives last at a parent reduces it
+  int64_t R = static_cast<int64_t>(CH) * FAN;           // level-0 entries covered by one chunk of the current level
+  for (int lv = 1; lv < p.n_levels; ++lv, R *= FAN) {
+    const int64_t parent = c / FAN;
+    const int64_t first_child = parent * FAN;
+    const int n_children = static_cast<int>((first_child + FAN <= p.n_chunks[lv - 1]) ? FAN : p.n_chunks[lv - 1] - first_child);
+    __threadfence();                                    // this group's slot rows / keys / dE rows are visible ...
+    group_sync(grp, GT);
+    if (gt == 0) {                                      // ... before it counts itself in
+      const int old = atomicAdd(p.counters[lv] + parent, 1);
+      const int last = old == n_children - 1 ? 1 : 0;
+      if (last) p.counters[lv][parent] = 0;             // ready for the next call on this plan
+      s_last[grp] = last;
+    }
+    group_sync(grp, GT);
+    if (!s_last[grp]) return;
+    __threadfence();
+    c = parent;
+    // slots [c * CH, c * CH + 2 * n_children) of level lv - 1
+    int32_t* s_key = s_seg[grp];
+    const int32_t* in_key = p.slot_key[lv - 1];
+    const float4* in_rows = p.slot_rows[lv - 1];
+    const int64_t b0 = c * CH;
+    if (gt < CH) s_key[gt] = gt < 2 * n_children ? __ldcg(in_key + b0 + gt) : -1;
+    if (gt == 0) { p.slot_key[lv][2 * c] = -1; p.slot_key[lv][2 * c + 1] = -1; }
+    group_sync(grp, GT);
+    const int64_t lo = c * R;
+    const int64_t hi = ((c + 1) * R < p.n) ? (c + 1) * R : p.n;
+    int e = 0;
+    bool first = true;
+    while (e < CH) {
+      const int g = s_key[e];
+      if (g < 0) { ++e; continue; }
+      int e1 = e;
+      while (e1 < CH && (s_key[e1] == g || s_key[e1] < 0)) ++e1;
+      const bool final_run = (p.seg_start[g] >= lo) && (p.seg_start[g + 1] <= hi);
+      float4* dst = final_run ? p.dE + static_cast<int64_t>(g) * ncol4 : p.slot_rows[lv] + (2 * c + (first ? 0 : 1)) * ncol4;
+      for (int col = gt; col < ncol4; col += GT) {      // partial rows of the run, four in flight, added left to right
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        int q = e;
+        while (q < e1) {
+          int idx[4], m = 0;
+          while (m < 4 && q < e1) { if (s_key[q] == g) idx[m++] = q; ++q; }
+          float4 v[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) v[i] = i < m ? __ldcg(in_rows + (b0 + idx[i]) * ncol4 + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) if (i < m) acc = f4add(acc, v[i]);
+        }
+        dst[col] = acc;
+      }
+      if (!final_run && gt == 0) p.slot_key[lv][2 * c + (first ? 0 : 1)] = g;
+      first = false;
+      e = e1;
+    }
   }
 }
 
 struct ScatterPlan {
   size_t off_keys_out, off_vals_in, off_vals_out, off_head, off_seg, off_seg_start;
   size_t off_cub, cub_bytes;
-  size_t off_slot_key[2], off_slot_rows[2];
+  int n_levels;
+  int64_t n_chunks[MAXLV];
+  size_t off_slot_key[MAXLV], off_slot_rows[MAXLV], off_counters[MAXLV];
+  size_t off_counters_all, counters_bytes;
   size_t total;
 };
 
@@ -224,13 +301,20 @@ ScatterPlan make_plan(int64_t n, int ncol4) {
   cub::DeviceScan::InclusiveSum(nullptr, scan_bytes, (const int32_t*)nullptr, (int32_t*)nullptr, static_cast<int>(n));
   p.cub_bytes = sort_bytes > scan_bytes ? sort_bytes : scan_bytes;
   p.off_cub = take(p.cub_bytes);
-  const int64_t chunks0 = ceil_div64(n, CH);
-  const int64_t slots1 = 2 * chunks0;
-  const int64_t slots2 = 2 * ceil_div64(slots1, CH);
-  p.off_slot_key[0] = take(slots1 * 4);
-  p.off_slot_rows[0] = take(static_cast<size_t>(slots1) * ncol4 * 16);
-  p.off_slot_key[1] = take(slots2 * 4);
-  p.off_slot_rows[1] = take(static_cast<size_t>(slots2) * ncol4 * 16);
+  // the reduction tree: level 0 = chunks of CH entries, level l + 1 = FAN chunks of level l, until one chunk is left
+  int lv = 0;
+  int64_t nc = ceil_div64(n, CH);
+  for (;; ++lv) {
+    p.n_chunks[lv] = nc;
+    p.off_slot_key[lv] = take(static_cast<size_t>(2 * nc) * 4);
+    p.off_slot_rows[lv] = take(static_cast<size_t>(2 * nc) * ncol4 * 16);
+    if (nc == 1) break;
+    nc = ceil_div64(nc, FAN);
+  }
+  p.n_levels = lv + 1;
+  p.off_counters_all = o;
+  for (int l = 0; l < p.n_levels; ++l) p.off_counters[l] = take(static_cast<size_t>(p.n_chunks[l]) * 4);
+  p.counters_bytes = o - p.off_counters_all;
   p.total = o;
   return p;
 }
@@ -275,6 +359,7 @@ int clsm_emb_scatter_plan(const int32_t* tok, int64_t n_tok, int Dpad, int D, in
   while (end_bit < 32 && (static_cast<int64_t>(1) << end_bit) < n_rows) ++end_bit;
 
   CLSM_CUDA(cudaMemsetAsync(row_of_id, 0xFF, static_cast<size_t>(n_rows) * 4, st));
+  CLSM_CUDA(cudaMemsetAsync(w + p.off_counters_all, 0, p.counters_bytes, st));     // arrival counters of the reduction tree
   iota_kernel<<<g256, 256, 0, st>>>(vals_in, n_tok);
   CLSM_LAUNCH_CHECK();
   size_t cb = p.cub_bytes;
@@ -308,37 +393,40 @@ int clsm_emb_scatter_reduce(int64_t n_tok, const void* dX, int dx_dtype, int Dpa
   const int32_t* seg = reinterpret_cast<const int32_t*>(w + p.off_seg);
   const int32_t* seg_start = reinterpret_cast<const int32_t*>(w + p.off_seg_start);
 
-  const int threads = (ncol4 + 31) / 32 * 32 < 64 ? 64 : (ncol4 + 31) / 32 * 32;
-  int32_t* skey[2] = {reinterpret_cast<int32_t*>(w + p.off_slot_key[0]), reinterpret_cast<int32_t*>(w + p.off_slot_key[1])};
-  float4* srow[2] = {reinterpret_cast<float4*>(w + p.off_slot_rows[0]), reinterpret_cast<float4*>(w + p.off_slot_rows[1])};
-  const int64_t chunks0 = ceil_div64(n_tok, CH);
-  const bool drop = keep < 1.0f;
+  const bool drop = keep < 1.0f && keep_threshold(keep) < 256u;      // a keep that rounds to 256/256 drops nothing
   const int mask = !drop ? 0 : (mask_bits != nullptr ? 2 : 1);
-  const float inv_keep = drop ? dropout_scale(keep) : 1.0f;
-  const uint32_t thr = drop ? keep_threshold(keep) : 256u;
-  float4* dE4 = reinterpret_cast<float4*>(dE_rows);
-  const unsigned g0 = static_cast<unsigned>(chunks0);
-#define L0(M, B) seg_reduce_l0_kernel<M, B><<<g0, threads, 0, st>>>(vals_out, seg, seg_start, n_tok, dX, ncol4, ncol4, \
-        inv_keep, thr, seed, mask_bits, dE4, ncol4, skey[0], srow[0])
-  if (dx_dtype == CLSM_BF16) { if (mask == 0) L0(0, true); else if (mask == 1) L0(1, true); else L0(2, true); }
-  else { if (mask == 0) L0(0, false); else if (mask == 1) L0(1, false); else L0(2, false); }
-#undef L0
-  CLSM_LAUNCH_CHECK();
-  // higher levels ping-pong between the two slot buffers
-  int64_t n_chunks_prev = chunks0;
-  int64_t R = static_cast<int64_t>(CH) * FAN;     // level-0 entries covered by one level-1 chunk
-  int src = 0;
-  while (n_chunks_prev > 1) {
-    const int64_t n_slots = 2 * n_chunks_prev;
-    const int64_t n_chunks = ceil_div64(n_slots, CH);
-    const int dst = src ^ 1;
-    seg_reduce_ln_kernel<<<static_cast<unsigned>(n_chunks), threads, 0, st>>>(skey[src], srow[src], n_slots, seg_start, n_tok, R,
-        ncol4, dE4, ncol4, skey[dst], srow[dst]);
-    CLSM_LAUNCH_CHECK();
-    n_chunks_prev = n_chunks;
-    R *= FAN;
-    src = dst;
+  TreeParams t{};
+  t.spos = vals_out; t.seg = seg; t.seg_start = seg_start; t.n = n_tok;
+  t.dX = dX; t.ncol4 = ncol4;
+  t.inv_keep = drop ? dropout_scale(keep) : 1.0f;
+  t.thr = drop ? keep_threshold(keep) : 256u;
+  t.seed = seed; t.mask_bits = mask_bits;
+  t.dE = reinterpret_cast<float4*>(dE_rows);
+  t.n_levels = p.n_levels;
+  for (int l = 0; l < p.n_levels; ++l) {
+    t.n_chunks[l] = p.n_chunks[l];
+    t.slot_key[l] = reinterpret_cast<int32_t*>(w + p.off_slot_key[l]);
+    t.slot_rows[l] = reinterpret_cast<float4*>(w + p.off_slot_rows[l]);
+    t.counters[l] = reinterpret_cast<int*>(w + p.off_counters[l]);
   }
+  const int64_t chunks0 = p.n_chunks[0];
+  // staged rows: 16 rows per group; bf16: 2 groups x 16 x Dpad*2 B, fp32: 1 group x 16 x Dpad*4 B -- the same bytes
+  const size_t smem = static_cast<size_t>(16) * Dpad * 4;
+#define TREE(M, B, G)                                                                                                   \
+  do {                                                                                                                  \
+    CLSM_CUDA(cudaFuncSetAttribute(seg_reduce_tree_kernel<M, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
+    CLSM_CUDA(cudaFuncSetAttribute(seg_reduce_tree_kernel<M, B>, cudaFuncAttributePreferredSharedMemoryCarveout, 100)); \
+    seg_reduce_tree_kernel<M, B><<<G, 128, smem, st>>>(t);                                                              \
+  } while (0)
+  if (dx_dtype == CLSM_BF16) {
+    const unsigned g0 = static_cast<unsigned>(ceil_div64(chunks0, 2));       // two 64-thread groups per CTA
+    if (mask == 0) TREE(0, true, g0); else if (mask == 1) TREE(1, true, g0); else TREE(2, true, g0);
+  } else {
+    const unsigned g0 = static_cast<unsigned>(chunks0);
+    if (mask == 0) TREE(0, false, g0); else if (mask == 1) TREE(1, false, g0); else TREE(2, false, g0);
+  }
+#undef TREE
+  CLSM_LAUNCH_CHECK();
   return CLSM_OK;
 }
 
