@@ -7,6 +7,7 @@
 // candidates a CTA holds in registers, then a bitonic sort of the k survivors; levels repeat on
 // the survivors until one list per query is left.
 #include "common.cuh"
+#include <stdlib.h>
 #include <mutex>
 
 namespace {
@@ -363,14 +364,27 @@ int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_
 
 }  // extern "C"
 
+void clsm_score_tc_geometry(int64_t rows, int* grid, int* nsub, int64_t* subcap);       // topk_tc.cu
+
 namespace {
 
 // ---- bf16 corpus: tensor-core scoring (topk_tc.cu) + the same exact selection --------------------------
-// The corpus is processed in segments of SEG rows.  For each 128-query block and segment: score_tc writes the
-// (128, SEG) key matrix (only keys >= the k-th best key found in earlier segments survive, the rest are 0),
-// one selection level reduces every 2048-key chunk to its k best, and a second level merges those lists with
-// the running best-k list of the block; its k-th key is the threshold for the next segment.
-constexpr int64_t SEG = 65536;
+// Per 128-query block the corpus is scanned once, in segments.  Every segment is scanned behind the k-th best key
+// found so far (none for the first): a row that beats it is appended to a compact per-query list -- one private
+// sub-list per (CTA, column half), so an append is a register increment and a store -- and one CTA per query folds the
+// lists into the running best-k, whose k-th key is the next segment's threshold.  A segment boundary costs a scan
+// launch and a fold (~20 us), so segments grow 16-fold: 4 096 rows (scanned DENSE: no threshold exists yet), then to
+// 65 536, to 1 Mi, and 1 Mi at a time from there on.  (Round 1 scanned the first 65 536 rows into a dense
+// 67 MB key matrix and appended survivors with a global atomic each: 47 % of a 1 M-row call went to the dense rows
+// and a segment whose threshold let 1 row in 600 through ran 3x slower than one without survivors.)
+constexpr int64_t SEG0 = 4096;                  // first segment: no threshold yet
+constexpr int64_t SEG_MAX = 1 << 20;            // 1 Mi rows
+constexpr int64_t GROW = 16;
+inline int64_t next_seg_len(int64_t done) {     // length of the segment that starts at row `done`
+  const int64_t target = done * GROW;           // scan up to 16 x what has been scanned
+  const int64_t len = target - done;
+  return len < SEG_MAX ? len : SEG_MAX;
+}
 
 __global__ void kth_key_kernel(const u64* __restrict__ best, int64_t nq, int k, u64* __restrict__ thr) {
   const int64_t q = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -388,35 +402,54 @@ __global__ void normalize_rows_bf16_kernel(const float* __restrict__ sem, int64_
   for (int h = lane; h < H; h += 32) vec[r * H + h] = __float2bfloat16_rn(sem[r * H + h] / n);
 }
 
-// Later segments run behind the threshold of everything scanned so far, so their survivors are few (k * rows / rows
-// already scanned, on average): the scan appends them to a COMPACT per-query list and one CTA per query folds the
-// list into the running best-k.  That makes the selection cost independent of the segment length, so the segments
-// grow fourfold (fewer, longer scans).  A list holds a whole segment, so no ordering of the corpus can overflow it.
-constexpr int64_t SEG_MAX = 16 * SEG;           // 1 Mi rows: 8 MiB of list per query in the worst case
-constexpr int64_t GROW = 4;                     // every launch costs ~45 us whatever its length: few, long segments
-
-// best (k, sorted descending, 0 = empty) <- k largest of best U list[0:cnt]; thr <- its k-th key; cnt <- 0
+// best (k, sorted descending, 0 = empty) <- k largest of best U (the query's nsub sub-lists); thr <- its k-th key
+constexpr int NSUB_MAX = 1024;
 __global__ void __launch_bounds__(TPB)
-select_compact_kernel(const u64* __restrict__ lists, int64_t cap, int* __restrict__ cnt, int k,
+select_compact_kernel(const u64* __restrict__ lists, int64_t cap, const int* __restrict__ cnt, int nsub, int64_t subcap, int k,
                       u64* __restrict__ best, u64* __restrict__ thr) {
   __shared__ unsigned s_hist[256];
   __shared__ unsigned s_ctl[4];
   __shared__ u64 s_out[KMAX];
   __shared__ u64 s_best[KMAX];
+  __shared__ int s_off[NSUB_MAX + 1];           // exclusive prefix sums of the sub-list lengths
   const int tid = threadIdx.x;
   const int64_t q = blockIdx.x;
   const u64* list = lists + q * cap;
-  int64_t n = cnt[q];
-  if (n > cap) n = cap;
+  for (int i = tid; i < nsub; i += TPB) {
+    int c = cnt[q * nsub + i];
+    s_off[i + 1] = c < subcap ? c : static_cast<int>(subcap);
+  }
+  if (tid == 0) s_off[0] = 0;
   if (tid < KMAX) s_best[tid] = tid < k ? best[q * k + tid] : 0ull;
   __syncthreads();
+  if (tid < 32) {                               // inclusive scan of s_off[1..nsub] by one warp, 32 entries at a time
+    int carry = 0;
+    for (int b0 = 1; b0 <= nsub; b0 += 32) {
+      const int i = b0 + tid;
+      int v = i <= nsub ? s_off[i] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int n2 = __shfl_up_sync(0xffffffffu, v, o); if (tid >= o) v += n2; }
+      if (i <= nsub) s_off[i] = v + carry;
+      carry += __shfl_sync(0xffffffffu, v, 31);
+    }
+  }
+  __syncthreads();
+  const int64_t n = s_off[nsub];
   for (int64_t off = 0; off < n; off += R - KMAX) {
     u64 keys[KPT];
 #pragma unroll
     for (int i = 0; i < KPT; ++i) {
       const int idx = tid + i * TPB;
       if (idx < KMAX) keys[i] = s_best[idx];
-      else { const int64_t j = off + idx - KMAX; keys[i] = j < n ? list[j] : 0ull; }
+      else {
+        const int64_t j = off + idx - KMAX;
+        keys[i] = 0ull;
+        if (j < n) {                            // flat index -> (sub-list, position): the last s with s_off[s] <= j
+          int lo = 0, hi = nsub;
+          while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_off[mid] <= j) lo = mid; else hi = mid; }
+          keys[i] = list[static_cast<int64_t>(lo) * subcap + (j - s_off[lo])];
+        }
+      }
     }
     select_topk(keys, k, s_hist, s_ctl, s_out);
     __syncthreads();
@@ -424,29 +457,34 @@ select_compact_kernel(const u64* __restrict__ lists, int64_t cap, int* __restric
     __syncthreads();
   }
   if (tid < k) best[q * k + tid] = s_best[tid];
-  if (tid == 0) { thr[q] = s_best[k - 1]; cnt[q] = 0; }
+  if (tid == 0) thr[q] = s_best[k - 1];
 }
 
-struct TcPlan { size_t off_keys, off_l1, off_l2, off_best, off_thr, off_cnt, total; int64_t l1_lists, cap; };
+struct TcPlan { size_t off_keys, off_l1, off_best, off_thr, off_cnt, total; int64_t cap; int max_nsub; };
 TcPlan tc_plan(int k, int64_t N) {
   TcPlan p{};
   size_t o = 0;
   auto take = [&](size_t b) { size_t r = o; o += align_up(b, 256); return r; };
-  p.l1_lists = SEG / R;                                           // 32 chunks of 2048 keys
-  // list capacity per query = the longest segment this corpus will use (dense first segment: SEG)
-  p.cap = SEG;
-  for (int64_t done = SEG, seg = GROW * SEG; done < N; done += seg, seg = (GROW * seg < SEG_MAX ? GROW * seg : SEG_MAX)) {
-    const int64_t len = (N - done < seg) ? N - done : seg;
-    if (len > p.cap) p.cap = len;
+  // list capacity per query = the largest sub-list footprint any segment of this corpus needs
+  p.cap = 0; p.max_nsub = 0;
+  for (int64_t done = SEG0; done < N;) {
+    int64_t len = next_seg_len(done);
+    if (len > N - done) len = N - done;
+    int grid, nsub; int64_t subcap;
+    clsm_score_tc_geometry(len, &grid, &nsub, &subcap);
+    if (nsub * subcap > p.cap) p.cap = nsub * subcap;
+    if (nsub > p.max_nsub) p.max_nsub = nsub;
+    done += len;
   }
+  if (p.cap < SEG0) p.cap = SEG0;                                 // the dense first segment uses the same region
   p.cap = (p.cap + 1) / 2 * 2;
   p.off_keys = take(static_cast<size_t>(128) * p.cap * 8);
-  p.off_cnt = take(128 * 4);
-  p.off_l1 = take(static_cast<size_t>(128) * (p.l1_lists + 1) * k * 8);   // + running best appended
-  p.off_l2 = take(static_cast<size_t>(128) * 4 * k * 8);
+  p.off_l1 = take(static_cast<size_t>(128) * (SEG0 / R) * k * 8);
+  p.off_cnt = take(static_cast<size_t>(128) * p.max_nsub * 4);
   p.off_best = take(static_cast<size_t>(128) * k * 8);
   p.off_thr = take(128 * 8);
   p.total = o;
+  (void)k;
   return p;
 }
 
@@ -479,53 +517,61 @@ int clsm_cos_topk_bf16(const void* Qn, int64_t nQ, const void* Cn, int64_t N, in
   char* w = static_cast<char*>(ws);
   u64* keys = reinterpret_cast<u64*>(w + p.off_keys);
   u64* l1 = reinterpret_cast<u64*>(w + p.off_l1);
-  u64* l2 = reinterpret_cast<u64*>(w + p.off_l2);
   u64* best = reinterpret_cast<u64*>(w + p.off_best);
   u64* thr = reinterpret_cast<u64*>(w + p.off_thr);
   int* cnt = reinterpret_cast<int*>(w + p.off_cnt);
-  const int64_t l1_stride = (p.l1_lists + 1) * k;
+  CLSM_REQUIRE(p.max_nsub <= NSUB_MAX, "cos_topk_bf16: too many SMs for the fold kernel's table");
+  // CLSM_TOPK_PROF=1 (diagnostics, synchronises): device time of every launch of the first query block, from events
+  static int prof_on = -1;
+  if (prof_on < 0) { const char* e = getenv("CLSM_TOPK_PROF"); prof_on = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  cudaEvent_t pev[64]; int64_t plen[64]; int npev = 0;
+  auto mark = [&](int64_t len) { if (prof_on && npev < 64) { cudaEventCreate(&pev[npev]); cudaEventRecord(pev[npev], st); plen[npev++] = len; } };
   for (int64_t qb = 0; qb < nQ; qb += 128) {
     const int64_t nq = (nQ - qb < 128) ? nQ - qb : 128;
-    // first segment, DENSE: the scan writes every key at its row position, two selection levels reduce the
-    // 2048-key chunks to the block's best-k list.  The level-1 select zeroes what it reads; the region must
-    // start all-empty (later segments of the previous block left their compact lists in it).
-    CLSM_CUDA(cudaMemsetAsync(keys, 0, static_cast<size_t>(128) * SEG * 8, st));
     CLSM_CUDA(cudaMemsetAsync(best, 0, static_cast<size_t>(nq) * k * 8, st));
-    CLSM_CUDA(cudaMemsetAsync(cnt, 0, 128 * 4, st));
+    CLSM_CUDA(cudaMemsetAsync(thr, 0, 128 * 8, st));          // no threshold yet: the first segment keeps every row
+    // first segment, DENSE (no threshold exists yet, so every row would survive: compact lists are the wrong tool): the
+    // scan writes each key at its row position, two selection levels reduce the 2048-key chunks to the block's best-k.
+    // The level-1 select zeroes what it reads; the region must start all-empty (compact lists were in it).
     {
-      const int64_t r1 = SEG < N ? SEG : N;
-      int rc = clsm_score_keys_tc(Qn, nQ, qb, Cn, N, H, 0, r1, keys, SEG, nullptr, nullptr, st);
+      const int64_t r1 = SEG0 < N ? SEG0 : N;
+      CLSM_CUDA(cudaMemsetAsync(keys, 0, static_cast<size_t>(128) * SEG0 * 8, st));
+      if (qb == 0) mark(r1);
+      int rc = clsm_score_keys_tc(Qn, nQ, qb, Cn, N, H, 0, r1, keys, SEG0, nullptr, nullptr, st);
       if (rc != CLSM_OK) return rc;
+      if (qb == 0) mark(-1);
       const int64_t n_chunks = ceil_div64(r1, R);
-      {
-        dim3 grid(static_cast<unsigned>(nq), static_cast<unsigned>(n_chunks));
-        topk_merge_kernel<true><<<grid, TPB, 0, st>>>(keys, SEG, ((r1 + 1) / 2) * 2, k, l1, l1_stride);
-        CLSM_LAUNCH_CHECK();
-      }
-      u64* bufs[2] = {l1, l2};
-      int64_t n_in = n_chunks * k;
-      int src = 0;
-      int64_t stride = l1_stride;
-      while (true) {                                   // 32 lists of k keys: at most two more levels
-        const int64_t nc = ceil_div64(n_in, R);
-        const int dst = src ^ 1;
-        u64* out = (nc == 1) ? best : bufs[dst];
-        dim3 grid(static_cast<unsigned>(nq), static_cast<unsigned>(nc));
-        topk_merge_kernel<false><<<grid, TPB, 0, st>>>(bufs[src], stride, n_in, k, out, nc * k);
-        CLSM_LAUNCH_CHECK();
-        if (nc == 1) break;
-        n_in = nc * k; stride = nc * k; src = dst;
-      }
+      dim3 g1(static_cast<unsigned>(nq), static_cast<unsigned>(n_chunks));
+      topk_merge_kernel<true><<<g1, TPB, 0, st>>>(keys, SEG0, ((r1 + 1) / 2) * 2, k, l1, n_chunks * k);
+      CLSM_LAUNCH_CHECK();
+      dim3 g2(static_cast<unsigned>(nq), 1);             // SEG0 / R lists of k keys: one more level
+      topk_merge_kernel<false><<<g2, TPB, 0, st>>>(l1, n_chunks * k, n_chunks * k, k, best, k);
+      CLSM_LAUNCH_CHECK();
       kth_key_kernel<<<1, 128, 0, st>>>(best, nq, k, thr);
       CLSM_LAUNCH_CHECK();
     }
-    // remaining segments, COMPACT, each four times as long as the one before
-    for (int64_t r0 = SEG, seg = GROW * SEG; r0 < N; r0 += seg, seg = (GROW * seg < SEG_MAX ? GROW * seg : SEG_MAX)) {
-      const int64_t r1 = (r0 + seg < N) ? r0 + seg : N;
-      int rc = clsm_score_keys_tc(Qn, nQ, qb, Cn, N, H, r0, r1, keys, p.cap, thr, cnt, st);
+    for (int64_t done = SEG0; done < N;) {
+      int64_t len = next_seg_len(done);
+      if (len > N - done) len = N - done;
+      int grid, nsub; int64_t subcap;
+      clsm_score_tc_geometry(len, &grid, &nsub, &subcap);
+      if (qb == 0) mark(len);
+      int rc = clsm_score_keys_tc(Qn, nQ, qb, Cn, N, H, done, done + len, keys, p.cap, thr, cnt, st);
       if (rc != CLSM_OK) return rc;
-      select_compact_kernel<<<static_cast<unsigned>(nq), TPB, 0, st>>>(keys, p.cap, cnt, k, best, thr);
+      if (qb == 0) mark(-1);
+      select_compact_kernel<<<static_cast<unsigned>(nq), TPB, 0, st>>>(keys, p.cap, cnt, nsub, subcap, k, best, thr);
       CLSM_LAUNCH_CHECK();
+      done += len;
+    }
+    if (qb == 0 && prof_on) {
+      mark(0);
+      cudaStreamSynchronize(st);
+      for (int i = 0; i + 1 < npev; ++i) {
+        float ms = 0.f; cudaEventElapsedTime(&ms, pev[i], pev[i + 1]);
+        if (plen[i] > 0) fprintf(stderr, "[topk prof] scan %8lld rows %.1f us", static_cast<long long>(plen[i]), ms * 1e3f);
+        else fprintf(stderr, " | fold %.1f us\n", ms * 1e3f);
+      }
+      for (int i = 0; i < npev; ++i) cudaEventDestroy(pev[i]);
     }
     const int64_t n = nq * k;
     topk_decode_kernel<<<static_cast<unsigned>(ceil_div64(n, 256)), 256, 0, st>>>(best, n, id_base, out_score + qb * k, out_id + qb * k);

@@ -36,18 +36,15 @@ struct ScoreParams {
   u64* keys;                    // (QB, seg_cap): keys[(q - q_begin) * seg_cap + (row - row_begin)]
   int64_t seg_cap;
   const u64* thr;               // (128) or nullptr: only keys >= thr[q - q_begin] are kept
-  int* cnt;                     // (128) or nullptr.  Non-null = COMPACT mode: survivor i of query q goes to
-                                // keys[q * seg_cap + atomicAdd(cnt[q], 1)] (order irrelevant: keys are unique and the
-                                // selection is exact); null = DENSE mode: keys[q * seg_cap + (row - row_begin)]
+  int* cnt;                     // nullptr = DENSE mode: keys[q * seg_cap + (row - row_begin)].  Non-null = COMPACT mode:
+                                // every (CTA, column half) owns a private sub-list per query, so appending a survivor
+                                // is a register increment and a store -- no atomic on the scan's critical path.
+                                // Sub-list s = 2 * blockIdx + half of query q starts at keys[q * seg_cap + s * subcap]
+                                // and its length goes to cnt[q * nsub + s] (order irrelevant: keys are unique and the
+                                // selection is exact).  subcap = rows one (CTA, half) can see in this segment.
+  int64_t subcap; int nsub;
   int stages;
 };
-
-// Out of line on purpose: lanes are different queries, so a survivor in one lane must not make the other 31
-// execute a predicated copy of this body for each of their rows -- the scan loop stays compare + branch.
-__device__ __noinline__ void append_survivor(float x, int64_t row, u64 thr, int* cnt, u64* krow, int64_t cap) {
-  const u64 key = (static_cast<u64>(f32_to_ordered(x + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row));
-  if (key >= thr) { const int pos = atomicAdd(cnt, 1); if (pos < cap) krow[pos] = key; }
-}
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmC, const ScoreParams p) {
@@ -135,8 +132,13 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // Compact mode rejects on the SCORE alone (one float compare per row; a tree max per 64 rows decides whether
     // anything in the batch needs a key at all).  A row that ties the threshold score but loses on the id passes
     // this test and is dropped by the exact 64-bit compare below; the selection is exact either way.
-    const float thr_f = thr != 0ull ? ordered_to_f32(static_cast<uint32_t>(thr >> 32)) : -INFINITY;
+    const float thr_f = !qok ? INFINITY : (thr != 0ull ? ordered_to_f32(static_cast<uint32_t>(thr >> 32)) : -INFINITY);
     u64* krow = p.keys + static_cast<int64_t>(ql) * p.seg_cap;
+    const int sub = 2 * static_cast<int>(blockIdx.x) + ((warp - 2) >> 2);
+    // compact mode: this thread's private sub-list (query-major: measured against a sub-list-major layout, whose 983 k-row
+    // segment ran 160 us instead of 102 us)
+    u64* klist = krow + static_cast<int64_t>(sub) * p.subcap;
+    int n_mine = 0;
     int acc = 0; uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
       const int64_t r0 = p.row_begin + static_cast<int64_t>(tile) * NT;
@@ -151,8 +153,11 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int c = 0; c < 4; ++c) tc_ld16_async(taddr + cb + c * 16, v[c]);
         tc_wait_ld();
         if (cb + 64 >= cb_begin + NT / 2) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(acc)); }
-        if (!qok) continue;
         if (p.cnt != nullptr) {
+          // Lanes are different queries, so a survivor in one lane must not make the other 31 pay for it: every test
+          // below is a WARP-UNIFORM branch on a vote (all 32 lanes are converged here; lanes of queries past nQ carry
+          // thr_f = +inf and never vote yes).  Behind a threshold one row in hundreds survives per query, i.e. a few
+          // per 32 x 64 batch: the batch costs ~50 compare/vote/branch triples plus the rare append.
           float m[4];
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
@@ -162,22 +167,25 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             m[c] = fmaxf(fmaxf(fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3])), fmaxf(fmaxf(x[4], x[5]), fmaxf(x[6], x[7]))),
                          fmaxf(fmaxf(fmaxf(x[8], x[9]), fmaxf(x[10], x[11])), fmaxf(fmaxf(x[12], x[13]), fmaxf(x[14], x[15]))));
           }
-          if (fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3])) >= thr_f) {       // rare behind a threshold
+          if (__any_sync(0xffffffffu, fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3])) >= thr_f)) {
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-              if (m[c] >= thr_f) {
+              if (__any_sync(0xffffffffu, m[c] >= thr_f)) {
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
                   const float x = __uint_as_float(v[c][i]);
-                  if (x >= thr_f) {
+                  const bool hit = x >= thr_f;
+                  if (__any_sync(0xffffffffu, hit)) {
                     const int64_t row = r0 + cb + c * 16 + i;
-                    if (row < p.row_end) append_survivor(x, row, thr, p.cnt + ql, krow, p.seg_cap);
+                    // a row that ties the threshold score but loses on the id is dropped by the exact 64-bit compare
+                    const u64 key = (static_cast<u64>(f32_to_ordered(x + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row));
+                    if (hit && row < p.row_end && key >= thr) klist[n_mine++] = key;
                   }
                 }
               }
             }
           }
-        } else {
+        } else if (qok) {
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
 #pragma unroll
@@ -200,6 +208,7 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+    if (p.cnt != nullptr && qok) p.cnt[static_cast<int64_t>(ql) * p.nsub + sub] = n_mine;
   }
 
   tc_fence_before();
@@ -239,6 +248,15 @@ bool make_map(CUtensorMap* map, const void* ptr, uint64_t cols, uint64_t rows, u
 }  // namespace
 
 // Scores queries [q_begin, q_begin+128) against corpus rows [row_begin, row_end) into keys (128, seg_cap).
+// Compact-mode geometry of a segment of `rows` rows: CTAs launched, sub-lists per query, rows per sub-list.
+void clsm_score_tc_geometry(int64_t rows, int* grid, int* nsub, int64_t* subcap) {
+  const int64_t n_tiles = ceil_div64(rows, NT);
+  int g = clsm_sm_count();
+  if (g > n_tiles) g = static_cast<int>(n_tiles);
+  if (g < 1) g = 1;
+  *grid = g; *nsub = 2 * g; *subcap = ceil_div64(n_tiles, g) * (NT / 2);
+}
+
 int clsm_score_keys_tc(const void* Qn, int64_t nQ, int64_t q_begin, const void* Cn, int64_t N, int H,
                        int64_t row_begin, int64_t row_end, unsigned long long* keys, int64_t seg_cap,
                        const unsigned long long* thr, int* cnt, cudaStream_t st) {
@@ -249,6 +267,9 @@ int clsm_score_keys_tc(const void* Qn, int64_t nQ, int64_t q_begin, const void* 
   p.hchunks = H / 64;
   p.n_tiles = static_cast<int>(ceil_div64(row_end - row_begin, NT));
   p.keys = keys; p.seg_cap = seg_cap; p.thr = thr; p.cnt = cnt;
+  int geo_grid = 0;
+  clsm_score_tc_geometry(row_end - row_begin, &geo_grid, &p.nsub, &p.subcap);
+  CLSM_REQUIRE(cnt == nullptr || static_cast<int64_t>(p.nsub) * p.subcap <= seg_cap, "cos_topk(bf16): survivor lists too small for this segment");
   const int q_bytes = p.hchunks * QB * 128;
   const int stage_bytes = p.hchunks * NT * 128;
   int stages = (SMEM_LIMIT - 2048 - q_bytes) / stage_bytes;

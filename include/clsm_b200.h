@@ -248,9 +248,10 @@ int clsm_topk_merge(const float* scores, const int64_t* ids, int n_parts, int64_
 /* bf16 corpus, tensor-core scoring (the production retrieval path): Qn (nQ, H) and Cn (N, H) are
  * L2-normalised bf16 (clsm_normalize_rows_bf16), H = 64 or 128 (other widths: clsm_cos_topk).  The corpus is read once per block of
  * 128 queries by a tcgen05 kernel; selection is the same exact radix select, so the order and the
- * independence from sharding are those of clsm_cos_topk.  The workspace grows with N up to 1 GiB (N >= 1.4 M
- * rows): segments after the first are scanned behind the running k-th best score, grow fourfold, and each
- * query's survivors go to a list that can hold a whole segment, so no corpus order can overflow it. */
+ * independence from sharding are those of clsm_cos_topk.  The corpus is scanned in segments (4 096 rows, then to 65 536,
+ * to 1 Mi, then 1 Mi at a time), each behind the k-th best key of the rows before it; a row that beats it goes to a
+ * per-query survivor list that can hold a whole segment, so no corpus order can overflow it.  The workspace
+ * therefore grows with N up to about 1 GiB (N >= 1.1 M rows). */
 int clsm_normalize_rows_bf16(const float* sem, int64_t N, int H, void* vec, void* stream);
 size_t clsm_cos_topk_bf16_workspace_bytes(int64_t nQ, int64_t N, int k);
 int clsm_cos_topk_bf16(const void* Qn, int64_t nQ, const void* Cn, int64_t N, int H, int k,

@@ -4,7 +4,7 @@ import torch
 from dnn_page_vectors_b200 import _lib
 from tests.gpu_util import P, ST, DEV
 lib = _lib.lib
-N, Q, H, k = 1_000_000, 128, 128, 100
+N, Q, H, k = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000, int(sys.argv[2]) if len(sys.argv) > 2 else 128, 128, 100
 g = torch.Generator(device="cuda").manual_seed(3)
 c = torch.nn.functional.normalize(torch.randn((N, H), generator=g, device="cuda"), dim=1).to(torch.bfloat16)
 q = torch.nn.functional.normalize(torch.randn((Q, H), generator=g, device="cuda"), dim=1).to(torch.bfloat16)
