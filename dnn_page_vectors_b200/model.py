@@ -634,8 +634,7 @@ class CLSM(object):
             self._head[("ws", name)] = t
         return t
 
-    # ---- persistence (cnn_dssm_tf.py:193,199-206).  h5py is not available here, so the on-disk
-    # format is a torch file holding the same tensors in the reference's layouts.
+    # ---- persistence (cnn_dssm_tf.py:193,199-206)
     def to_json(self):
         return json.dumps({"class_name": "CLSM", "config": dict(self.params.to_dict(),
                            query_length=self.query_length, document_length=self.document_length,
@@ -649,14 +648,34 @@ class CLSM(object):
         self.doc_model.set_weights(w["doc"], theano_kernels)
 
     def save_weights(self, path):
-        torch.save({"weights": self.get_weights()}, path)
+        """model.save_weights (cnn_dssm_tf.py:206).  The container follows the extension: '.npz' = the dependency-free
+        interchange with Keras-1 layer / weight names and kernel layouts (keras_io.py), '.h5' / '.hdf5' = the reference's
+        own HDF5 layout (needs h5py), anything else = a torch file of plain tensors."""
+        from . import keras_io
+        kind = keras_io.container_of(path)
+        if kind == "torch":
+            w = self.get_weights()
+            torch.save({"weights": {t: {k: torch.as_tensor(v) for k, v in w[t].items()} for t in w}}, path)
+            return
+        layers = keras_io.export_layers(self.get_weights(), len(self.query_model.windows))
+        (keras_io.save_npz if kind == "npz" else keras_io.save_h5)(path, layers)
 
     def load_weights(self, path, theano_kernels=False):
-        self.set_weights(torch.load(path, weights_only=False)["weights"], theano_kernels)
+        """Loads what save_weights wrote -- or, for '.npz' / '.h5', a checkpoint trained by the REFERENCE
+        (ModelCheckpoint / save_weights / model.save of cnn_dssm_tf.py:193,199-206; theano_kernels=True for the
+        Theano backend, whose kernels are applied flipped)."""
+        from . import keras_io
+        kind = keras_io.container_of(path)
+        if kind == "torch":
+            w = torch.load(path, weights_only=True)["weights"]        # tensors only: nothing in the file is executed
+            self.set_weights({t: {k: v.numpy() for k, v in w[t].items()} for t in w}, theano_kernels)
+            return
+        layers = keras_io.load_npz(path) if kind == "npz" else keras_io.load_h5(path)
+        self.set_weights(keras_io.import_layers(layers, theano_kernels))
 
     def save(self, path):
-        """Whole model: architecture JSON, weights, optimizer state and step (resume-able,
-        which the reference's save is not)."""
+        """Whole model: architecture JSON, weights, optimizer state and step (resume-able, which the reference's
+        save is not).  A torch file of plain tensors / strings / ints (loadable with weights_only=True)."""
         if self.dp is not None:
             for tower in (self.query_model, self.doc_model):
                 self.dp.gather_masters(tower)
@@ -666,7 +685,7 @@ class CLSM(object):
         torch.save(st, path)
 
     def load(self, path):
-        st = torch.load(path, weights_only=False)
+        st = torch.load(path, weights_only=True)
         self.iterations = int(st["iterations"])
         for tower, key in ((self.query_model, "query"), (self.doc_model, "doc")):
             for name, t in tower.state().items():

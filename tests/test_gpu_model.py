@@ -470,3 +470,26 @@ def test_two_stream_step_is_bit_identical_to_one_stream():
         for k in a[i]:
             assert torch.equal(a[i][k], b_[i][k]), k
     assert torch.equal(a[3], b_[3]) and torch.equal(a[4], b_[4])
+
+
+def test_keras_checkpoint_interchange_on_the_model(tmp_path):
+    """save_weights / load_weights / ModelCheckpoint with the '.npz' container (Keras-1 names and kernel layouts):
+    a second model that loads the file predicts exactly what the first one does."""
+    cfg = dict(CFG_SMALL, B=8)
+    x = synth(21, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"])
+    net, _, _ = build("fp32", "relu", conv_impl="simt", **cfg)
+    net.train_on_batch(x)
+    p = str(tmp_path / "weights.00.npz")
+    ModelCheckpoint(str(tmp_path / "weights.{epoch:02d}.npz"))(net, 0, {})
+    from dnn_page_vectors_b200 import keras_io
+    layers = keras_io.load_npz(p)
+    assert list(layers) == ["sequential_1", "sequential_2"]
+    assert dict(layers["sequential_2"])["convolution1d_3_W"].shape == (3, 1, cfg["D"], cfg["F"])
+    net2, _, _ = build("fp32", "relu", conv_impl="simt", seed=5, **cfg)
+    assert not np.array_equal(net2.predict(x), net.predict(x))
+    net2.load_weights(p)
+    np.testing.assert_array_equal(net2.predict(x), net.predict(x))
+    net.save_weights(str(tmp_path / "w.pt"))                   # torch container: plain tensors, loaded with weights_only=True
+    net3, _, _ = build("fp32", "relu", conv_impl="simt", seed=6, **cfg)
+    net3.load_weights(str(tmp_path / "w.pt"))
+    np.testing.assert_array_equal(net3.predict(x), net.predict(x))
