@@ -102,6 +102,22 @@ emb_gather_bf16_drop_kernel(const int32_t* __restrict__ tok, int64_t n_tok, cons
   dst[1] = v[1];
 }
 
+// out[r, c] = x[r, c] * mask(r, c) * inv_keep: the same counter-based mask as the embedding dropout, on any (n, H) matrix
+__global__ void dropout_rows_kernel(const float* __restrict__ x, int64_t n, int H, float inv_keep, uint32_t thr, uint64_t seed,
+                                    float* __restrict__ out) {
+  const int nblk = (H + 15) / 16;
+  const int64_t item = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (item >= n * nblk) return;
+  const int64_t r = item / nblk;
+  const int blk = static_cast<int>(item - r * nblk);
+  uint32_t bytes[4];
+  dropout_bytes16(seed, static_cast<uint64_t>(r), static_cast<uint32_t>(blk), bytes);
+  for (int c = 0; c < 16; ++c) {
+    const int col = blk * 16 + c;
+    if (col < H) out[r * H + col] = dropout_keep(bytes, c, thr) ? x[r * H + col] * inv_keep : 0.0f;
+  }
+}
+
 __global__ void check_ids_kernel(const int32_t* __restrict__ tok, int64_t n, int64_t n_rows, int32_t* __restrict__ n_bad) {
   const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const bool bad = i < n && (tok[i] < 0 || tok[i] >= n_rows);
@@ -201,6 +217,19 @@ int clsm_check_token_ids(const int32_t* tok, int64_t n_tok, int64_t n_rows, int3
   CLSM_CUDA(cudaMemsetAsync(n_bad, 0, sizeof(int32_t), st));
   if (n_tok == 0) return CLSM_OK;
   check_ids_kernel<<<static_cast<unsigned>(ceil_div64(n_tok, 256)), 256, 0, st>>>(tok, n_tok, n_rows, n_bad);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
+}
+
+int clsm_dropout_rows(const float* x, int64_t n, int H, float keep, uint64_t seed, float* out, void* stream) {
+  CLSM_REQUIRE(n >= 0 && H > 0 && keep > 0.0f, "dropout_rows: bad arguments");
+  if (n == 0) return CLSM_OK;
+  const uint32_t thr = keep_threshold(keep);
+  const bool drop = keep < 1.0f && thr < 256u;
+  CLSM_REQUIRE(!drop || thr > 0, "dropout_rows: keep %g rounds to a keep probability of 0/256", keep);
+  const int64_t total = n * ((H + 15) / 16);
+  dropout_rows_kernel<<<static_cast<unsigned>(ceil_div64(total, 256)), 256, 0, as_stream(stream)>>>(
+      x, n, H, drop ? dropout_scale(keep) : 1.0f, drop ? thr : 256u, seed, out);
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
 }

@@ -206,6 +206,10 @@ class Tower(object):
         call("clsm_dense_fwd", _ptr(b["pooled"]), S, self.P, self.P, _ptr(self.Wd), _ptr(self.bd), self.H,
              ACT[net.params.activation] | (MATH_TF32 if self.bf16 else 0), _ptr(b["sem"]), st)
         b["keep"], b["seed"] = keep, seed
+        b["keep2"] = 1.0
+        if train and net.post_dense_dropout:           # v1's second Dropout, dssm_cnn/cnn_dssm.py:149
+            b["keep2"], b["seed2"] = 1.0 - net.params.dropout_prob[1], seed ^ 0x5DEECE66D
+            call("clsm_dropout_rows", _ptr(b["sem"]), S, self.H, b["keep2"], b["seed2"], _ptr(b["sem"]), st)
         return b["sem"]
 
     # ---- backward: gradient of the loss wrt sem in b['dsem']; fills flat_g and the sparse table grad
@@ -214,6 +218,8 @@ class Tower(object):
         st = _stream()
         S, n_tok = b["S"], b["n_tok"]
         act = ACT[net.params.activation]
+        if b.get("keep2", 1.0) < 1.0:                  # dropped semantic units get no gradient, kept ones 1/keep of it
+            call("clsm_dropout_rows", _ptr(b["dsem"]), S, self.H, b["keep2"], b["seed2"], _ptr(b["dsem"]), st)
         call("clsm_dense_bwd", _ptr(b["pooled"]), _ptr(b["sem"]), _ptr(b["dsem"]), S, self.P, self.P, _ptr(self.Wd),
              self.H, act | (MATH_TF32 if self.bf16 else 0), _ptr(self.g_Wd), _ptr(self.g_bd), _ptr(b["G"]),
              _ptr(b["ws"]), b["ws_bytes"], st)
@@ -312,7 +318,12 @@ class CLSM(object):
     """
 
     def __init__(self, params=None, query_length=20, document_length=975, embedding_weights=None,
-                 vocab_size=None, device=None, conv_impl="auto", lazy_table_adam=False):
+                 vocab_size=None, device=None, conv_impl="auto", lazy_table_adam=False,
+                 shared_doc_tower=True, post_dense_dropout=False):
+        """shared_doc_tower=False, post_dense_dropout=True is the v1 model (dssm_cnn/cnn_dssm.py:105-167): the
+        query, the positive document and every negative document each get their OWN tower (embedding table included,
+        :160-164) and a second Dropout(dropout_prob[1]) sits between Dense and relu (:148-150).  The default is v2
+        (dssm_cnn_v2): one document tower shared by the positive and all negatives, no second dropout."""
         if not torch.cuda.is_available():
             raise RuntimeError("dnn_page_vectors_b200 needs a CUDA device (sm_100a); there is no CPU path")
         self.params = params if params is not None else ModelParams()
@@ -328,8 +339,18 @@ class CLSM(object):
                 raise ValueError("pass embedding_weights (word level) or vocab_size (char/ngram level)")
             embedding_weights = self.rng.uniform(-0.05, 0.05, size=(vocab_size, self.params.embedding_dim))
         self.embedding_weights = np.asarray(embedding_weights)
+        self.shared_doc_tower = bool(shared_doc_tower)
+        self.post_dense_dropout = bool(post_dense_dropout)
+        if self.post_dense_dropout and self.params.activation not in ("relu", "linear"):
+            raise ValueError("the second dropout sits before the activation (dssm_cnn/cnn_dssm.py:148-150); it is applied "
+                             "after it here, which is the same thing only for relu / linear")
         self.query_model = self.model(self.query_length)
-        self.doc_model = self.model(self.document_length)
+        if self.shared_doc_tower:
+            self.doc_model = self.model(self.document_length)
+            self.doc_models = [self.doc_model]
+        else:
+            self.doc_models = [self.model(self.document_length) for _ in range(1 + self.J)]
+            self.doc_model = self.doc_models[0]          # the positive-document tower (encode_pages uses it)
         self.iterations = 0
         self.compiled = False
         self.dp = None                 # set by parallel.DataParallel
@@ -485,6 +506,12 @@ class CLSM(object):
 
     # ---- Keras-like batch API (host numpy in, python floats out)
     def train_on_batch(self, x, y=None):
+        if not self.shared_doc_tower:
+            h = self._step_independent(x, True)
+            if h is None:
+                return [0.0, 0.0]
+            la = h["loss_acc"].cpu().numpy()
+            return [float(la[0]), float(la[1])]
         B, bq, bd = self._stage(x, True)
         if B == 0:
             return [0.0, 0.0]
@@ -493,6 +520,9 @@ class CLSM(object):
         return [float(la[0]), float(la[1])]
 
     def test_on_batch(self, x, y=None):
+        if not self.shared_doc_tower:
+            la = self._step_independent(x, False)["loss_acc"].cpu().numpy()
+            return [float(la[0]), float(la[1])]
         B, bq, bd = self._stage(x, False)
         self.query_model.forward(bq, False)
         self.doc_model.forward(bd, False)
@@ -500,10 +530,54 @@ class CLSM(object):
         return [float(la[0]), float(la[1])]
 
     def predict_on_batch(self, x):
+        if not self.shared_doc_tower:
+            return self._step_independent(x, False)["prob"][:, :1].cpu().numpy()
         B, bq, bd = self._stage(x, False)
         self.query_model.forward(bq, False)
         self.doc_model.forward(bd, False)
         return self._forward_head(B, bq, bd, False)["prob"][:, :1].cpu().numpy()
+
+    # ---- the v1 wiring: 2 + J independent towers (dssm_cnn/cnn_dssm.py:153-185), same kernels
+    def _step_independent(self, x, train):
+        """One step (train) or forward (eval) of the model with one tower per input.  Each document tower sees its own
+        (B, Ld) token matrix; their semantic vectors are interleaved into the (B, 1+J, H) layout the loss kernel reads,
+        and its gradient is dealt back tower by tower.  Towers are stepped one after the other on one stream."""
+        if len(x) != 2 + self.J:
+            raise ValueError("expected %d input arrays [query, pos_doc, %d neg_docs], got %d" % (2 + self.J, self.J, len(x)))
+        if self.dp is not None:
+            raise RuntimeError("data parallelism is wired for the shared-document-tower model only")
+        B = int(np.asarray(x[0]).shape[0])
+        if B == 0:
+            return None
+        towers = [self.query_model] + self.doc_models
+        bufs = [t.buffers(B, train) for t in towers]
+        for b, a in zip(bufs, x):
+            b["tok"].copy_(torch.as_tensor(np.ascontiguousarray(a, dtype=np.int32)), non_blocking=False)
+        H = self.query_model.H
+        key = ("indep", B, train)
+        hb = self._head.get(key)
+        if hb is None:
+            hb = {"sem": torch.empty((B, 1 + self.J, H), dtype=torch.float32, device=self.device),
+                  "dsem": torch.empty((B, 1 + self.J, H), dtype=torch.float32, device=self.device)}
+            self._head[key] = hb
+        base = (self.params.seed << 20) + self.iterations * (2 + self.J)
+        for i, (t, b) in enumerate(zip(towers, bufs)):
+            t.forward(b, train, base + i)
+            if i > 0:
+                hb["sem"][:, i - 1, :].copy_(b["sem"])
+        h = self._head_bufs(B)
+        bq = bufs[0]
+        call("clsm_sim_loss", _ptr(bq["sem"]), _ptr(hb["sem"]), B, self.J, H, float(self.params.GAMMA), B,
+             _ptr(h["cos"]), _ptr(h["prob"]), _ptr(h["loss_acc"]),
+             _ptr(bq["dsem"]) if train else C.c_void_p(0), _ptr(hb["dsem"]) if train else C.c_void_p(0), _stream())
+        if train:
+            self.iterations += 1
+            for i, (t, b) in enumerate(zip(towers, bufs)):
+                if i > 0:
+                    b["dsem"].copy_(hb["dsem"][:, i - 1, :])
+                t.backward(b)
+                t.adam(b, self.iterations)
+        return h
 
     predict = predict_on_batch
 
@@ -641,11 +715,18 @@ class CLSM(object):
                            vocab_rows=int(self.embedding_weights.shape[0]))})
 
     def get_weights(self):
-        return {"query": self.query_model.get_weights(), "doc": self.doc_model.get_weights()}
+        w = {"query": self.query_model.get_weights(), "doc": self.doc_model.get_weights()}
+        if not self.shared_doc_tower:
+            w["docs"] = [t.get_weights() for t in self.doc_models]       # 'doc' is docs[0], the positive-document tower
+        return w
 
     def set_weights(self, w, theano_kernels=False):
         self.query_model.set_weights(w["query"], theano_kernels)
-        self.doc_model.set_weights(w["doc"], theano_kernels)
+        if self.shared_doc_tower:
+            self.doc_model.set_weights(w["doc"], theano_kernels)
+        else:
+            for t, wt in zip(self.doc_models, w["docs"]):
+                t.set_weights(wt, theano_kernels)
 
     def save_weights(self, path):
         """model.save_weights (cnn_dssm_tf.py:206).  The container follows the extension: '.npz' = the dependency-free
@@ -653,6 +734,13 @@ class CLSM(object):
         own HDF5 layout (needs h5py), anything else = a torch file of plain tensors."""
         from . import keras_io
         kind = keras_io.container_of(path)
+        if not self.shared_doc_tower:
+            if kind != "torch":
+                raise ValueError("the Keras-named containers describe the two-tower v2 model; save the v1 model as a torch file")
+            w = self.get_weights()
+            torch.save({"weights": {"query": {k: torch.as_tensor(v) for k, v in w["query"].items()},
+                                    "docs": [{k: torch.as_tensor(v) for k, v in d.items()} for d in w["docs"]]}}, path)
+            return
         if kind == "torch":
             w = self.get_weights()
             torch.save({"weights": {t: {k: torch.as_tensor(v) for k, v in w[t].items()} for t in w}}, path)
@@ -668,7 +756,11 @@ class CLSM(object):
         kind = keras_io.container_of(path)
         if kind == "torch":
             w = torch.load(path, weights_only=True)["weights"]        # tensors only: nothing in the file is executed
-            self.set_weights({t: {k: v.numpy() for k, v in w[t].items()} for t in w}, theano_kernels)
+            if "docs" in w:
+                self.set_weights({"query": {k: v.numpy() for k, v in w["query"].items()},
+                                  "docs": [{k: v.numpy() for k, v in d.items()} for d in w["docs"]]}, theano_kernels)
+            else:
+                self.set_weights({t: {k: v.numpy() for k, v in w[t].items()} for t in w}, theano_kernels)
             return
         layers = keras_io.load_npz(path) if kind == "npz" else keras_io.load_h5(path)
         self.set_weights(keras_io.import_layers(layers, theano_kernels))
@@ -682,14 +774,18 @@ class CLSM(object):
         st = {"json": self.to_json(), "iterations": self.iterations,
               "query": {k: v.cpu() for k, v in self.query_model.state().items()},
               "doc": {k: v.cpu() for k, v in self.doc_model.state().items()}}
+        if not self.shared_doc_tower:
+            st["docs"] = [{k: v.cpu() for k, v in t.state().items()} for t in self.doc_models]
         torch.save(st, path)
 
     def load(self, path):
         st = torch.load(path, weights_only=True)
         self.iterations = int(st["iterations"])
-        for tower, key in ((self.query_model, "query"), (self.doc_model, "doc")):
+        pairs = [(self.query_model, st["query"])]
+        pairs += [(self.doc_model, st["doc"])] if self.shared_doc_tower else list(zip(self.doc_models, st["docs"]))
+        for tower, saved in pairs:
             for name, t in tower.state().items():
-                t.copy_(st[key][name])
+                t.copy_(saved[name])
             tower.refresh_compute_copies(table_too=True)
         return self
 

@@ -73,6 +73,11 @@ int clsm_emb_gather_mask(const int32_t* tok, int64_t n_tok, const void* table, i
                          int D, int ld_table, int dtype, void* X, int ldx,
                          float keep, uint64_t seed, uint16_t* mask_bits, void* stream);
 float clsm_dropout_scale(float keep);
+/* out (n, H) = x * mask / keep with the same counter-based mask (clsm_dropout_mask(n, H, keep, seed) exports it);
+ * out may be x.  replaces the SECOND Dropout of the v1 model, Dense -> Dropout(dropout_prob[1]) -> relu
+ * (dssm_cnn/cnn_dssm.py:148-150), applied to the semantic vectors (relu commutes with the non-negative scaling) and,
+ * in the backward pass, to their gradient. */
+int clsm_dropout_rows(const float* x, int64_t n, int H, float keep, uint64_t seed, float* out, void* stream);
 
 /* ---- conv weights: reference layout -> compute layout ------------------------------------
  * W_ref fp32 (k, D, F)  [Keras-1 Convolution1D kernel (k,1,D,F), cnn_dssm_tf.py:85-91]

@@ -86,11 +86,14 @@ def conv_pool_fwd(X, W, b, act="relu"):
     return pooled, arg
 
 
-def tower_fwd(tok, p, act="relu", mask=None, keep=1.0):
+def tower_fwd(tok, p, act="relu", mask=None, keep=1.0, post_mask=None, post_keep=1.0):
     """tok (S, L) int -> dict with X, pooled, argmax, sem.
 
     p: {'E': (V1, D), 'convW': [(k, D, F)], 'convb': [(F,)], 'Wd': (P, H), 'bd': (H,)}
     mask: optional (S, L, D) 0/1 keep-mask of Dropout(1-keep); X = E[tok]*mask/keep.
+    post_mask: optional (S, H) keep-mask of the v1 model's second Dropout, which sits between Dense and the
+    activation (dssm_cnn/cnn_dssm.py:148-150: Dense -> Dropout(dropout_prob[1]) -> relu).  relu commutes with a
+    non-negative scaling, so relu(pre * m / keep) = relu(pre) * m / keep, which is what is computed here.
     """
     X = p["E"][tok]
     if mask is not None:
@@ -103,6 +106,9 @@ def tower_fwd(tok, p, act="relu", mask=None, keep=1.0):
     P = np.concatenate(pooled, axis=1)
     A = np.concatenate(args, axis=1)
     Z = act_fwd(P @ p["Wd"] + p["bd"][None, :], act)
+    if post_mask is not None:
+        assert act in ("relu", "linear"), "the second dropout commutes only with relu / linear"
+        Z = Z * post_mask / post_keep
     return {"X": X, "pooled": P, "argmax": A, "sem": Z}
 
 
@@ -162,10 +168,12 @@ def sim_loss_bwd(zq, zd, fw, gamma=10.0, batch_total=None):
 # --------------------------------------------------------------------------
 # tower backward
 # --------------------------------------------------------------------------
-def tower_bwd(tok, p, fw, dZ, act="relu", mask=None, keep=1.0):
+def tower_bwd(tok, p, fw, dZ, act="relu", mask=None, keep=1.0, post_mask=None, post_keep=1.0):
     """Returns grads dict {'E','convW','convb','Wd','bd'} for one tower call."""
     X, P, A, Z = fw["X"], fw["pooled"], fw["argmax"], fw["sem"]
     S, L, D = X.shape
+    if post_mask is not None:                    # Z = act(pre) * m / keep: dropped units get no gradient
+        dZ = dZ * post_mask / post_keep
     dpre = dZ * act_grad_from_output(Z, act)
     g = {"Wd": P.T @ dpre, "bd": dpre.sum(axis=0)}
     dP = dpre @ p["Wd"].T
@@ -272,6 +280,25 @@ def topk_merge(score_parts, id_parts, k):
         out_s[i] = sc[i][order]
         out_i[i] = ids[i][order]
     return out_s, out_i
+
+
+def model_v1_loss_and_grads(q_tok, d_tok, pq, pds, act="relu", gamma=10.0, masks=None, keep=1.0,
+                            post_masks=None, post_keep=1.0):
+    """The v1 model (dssm_cnn/cnn_dssm.py:153-185): FIVE independent towers -- the query, the positive document and
+    every negative document each have their own embedding table and weights (:160-164) -- and a second dropout after
+    the Dense layer (:149).  d_tok (B, 1+J, Ld); pds: list of 1+J parameter dicts; masks / post_masks: optional lists
+    [query, doc_0 .. doc_J] of (B, L, D) / (B, H) keep masks.  Returns head, gq, [gd_j], fq, [fd_j]."""
+    B, J1, Ld = d_tok.shape
+    m = masks or [None] * (1 + J1)
+    pm = post_masks or [None] * (1 + J1)
+    fq = tower_fwd(q_tok, pq, act, m[0], keep, pm[0], post_keep)
+    fds = [tower_fwd(d_tok[:, j], pds[j], act, m[1 + j], keep, pm[1 + j], post_keep) for j in range(J1)]
+    zd = np.stack([f["sem"] for f in fds], axis=1)
+    head = sim_loss_fwd(fq["sem"], zd, gamma)
+    dzq, dzd = sim_loss_bwd(fq["sem"], zd, head, gamma)
+    gq = tower_bwd(q_tok, pq, fq, dzq, act, m[0], keep, pm[0], post_keep)
+    gds = [tower_bwd(d_tok[:, j], pds[j], fds[j], dzd[:, j], act, m[1 + j], keep, pm[1 + j], post_keep) for j in range(J1)]
+    return head, gq, gds, fq, fds
 
 
 # --------------------------------------------------------------------------

@@ -493,3 +493,52 @@ def test_keras_checkpoint_interchange_on_the_model(tmp_path):
     net3, _, _ = build("fp32", "relu", conv_impl="simt", seed=6, **cfg)
     net3.load_weights(str(tmp_path / "w.pt"))
     np.testing.assert_array_equal(net3.predict(x), net.predict(x))
+
+
+def test_v1_five_independent_towers_with_second_dropout_match_the_oracle():
+    """The v1 model (dssm_cnn/cnn_dssm.py:105-185): query, positive and each negative document have their OWN tower
+    (embedding table included) and Dropout(dropout_prob[1]) sits between Dense and relu.  One training step with both
+    dropouts on, replayed in the oracle through the exported masks: loss, and every tower's weights after the Adam
+    step; then the evaluation loss (no dropout) on the updated weights."""
+    B, J, Lq, Ld, V, D, windows, F, H = 6, 3, 8, 20, 120, 100, (3, 4), 150, 150
+    mp = ModelParams(embedding_dim=D, batch_size=B, filter_sizes=windows, num_filters=F, hidden_dims=H, J=J,
+                     dropout_prob=(0.25, 0.5), activation="relu", precision="fp32")
+    rng = np.random.RandomState(3)
+    ps = [oracle_params(rng, V + 1, D, windows, F, H) for _ in range(2 + J)]
+    net = CLSM(mp, Lq, Ld, embedding_weights=ps[0]["E"], device=DEV, conv_impl="simt",
+               shared_doc_tower=False, post_dense_dropout=True).compile()
+    assert len(net.doc_models) == 1 + J
+    net.set_weights({"query": to_model_weights(ps[0]), "docs": [to_model_weights(p) for p in ps[1:]]})
+    x = synth(7, B, J, Lq, Ld, V)
+    q64, d64 = x[0].astype(np.int64), np.stack(x[1:], axis=1).astype(np.int64)
+    keep, keep2 = 0.75, 0.5
+    base = (mp.seed << 20) + net.iterations * (2 + J)
+    masks, post_masks = [], []
+    for i in range(2 + J):
+        L = Lq if i == 0 else Ld
+        m1 = torch.empty((B * L, D), dtype=torch.uint8, device=DEV)
+        m2 = torch.empty((B, H), dtype=torch.uint8, device=DEV)
+        call("clsm_dropout_mask", B * L, D, keep, base + i, P(m1), ST())
+        call("clsm_dropout_mask", B, H, keep2, (base + i) ^ 0x5DEECE66D, P(m2), ST())
+        masks.append(m1.cpu().numpy().reshape(B, L, D).astype(np.float64))
+        post_masks.append(m2.cpu().numpy().astype(np.float64))
+    assert 0.3 < post_masks[0].mean() < 0.7
+    head, gq, gds, _, _ = O.model_v1_loss_and_grads(q64, d64, ps[0], ps[1:], masks=masks, keep=keep,
+                                                    post_masks=post_masks, post_keep=keep2)
+    l, _ = net.train_on_batch(x)
+    assert abs(l - head["loss"]) <= 2e-5 * max(1.0, head["loss"]), (l, head["loss"])
+    ops = copy.deepcopy(ps)
+    for p_, g in zip(ops, [gq] + gds):
+        for (name, arr), (_, grad) in zip(O.flat_params(p_), O.flat_grads(g)):
+            O.adam_step(arr, np.zeros_like(arr), np.zeros_like(arr), grad, 1)
+    w = net.get_weights()
+    for got_t, want in zip([w["query"]] + w["docs"], ops):
+        for got, ref in ((got_t["E"], want["E"]), (got_t["convW1"], want["convW"][1]), (got_t["Wd"], want["Wd"])):
+            err = np.abs(got - ref)
+            assert (err > 2e-5).mean() < 1e-3 and err.max() < 2.1e-3, ((err > 2e-5).mean(), err.max())
+    # towers are independent: the negative towers' tables differ from each other after the step
+    assert not np.array_equal(w["docs"][1]["E"], w["docs"][2]["E"])
+    l_eval, _ = net.test_on_batch(x)
+    h2, _, _, _, _ = O.model_v1_loss_and_grads(q64, d64, ops[0], ops[1:])
+    assert abs(l_eval - h2["loss"]) <= 5e-5 * max(1.0, h2["loss"])
+    assert net.predict(x).shape == (B, 1)
