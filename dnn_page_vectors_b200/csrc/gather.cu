@@ -234,6 +234,16 @@ int clsm_dropout_rows(const float* x, int64_t n, int H, float keep, uint64_t see
   return CLSM_OK;
 }
 
+int clsm_copy_rows_strided(const void* src, size_t src_pitch, void* dst, size_t dst_pitch, size_t width_bytes,
+                           int64_t rows, void* stream) {
+  CLSM_REQUIRE(src != nullptr && dst != nullptr && rows >= 0 && src_pitch >= width_bytes && dst_pitch >= width_bytes,
+               "copy_rows_strided: bad arguments");
+  if (rows == 0 || width_bytes == 0) return CLSM_OK;
+  CLSM_CUDA(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width_bytes, static_cast<size_t>(rows), cudaMemcpyDefault,
+                              as_stream(stream)));
+  return CLSM_OK;
+}
+
 float clsm_dropout_scale(float keep) { return keep < 1.0f ? dropout_scale(keep) : 1.0f; }
 
 int clsm_emb_gather_h(const int32_t* tok_h, int32_t* tok_d, int64_t n_tok, const void* table,

@@ -399,8 +399,8 @@ class CLSM(object):
 
     def _stage_tensors(self, x, train):
         """Batches handed over as int32 torch tensors (pinned host memory, or already on the device): no host-side
-        repacking.  Each array goes to the device with one asynchronous contiguous copy and the (pair, document)
-        interleave of the document tower happens there."""
+        repacking.  Each array goes to the device with one asynchronous copy; the document inputs land directly in
+        their slots of the document tower's interleaved (pair, document) token matrix (a strided copy each)."""
         B = int(x[0].shape[0])
         for a in x:
             if a.dtype != torch.int32 or not a.is_contiguous():
@@ -408,12 +408,11 @@ class CLSM(object):
         bq = self.query_model.buffers(B, train)
         bd = self.doc_model.buffers(B * (1 + self.J), train)
         bq["tok"].copy_(x[0], non_blocking=True)
-        stage = bd.get("tok_stage")
-        if stage is None:
-            stage = bd["tok_stage"] = torch.empty((1 + self.J, B, self.document_length), dtype=torch.int32, device=self.device)
-        for j in range(1 + self.J):
-            stage[j].copy_(x[1 + j], non_blocking=True)
-        bd["tok"].view(B, 1 + self.J, self.document_length).copy_(stage.permute(1, 0, 2))
+        Ld, n = self.document_length, 1 + self.J
+        st = _stream()
+        for j in range(n):        # one strided copy per input, straight into its slot of the (B, 1+J, Ld) token matrix
+            call("clsm_copy_rows_strided", C.c_void_p(x[1 + j].data_ptr()), Ld * 4, C.c_void_p(bd["tok"].data_ptr() + j * Ld * 4),
+                 n * Ld * 4, Ld * 4, B, st)
         return B, bq, bd
 
     def _head_bufs(self, B):

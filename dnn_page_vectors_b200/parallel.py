@@ -29,6 +29,43 @@ import torch
 import torch.distributed as dist
 
 
+# ---- collectives that also work on CUDA tensors under the gloo backend --------------------------------------------
+# NCCL is the backend on a multi-GPU box.  gloo carries CUDA tensors only for broadcast and all_reduce; the others are
+# staged through the host here, so that the SAME DataParallel code (peer-memory kernels, CUDA IPC mappings, ordering
+# collectives) can run as several processes on ONE GPU -- which is how the single-GPU test box exercises it
+# (tests/test_gpu_dp.py).  Staging synchronises the stream, which only strengthens the ordering the callers rely on.
+def _staged(t, group):
+    return t.is_cuda and dist.get_backend(group) == "gloo"
+
+
+def c_all_gather_into(out, inp, group=None):
+    if _staged(inp, group):
+        o = torch.empty(out.numel(), dtype=out.dtype)           # gloo wants flat (world * n) <- (n)
+        dist.all_gather_into_tensor(o, inp.contiguous().cpu().reshape(-1), group=group)
+        out.copy_(o.view(out.shape))
+    else:
+        dist.all_gather_into_tensor(out, inp, group=group)
+
+
+def c_all_gather(outs, inp, group=None):
+    if _staged(inp, group):
+        o = [torch.empty(t.shape, dtype=t.dtype) for t in outs]
+        dist.all_gather(o, inp.contiguous().cpu(), group=group)
+        for a, b in zip(outs, o):
+            a.copy_(b)
+    else:
+        dist.all_gather(outs, inp, group=group)
+
+
+def c_all_to_all_single(out, inp, out_splits=None, in_splits=None, group=None):
+    if _staged(inp, group):
+        o = torch.empty(out.shape, dtype=out.dtype)
+        dist.all_to_all_single(o, inp.contiguous().cpu(), out_splits, in_splits, group=group)
+        out.copy_(o)
+    else:
+        dist.all_to_all_single(out, inp, out_splits, in_splits, group=group)
+
+
 def shard_range(n, rank, world):
     """Contiguous row range [lo, hi) of shard `rank` (first n % world shards get one extra row)."""
     base, rem = divmod(int(n), int(world))
@@ -47,13 +84,13 @@ def allgather_padded(rows, count, group=None):
     world = dist.get_world_size(group)
     cnt = torch.tensor([int(count)], dtype=torch.int64, device=rows.device)
     counts = [torch.zeros_like(cnt) for _ in range(world)]
-    dist.all_gather(counts, cnt, group=group)
+    c_all_gather(counts, cnt, group=group)
     counts = [int(c.item()) for c in counts]
     cap = max(max(counts), 1)
     send = rows[:cap] if rows.shape[0] >= cap else torch.cat(
         [rows, rows.new_zeros((cap - rows.shape[0],) + tuple(rows.shape[1:]))])
     out = rows.new_empty((world * cap,) + tuple(rows.shape[1:]))
-    dist.all_gather_into_tensor(out, send.contiguous(), group=group)
+    c_all_gather_into(out, send.contiguous(), group=group)
     parts = [out[r * cap:r * cap + counts[r]] for r in range(world)]
     return torch.cat(parts, dim=0), counts
 
@@ -164,7 +201,7 @@ class DataParallel(object):
         # counts: row i of send_cnt goes to ... transpose so that the all-to-all splits by destination rank
         s_t = send_cnt.t().contiguous()                                        # (W, 2): what I send to each rank
         r_t = torch.empty_like(s_t)
-        dist.all_to_all_single(r_t, s_t, group=self.group)
+        c_all_to_all_single(r_t, s_t, group=self.group)
         recv_cnt = r_t.t().contiguous()
         sc, rc = send_cnt.tolist(), recv_cnt.tolist()                          # second (and last) host sync
         out = []
@@ -186,8 +223,8 @@ class DataParallel(object):
                 g["ws"] = torch.empty(g["ws_bytes"], dtype=torch.uint8, device=dev)
                 self._bufs[tag] = g
             ids_in, rows_in = g["ids_in"][:n_in], g["rows_in"][:n_in]
-            dist.all_to_all_single(ids_in, b["uniq"][:n], rc[i], sc[i], group=self.group)
-            dist.all_to_all_single(rows_in, b["dE_rows"][:n], rc[i], sc[i], group=self.group)
+            c_all_to_all_single(ids_in, b["uniq"][:n], rc[i], sc[i], group=self.group)
+            c_all_to_all_single(rows_in, b["dE_rows"][:n], rc[i], sc[i], group=self.group)
             if n_in > 0:
                 call("clsm_emb_scatter", _ptr(ids_in), n_in, _ptr(rows_in), tower.Dpad, tower.D, 1.0, 0, tower.V1,
                      _ptr(g["uniq"]), _ptr(g["n_uniq"]), _ptr(g["rows"]), _ptr(g["row_of_id"]),
@@ -249,7 +286,7 @@ class DataParallel(object):
                 self.gather_masters(tower, state=False)
                 continue
             R = tower.rows_per_owner
-            dist.all_gather_into_tensor(tower.E_c, tower.E_c[self.rank * R:(self.rank + 1) * R], group=self.group)
+            c_all_gather_into(tower.E_c, tower.E_c[self.rank * R:(self.rank + 1) * R], group=self.group)
 
     def gather_masters(self, tower, state=True):
         """Make the fp32 master table (and, with state=True, Adam m/v) complete on every rank
@@ -260,7 +297,7 @@ class DataParallel(object):
             full = t.new_zeros((R * self.world, t.shape[1]))
             mine = full[self.rank * R:(self.rank + 1) * R]
             mine[:hi - lo].copy_(t[lo:hi])
-            dist.all_gather_into_tensor(full, mine, group=self.group)
+            c_all_gather_into(full, mine, group=self.group)
             t.copy_(full[:t.shape[0]])
 
     def reduce_metrics(self, loss_acc):
@@ -274,6 +311,6 @@ class DataParallel(object):
         sc, ids = self.net.topk(query_vecs, local_corpus, k=k, id_base=id_base)
         all_s = sc.new_empty((self.world,) + tuple(sc.shape))
         all_i = ids.new_empty((self.world,) + tuple(ids.shape))
-        dist.all_gather_into_tensor(all_s, sc.contiguous(), group=self.group)
-        dist.all_gather_into_tensor(all_i, ids.contiguous(), group=self.group)
+        c_all_gather_into(all_s, sc.contiguous(), group=self.group)
+        c_all_gather_into(all_i, ids.contiguous(), group=self.group)
         return self.net.topk_merge(all_s, all_i)

@@ -284,6 +284,13 @@ int clsm_cos_topk_bf16(const void* Qn, int64_t nQ, const void* Cn, int64_t N, in
 int clsm_topk_merge_static(const float* scores, const int64_t* ids, int n_parts, int64_t nQ, int k,
                            float* out_score, int64_t* out_id, void* stream);
 
+/* One strided copy (cudaMemcpy2DAsync, any direction): `rows` rows of width_bytes from src (row pitch src_pitch) to dst
+ * (row pitch dst_pitch).  The host model uses it to put each document input of a batch -- pos_doc, neg_doc_j as
+ * separate (B, Ld) arrays, data_helpers.py:196-197 -- straight from pinned host memory into its slot of the
+ * document tower's interleaved (B, 1+J, Ld) token matrix: no staging buffer, no transpose kernel. */
+int clsm_copy_rows_strided(const void* src, size_t src_pitch, void* dst, size_t dst_pitch, size_t width_bytes,
+                           int64_t rows, void* stream);
+
 /* ---- host-buffer convenience (the e2e / drop-in call): ids on the HOST ------------------------
  * Copies tok_h (pinned or pageable) to tok_d on `stream`, then clsm_emb_gather. */
 int clsm_emb_gather_h(const int32_t* tok_h, int32_t* tok_d, int64_t n_tok, const void* table,

@@ -1,4 +1,5 @@
-"""Data-parallel equivalence check, run under torchrun on >= 2 GPUs (tests/test_gpu_dp.py launches it):
+"""Data-parallel equivalence check, run under torchrun on >= 2 GPUs, or as 2 processes on ONE GPU with
+DP_CHECK_ONE_GPU=1 (tests/test_gpu_dp.py launches both forms):
 
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/dp_check.py
 
@@ -20,8 +21,11 @@ from dnn_page_vectors_b200.parallel import DataParallel, shard_range   # noqa: E
 
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
-    dist.init_process_group("nccl")
+    # DP_CHECK_ONE_GPU=1: every rank is a process on cuda:0 (the single-GPU test box): CUDA IPC still maps the peers'
+    # slabs and tables, the small collectives go over gloo (NCCL refuses two ranks on one device)
+    one_gpu = os.environ.get("DP_CHECK_ONE_GPU") == "1"
+    torch.cuda.set_device(0 if one_gpu else int(os.environ.get("LOCAL_RANK", rank)))
+    dist.init_process_group(os.environ.get("DP_CHECK_BACKEND", "gloo" if one_gpu else "nccl"))
     ok = True
     for precision, tol in (("fp32", 3e-6), ("bf16", 3e-6)):
         V, D, F, H, J, Lq, Ld, Bg = 997, 100, 150, 64, 3, 8, 24, 16 * world
@@ -86,7 +90,8 @@ def main():
             t = tower.E_c if tower.E_c is not None else tower.E
             sig = torch.stack([t[:tower.V1].float().double().sum(), tower.flat.double().sum()])
             sigs = [torch.zeros_like(sig) for _ in range(world)]
-            dist.all_gather(sigs, sig)
+            from dnn_page_vectors_b200.parallel import c_all_gather
+            c_all_gather(sigs, sig)
             if any(not torch.equal(s, sigs[0]) for s in sigs):
                 ok = False
                 print("rank %d %s replicas differ" % (rank, precision))
