@@ -129,6 +129,8 @@ __global__ void pool_finalize_kernel(const unsigned long long* __restrict__ keys
 
 int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void* Wt, int k, int F, int Fpad,
                           uint64_t* keys, int ldk, int col0, cudaStream_t st);   // conv_tc.cu
+int clsm_conv_pool_fwd_tok_tc(const int32_t* tok, const void* table, int64_t table_rows, int64_t S, int L, int Dpad,
+                              const void* Wt, int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, cudaStream_t st);
 
 extern "C" {
 
@@ -161,6 +163,21 @@ int clsm_conv_pool_fwd(const void* X, int dtype, int64_t S, int L, int Dpad,
         static_cast<const float*>(Wt), k, F, Fpad, reinterpret_cast<unsigned long long*>(keys), ldk, col0);
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
+}
+
+int clsm_conv_pool_fwd_tok(const int32_t* tok, const void* table, int64_t n_rows, int ld_table, int64_t S, int L, int Dpad,
+                           const void* Wt, int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, void* stream) {
+  CLSM_REQUIRE(tok != nullptr && table != nullptr && n_rows > 0, "conv_pool_fwd_tok: null tokens / table");
+  CLSM_REQUIRE(S >= 0 && L >= k && k >= 1 && F >= 1 && Fpad >= F, "conv_pool_fwd_tok: bad sizes");
+  CLSM_REQUIRE(Dpad % 64 == 0 && ld_table == Dpad && Fpad % 16 == 0 && Fpad <= 512,
+               "conv_pool_fwd_tok: needs a bf16 table with row pitch Dpad (a multiple of 64), Fpad %% 16 == 0, Fpad <= 512");
+  CLSM_REQUIRE(ldk >= col0 + F, "conv_pool_fwd_tok: key row too short");
+  if (S == 0) return CLSM_OK;
+  cudaStream_t st = as_stream(stream);
+  clear_keys_kernel<<<static_cast<unsigned>(ceil_div64(S * F, 256)), 256, 0, st>>>(
+      reinterpret_cast<unsigned long long*>(keys), S, F, ldk, col0);
+  CLSM_LAUNCH_CHECK();
+  return clsm_conv_pool_fwd_tok_tc(tok, table, n_rows, S, L, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
 }
 
 int clsm_pool_finalize(const uint64_t* keys, int64_t S, int P, int ldk, const float* bias,

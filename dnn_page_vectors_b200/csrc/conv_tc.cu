@@ -57,14 +57,16 @@ struct TcParams {
   int xstages, wstages;  // mode 1: xstages = cpj token slots, wstages weight slots of one M tile chunk (16 KB)
   int nreg;              // mode 1: TMEM accumulator regions of NT columns used round-robin by the (tile, M tile) units
   long long* prof;       // optional cycle counters (CLSM_CONV_TC_PROF=1), else nullptr
+  const int32_t* tok;    // GATHER kernels: token ids (n_rows); tmX then maps the embedding TABLE and the token tile is
+                         // fetched row by row with TMA gather4 (ids as row coordinates) -- X is never materialised
 };
 
 using namespace tcptx;
 
 __device__ long long g_conv_tc_prof[8];      // CLSM_CONV_TC_PROF=1 diagnostics
 
-template <bool CLUSTER, int NCH>     // NCH = 16-column chunks per epilogue warp (NT / 32)
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+template <bool CLUSTER, int NCH, bool GATHER = false>     // NCH = 16-column chunks per epilogue warp (NT / 32)
+__global__ void __launch_bounds__(NUM_THREADS + 32, 1)    // GATHER adds an 11th warp: the token-row gather producer
 conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW, const TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -152,7 +154,7 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
         const int r0 = tile * p.NT;
         for (int m = 0; m < p.n_mt; ++m) {
           for (int cc = 0; cc < p.cpj; ++cc) {
-            if (m == 0) {                            // the token tile: one slot per c chunk, loaded once per tile
+            if (m == 0 && !GATHER) {                 // the token tile: one slot per c chunk, loaded once per tile
               mbar_wait(empty_bar(p.wstages + cc), xphase ^ 1u);
               if (elect_one()) {
                 mbar_expect_tx(full_bar(p.wstages + cc), static_cast<uint32_t>(p.xrows) * 128u);
@@ -256,6 +258,37 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
         atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 1), static_cast<unsigned long long>(w_tmem));
         atomicAdd(reinterpret_cast<unsigned long long*>(p.prof + 2), static_cast<unsigned long long>(w_feed));
       }
+    }
+  } else if (GATHER && warp == 2 + NUM_EPI_WARPS) {
+    // ---- token-row gather (inference): the tile's NT + k - 1 token rows come straight from the embedding table, four
+    // rows per TMA gather4 with the token ids as row coordinates, 64 columns (one swizzle row) per c chunk.  Lane l
+    // owns row groups l and l + 32 of the tile and issues them for every chunk; one lane arms the slot's barrier.
+    const int ngroups = p.xrows / 4;
+    uint32_t xphase = 0;
+    for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+      const int64_t r0 = static_cast<int64_t>(tile) * p.NT;
+      int ids[2][4];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int64_t r = r0 + (lane + 32 * h) * 4 + i;
+          ids[h][i] = (lane + 32 * h < ngroups && r < p.n_rows) ? __ldg(p.tok + r) : 0;       // rows past the end: any valid row (masked later)
+        }
+      }
+      for (int cc = 0; cc < p.cpj; ++cc) {
+        mbar_wait(empty_bar(p.wstages + cc), xphase ^ 1u);
+        if (lane == 0) mbar_expect_tx(full_bar(p.wstages + cc), static_cast<uint32_t>(p.xrows) * 128u);
+        __syncwarp();
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int g = lane + 32 * h;
+          if (g < ngroups)
+            tma_gather4_2d(x_ring + cc * x_slot_bytes + static_cast<uint32_t>(g) * 512u, &tmX, cc * KCHUNK,
+                           ids[h][0], ids[h][1], ids[h][2], ids[h][3], full_bar(p.wstages + cc));
+        }
+      }
+      xphase ^= 1u;
     }
   } else {
     const int lq = warp & 3;                           // TMEM lane quarter this warp may read
@@ -411,8 +444,24 @@ bool make_map_2d(CUtensorMap* map, const void* ptr, uint64_t cols, uint64_t rows
 
 }  // namespace
 
+static int conv_fwd_tc_impl(const void* X, const int32_t* tok, int64_t table_rows, int64_t S, int L, int Dpad, const void* Wt,
+                            int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, cudaStream_t st);
+
 int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void* Wt, int k, int F, int Fpad,
                           uint64_t* keys, int ldk, int col0, cudaStream_t st) {
+  return conv_fwd_tc_impl(X, nullptr, 0, S, L, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
+}
+
+// Same kernel, token tile fetched from the embedding table by TMA gather4 (tok != nullptr, X = the (table_rows, Dpad)
+// bf16 table): the inference path, no dropout, X never written.
+int clsm_conv_pool_fwd_tok_tc(const int32_t* tok, const void* table, int64_t table_rows, int64_t S, int L, int Dpad,
+                              const void* Wt, int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, cudaStream_t st) {
+  return conv_fwd_tc_impl(table, tok, table_rows, S, L, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
+}
+
+static int conv_fwd_tc_impl(const void* X, const int32_t* tok, int64_t table_rows, int64_t S, int L, int Dpad, const void* Wt,
+                            int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, cudaStream_t st) {
+  const bool gather = tok != nullptr;
   const int64_t n_rows = S * L;
   CLSM_REQUIRE(n_rows + 512 < (1ll << 31), "conv_pool_fwd(tcgen05): S*L too large for 32-bit TMA coordinates");
   CLSM_REQUIRE(Dpad % 64 == 0 && Fpad % 16 == 0 && Fpad >= 16 && Fpad <= 512, "conv_pool_fwd(tcgen05): bad Dpad/Fpad");
@@ -423,13 +472,14 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
   if (p.NT > 256) p.NT = 256;
   p.n_tiles = static_cast<int>(ceil_div64(n_rows, p.NT));
   p.ldk = ldk; p.col0 = col0; p.keys = reinterpret_cast<unsigned long long*>(keys);
+  p.tok = tok;
   // variant: 0 (default) = independent CTAs, 1 = CTA pairs with multicast weights.  CLSM_CONV_TC_VARIANT overrides.
   static int variant = -1;
   if (variant < 0) {
     const char* e = getenv("CLSM_CONV_TC_VARIANT");
     variant = (e != nullptr && e[0] == '1') ? 1 : 0;
   }
-  const bool cluster = variant == 1 && clsm_sm_count() >= 2;
+  const bool cluster = variant == 1 && clsm_sm_count() >= 2 && !gather;
   const int a_rows = p.n_mt * MT;
   if (cluster) { p.wbox = a_rows / 2; p.n_wbox = 2; }
   else { p.wbox = MT; p.n_wbox = p.n_mt; }
@@ -479,10 +529,16 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
     smem_bytes = stages * stage_bytes + 1024 /*alignment slack*/ + 8 * (2 * stages + 9);
   }
 
+  if (gather && p.shift_mode == 0) {
+    clsm_set_error("conv_pool_fwd(tcgen05, token gather): shape outside the resident-tile plan");
+    return CLSM_EUNSUPPORTED;
+  }
   CUtensorMap tmX, tmW;
   // rows of Wt past Fpad (the last M tile is usually partial) are zero-filled by TMA
-  if (!make_map_2d(&tmX, X, static_cast<uint64_t>(Dpad), static_cast<uint64_t>(n_rows), KCHUNK,
-                   static_cast<uint32_t>(p.shift_mode ? p.xrows : p.NT)) ||
+  // gather: the map covers the TABLE, box = one row of 64 columns (tile::gather4 fetches four such rows per instruction)
+  if (!(gather ? make_map_2d(&tmX, X, static_cast<uint64_t>(Dpad), static_cast<uint64_t>(table_rows), KCHUNK, 1)
+               : make_map_2d(&tmX, X, static_cast<uint64_t>(Dpad), static_cast<uint64_t>(n_rows), KCHUNK,
+                             static_cast<uint32_t>(p.shift_mode ? p.xrows : p.NT))) ||
       !make_map_2d(&tmW, Wt, static_cast<uint64_t>(k) * Dpad, static_cast<uint64_t>(Fpad), KCHUNK,
                    static_cast<uint32_t>(p.shift_mode ? (cluster ? MT / 2 : MT) : p.wbox))) {
     clsm_set_error("conv_pool_fwd(tcgen05): cuTensorMapEncodeTiled failed");
@@ -519,7 +575,23 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
     CLSM_CUDA(cudaLaunchKernelEx(&cfg, conv_pool_tc_kernel<CL, N>, tmX, tmW, p));                                        \
   } while (0)
   const int nch = p.NT / 32;
-  if (cluster) {
+#define TC_LAUNCH_G(N)                                                                                                          \
+  do {                                                                                                                          \
+    CLSM_CUDA(cudaFuncSetAttribute(conv_pool_tc_kernel<false, N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)); \
+    CLSM_CUDA(cudaLaunchKernelEx(&cfg, conv_pool_tc_kernel<false, N, true>, tmX, tmW, p));                                      \
+  } while (0)
+  if (gather) {
+    cfg.blockDim = dim3(NUM_THREADS + 32);
+    switch (nch) {
+      case 2: TC_LAUNCH_G(2); break;
+      case 3: TC_LAUNCH_G(3); break;
+      case 4: TC_LAUNCH_G(4); break;
+      case 5: TC_LAUNCH_G(5); break;
+      case 6: TC_LAUNCH_G(6); break;
+      case 7: TC_LAUNCH_G(7); break;
+      default: TC_LAUNCH_G(8); break;
+    }
+  } else if (cluster) {
     switch (nch) {
       case 2: TC_LAUNCH(true, 2); break;
       case 3: TC_LAUNCH(true, 3); break;
@@ -542,6 +614,7 @@ int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void*
     }
   }
 #undef TC_LAUNCH
+#undef TC_LAUNCH_G
   CLSM_LAUNCH_CHECK();
   if (prof_on) {           // diagnostics only: synchronises and prints average cycles per CTA
     long long h[8];

@@ -196,11 +196,20 @@ class Tower(object):
         keep = 1.0 - net.params.dropout_prob[0] if train else 1.0
         table = self.E_c if self.bf16 else self.E
         ld_table = self.Dpad if self.bf16 else self.D
-        call("clsm_emb_gather_mask", _ptr(b["tok"]), n_tok, _ptr(table), self.V1, self.D, ld_table,
-             self.dtype_code, _ptr(b["X"]), self.Dpad, keep, seed, _ptr(b["mask"]) if (train and keep < 1.0) else C.c_void_p(0), st)
-        for i, k in enumerate(self.windows):
-            call("clsm_conv_pool_fwd", _ptr(b["X"]), self.dtype_code, S, self.L, self.Dpad, _ptr(self.Wt[i]),
-                 k, self.F, self.Fpad, _ptr(b["keys"]), self.P, i * self.F, IMPL[net.conv_impl], st)
+        if not train and self.bf16 and net.conv_impl != "simt" and b.get("fused_gather", True):
+            # inference: the embedding lookup happens inside the conv kernel (TMA gather4 of table rows by token id);
+            # the gathered matrix X is never written.  Shapes outside that kernel's plan fall back to gather + conv.
+            try:
+                for i, k in enumerate(self.windows):
+                    call("clsm_conv_pool_fwd_tok", _ptr(b["tok"]), _ptr(table), self.V1, self.Dpad, S, self.L, self.Dpad,
+                         _ptr(self.Wt[i]), k, self.F, self.Fpad, _ptr(b["keys"]), self.P, i * self.F, st)
+                fused = True
+            except _lib.ClsmError:
+                b["fused_gather"] = fused = False
+        else:
+            fused = False
+        if not fused:
+            self._gather_and_conv(b, train, keep, seed, table, ld_table, st)
         call("clsm_pool_finalize", _ptr(b["keys"]), S, self.P, self.P, _ptr(self.convb), ACT[net.params.activation],
              _ptr(b["pooled"]), _ptr(b["argmax"]), self.P, st)
         call("clsm_dense_fwd", _ptr(b["pooled"]), S, self.P, self.P, _ptr(self.Wd), _ptr(self.bd), self.H,
@@ -211,6 +220,15 @@ class Tower(object):
             b["keep2"], b["seed2"] = 1.0 - net.params.dropout_prob[1], seed ^ 0x5DEECE66D
             call("clsm_dropout_rows", _ptr(b["sem"]), S, self.H, b["keep2"], b["seed2"], _ptr(b["sem"]), st)
         return b["sem"]
+
+    def _gather_and_conv(self, b, train, keep, seed, table, ld_table, st):
+        net = self.net
+        S, n_tok = b["S"], b["n_tok"]
+        call("clsm_emb_gather_mask", _ptr(b["tok"]), n_tok, _ptr(table), self.V1, self.D, ld_table,
+             self.dtype_code, _ptr(b["X"]), self.Dpad, keep, seed, _ptr(b["mask"]) if (train and keep < 1.0) else C.c_void_p(0), st)
+        for i, k in enumerate(self.windows):
+            call("clsm_conv_pool_fwd", _ptr(b["X"]), self.dtype_code, S, self.L, self.Dpad, _ptr(self.Wt[i]),
+                 k, self.F, self.Fpad, _ptr(b["keys"]), self.P, i * self.F, IMPL[net.conv_impl], st)
 
     # ---- backward: gradient of the loss wrt sem in b['dsem']; fills flat_g and the sparse table grad
     def backward(self, b):

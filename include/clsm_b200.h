@@ -99,6 +99,16 @@ int clsm_conv_pool_fwd(const void* X, int dtype, int64_t S, int L, int Dpad,
                        const void* Wt, int k, int F, int Fpad,
                        uint64_t* keys, int ldk, int col0, int impl, void* stream);
 
+/* The same convolution + max over time with the embedding lookup INSIDE the kernel (inference: no dropout):
+ * replaces Embedding + Convolution1D + MaxPooling1D, cnn_dssm_tf.py:111-116,84-100, in one launch.
+ * tok (S*L) int32 ids, table (n_rows, ld_table = Dpad) bf16 as clsm_table_to_bf16 writes it.  The token tile of the
+ * tensor-core kernel is fetched row by row from the table by the copy engine (TMA tile::gather4, the token ids are
+ * the row coordinates), so the gathered matrix X is never written to memory or read back.  Results are bit-identical
+ * to clsm_emb_gather (keep = 1) + clsm_conv_pool_fwd.  Ids are trusted to lie in [0, n_rows).  CLSM_EUNSUPPORTED for
+ * shapes outside the kernel's resident-tile plan (then gather + clsm_conv_pool_fwd). */
+int clsm_conv_pool_fwd_tok(const int32_t* tok, const void* table, int64_t n_rows, int ld_table, int64_t S, int L, int Dpad,
+                           const void* Wt, int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, void* stream);
+
 /* keys -> pooled = act(max + bias) fp32 (S, ldp), argmax int32 (S, ldp) (may be NULL).
  * For relu a column with pooled == 0 reports argmax 0 (all positions tie at 0 after the
  * activation).  replaces the activation of Convolution1D + concat, cnn_dssm_tf.py:88,102-107 */

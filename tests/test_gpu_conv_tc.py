@@ -50,3 +50,36 @@ def test_tc_is_default_for_bf16_and_rejects_fp32():
     assert torch.equal(a[2], b[2])
     with pytest.raises(_lib.ClsmError):
         run_conv(X, W, False, "tcgen05")
+
+
+@pytest.mark.parametrize("shape", [(40, 100, 300, 3, 300), (5, 1000, 100, 4, 150), (300, 7, 64, 1, 16), (3, 9, 10, 2, 5),
+                                   (2, 129, 64, 2, 48), (11, 33, 128, 7, 500), (4096, 100, 300, 3, 300)],
+                         ids=lambda s: "S%d-L%d-D%d-k%d-F%d" % s)
+def test_token_gather_inside_the_conv_kernel_is_bit_identical(shape):
+    """clsm_conv_pool_fwd_tok: the token tile comes from the embedding table by TMA gather4 (ids = row coordinates).
+    Same keys, bit for bit, as clsm_emb_gather + clsm_conv_pool_fwd on the same ids -- Zipf-like ids with a heavy PAD
+    row, the first and last table rows, and a token count that is not a multiple of the tile."""
+    from tests.gpu_util import DEV, P, ST, call, dev, pack_w, rup
+    from dnn_page_vectors_b200 import _lib
+    S, L, D, k, F = shape
+    rng = np.random.RandomState(23)
+    V1 = 5000
+    Dpad, Fpad = rup(D, 64), rup(F, 16)
+    E = rng.uniform(-0.25, 0.25, size=(V1, D)).astype(np.float32)
+    W = rng.uniform(-0.05, 0.05, size=(k, D, F))
+    tok = (rng.zipf(1.2, size=(S, L)) % V1).astype(np.int32)
+    tok[rng.rand(S, L) < 0.3] = V1 - 1
+    tok[0, 0], tok[-1, -1] = 0, V1 - 1
+    table = torch.zeros((V1, Dpad), dtype=torch.bfloat16, device=DEV)
+    E_d = dev(E)
+    call("clsm_table_to_bf16", P(E_d), V1, D, P(table), Dpad, ST())
+    Wt = pack_w(W, Dpad, Fpad, True)
+    tok_d = dev(tok.reshape(-1))
+    X = torch.zeros((S * L + 8, Dpad), dtype=torch.bfloat16, device=DEV)
+    call("clsm_emb_gather", P(tok_d), S * L, P(table), V1, D, Dpad, _lib.BF16, P(X), Dpad, 1.0, 0, ST())
+    k1 = torch.full((S, F), -1, dtype=torch.int64, device=DEV)
+    k2 = torch.full((S, F), -1, dtype=torch.int64, device=DEV)
+    call("clsm_conv_pool_fwd", P(X), _lib.BF16, S, L, Dpad, P(Wt), k, F, Fpad, P(k1), F, 0, _lib.IMPL["tcgen05"], ST())
+    call("clsm_conv_pool_fwd_tok", P(tok_d), P(table), V1, Dpad, S, L, Dpad, P(Wt), k, F, Fpad, P(k2), F, 0, ST())
+    torch.cuda.synchronize()
+    assert torch.equal(k1, k2)
