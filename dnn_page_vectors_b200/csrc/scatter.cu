@@ -1,13 +1,18 @@
 // Embedding gradient: dE[id] = sum over token positions with that id of dX[pos], deterministic.
 //   replaces the gradient of Embedding (Theano AdvancedIncSubtensor1 / TF UnsortedSegmentSum) that
 //   Keras builds for dssm_cnn_v2/cnn_dssm_tf.py:111-116.
-// 1. stable radix sort of (id, position)            (cub::DeviceRadixSort, utility primitive)
-// 2. segment heads + inclusive scan -> segment index per sorted entry (cub::DeviceScan)
-// 3. segmented reduce by RECURSIVE CHUNKING (hand-written): level 0 sums 64 consecutive sorted
-//    entries per CTA; a run that lies wholly inside its chunk is final, a run cut by a chunk edge
-//    leaves a partial row in one of the chunk's two slots; level l+1 repeats over the slots of 32
-//    chunks.  The shape of the tree depends only on n, and every run is added left to right, so
-//    the result is bit-identical from run to run; a 40 %-PAD batch costs no more than a uniform one.
+// plan (clsm_emb_scatter_plan, needs only the token ids, so the host runs it under the forward pass):
+//   1. stable radix sort of (id, position)            (cub::DeviceRadixSort, utility primitive)
+//   2. segment heads + inclusive scan -> segment index per sorted entry (cub::DeviceScan)
+// reduce (clsm_emb_scatter_reduce, ONE launch):
+//   3. segmented reduce by RECURSIVE CHUNKING (hand-written): level 0 sums 64 consecutive sorted entries per thread
+//      group; a run that lies wholly inside its chunk is final, a run cut by a chunk edge leaves a partial row in
+//      one of the chunk's two slots; level l+1 repeats over the slots of 32 chunks and is executed by whichever group
+//      finishes last among its children.  The shape of the tree depends only on n, and every run is added left to
+//      right, so the result is bit-identical from run to run; a 40 %-PAD batch costs no more than a uniform one.
+//      dX rows (fp32, or bf16 from the single-window tensor-core backward) and the forward's keep bits are staged
+//      through shared memory with cp.async.  (No shared-memory carve-out preference is set on purpose: with one, the
+//      kernel could not share an SM with the other stream's kernels and the two-stream step lost 0.6 ms.)
 #include "common.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -415,7 +420,6 @@ int clsm_emb_scatter_reduce(int64_t n_tok, const void* dX, int dx_dtype, int Dpa
 #define TREE(M, B, G)                                                                                                   \
   do {                                                                                                                  \
     CLSM_CUDA(cudaFuncSetAttribute(seg_reduce_tree_kernel<M, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem))); \
-    CLSM_CUDA(cudaFuncSetAttribute(seg_reduce_tree_kernel<M, B>, cudaFuncAttributePreferredSharedMemoryCarveout, 100)); \
     seg_reduce_tree_kernel<M, B><<<G, 128, smem, st>>>(t);                                                              \
   } while (0)
   if (dx_dtype == CLSM_BF16) {
