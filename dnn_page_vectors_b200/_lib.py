@@ -42,7 +42,8 @@ SIGNATURES = {
     "clsm_emb_scatter_reduce": (i32, [i64, vp, i32, i32, i32, f32, u64, vp, vp, vp, sz, vp]),
     "clsm_pack_conv_w": (i32, [vp, i32, i32, i32, i32, i32, i32, vp, vp]),
     "clsm_conv_pool_fwd": (i32, [vp, i32, i64, i32, i32, vp, i32, i32, i32, vp, i32, i32, i32, vp]),
-    "clsm_conv_pool_fwd_tok": (i32, [vp, vp, i64, i32, i64, i32, i32, vp, i32, i32, i32, vp, i32, i32, vp]),
+    "clsm_conv_pool_fwd_tok": (i32, [vp, vp, i64, i32, i64, i32, i32, i32, vp, i32, i32, i32, vp, i32, i32, vp]),
+    "clsm_conv_pool_fwd_d": (i32, [vp, i32, i64, i32, i32, i32, vp, i32, i32, i32, vp, i32, i32, i32, vp]),
     "clsm_pool_finalize": (i32, [vp, i64, i32, i32, vp, i32, vp, vp, i32, vp]),
     "clsm_dense_fwd": (i32, [vp, i64, i32, i32, vp, vp, i32, i32, vp, vp]),
     "clsm_dense_bwd_workspace_bytes": (sz, [i64, i32, i32]),

@@ -305,6 +305,7 @@ struct Dx2Params {
   int n_mt, NT, n_tiles, fblocks;
   const float* G; const int32_t* A; int ldp, col0;
   float* dX; int accumulate;
+  int last_ks;                 // K = 16 steps of the last 64-filter block that hold real filters (F = 300: 3 of 4)
   int dx_bf16;                 // dX rows are bf16 (overwrite mode only: the single-window case); halves the largest stream of the step
   int wstages, xrows, nreg;
   long long* prof;
@@ -383,9 +384,11 @@ dx2_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const Dx2Params p) {
             w_full += clock64() - c0;
             tc_fence_after();
             const uint32_t a_lo = sw128_desc_lo(w_ring + ws * MT_BYTES);
+            const int nks = fb == p.fblocks - 1 ? p.last_ks : KCHUNK / 16;      // filters past F are zero in Wb and never built into dY
 #pragma unroll
             for (int ks = 0; ks < KCHUNK / 16; ++ks)      // output token n reads tile row n + (k-1-j): 8 units of 16 B per row
-              tc_mma_bf16_u(d_tmem, a_lo + ks * 2, x_lo + static_cast<uint32_t>(p.k - 1 - j) * 8u + ks * 2, idesc, (fb | j | ks) != 0 ? 1u : 0u);
+              if (ks < nks)
+                tc_mma_bf16_u(d_tmem, a_lo + ks * 2, x_lo + static_cast<uint32_t>(p.k - 1 - j) * 8u + ks * 2, idesc, (fb | j | ks) != 0 ? 1u : 0u);
             tc_commit_u(empty_bar(ws));
             if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
           }
@@ -1037,6 +1040,7 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
     q.n_rows = p.n_rows; q.L = L; q.k = k; q.F = F; q.Dpad = Dpad; q.n_mt = p.n_mt; q.NT = nt; q.fblocks = p.fblocks;
     q.n_tiles = static_cast<int>(ceil_div64(p.n_rows, nt));
     q.G = G; q.A = A; q.ldp = ldp; q.col0 = col0; q.dX = dX; q.accumulate = accumulate; q.dx_bf16 = dx_bf16;
+    q.last_ks = (F - (q.fblocks - 1) * 64 + 15) / 16;
     q.xrows = (nt + k - 1 + 7) / 8 * 8;
     q.nreg = 512 / nt; if (q.nreg > 4) q.nreg = 4;
     const int x_slot = (q.xrows * 128 + 1023) / 1024 * 1024;

@@ -127,9 +127,9 @@ __global__ void pool_finalize_kernel(const unsigned long long* __restrict__ keys
 
 }  // namespace
 
-int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void* Wt, int k, int F, int Fpad,
+int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int D, int Dpad, const void* Wt, int k, int F, int Fpad,
                           uint64_t* keys, int ldk, int col0, cudaStream_t st);   // conv_tc.cu
-int clsm_conv_pool_fwd_tok_tc(const int32_t* tok, const void* table, int64_t table_rows, int64_t S, int L, int Dpad,
+int clsm_conv_pool_fwd_tok_tc(const int32_t* tok, const void* table, int64_t table_rows, int64_t S, int L, int D, int Dpad,
                               const void* Wt, int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, cudaStream_t st);
 
 extern "C" {
@@ -137,6 +137,13 @@ extern "C" {
 int clsm_conv_pool_fwd(const void* X, int dtype, int64_t S, int L, int Dpad,
                        const void* Wt, int k, int F, int Fpad,
                        uint64_t* keys, int ldk, int col0, int impl, void* stream) {
+  return clsm_conv_pool_fwd_d(X, dtype, S, L, 0, Dpad, Wt, k, F, Fpad, keys, ldk, col0, impl, stream);
+}
+
+int clsm_conv_pool_fwd_d(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
+                         const void* Wt, int k, int F, int Fpad,
+                         uint64_t* keys, int ldk, int col0, int impl, void* stream) {
+  CLSM_REQUIRE(D >= 0 && D <= Dpad, "conv_pool_fwd: D must be 0 (unknown) or in [1, Dpad]");
   CLSM_REQUIRE(dtype == CLSM_BF16 || dtype == CLSM_F32, "conv_pool_fwd: bad dtype %d", dtype);
   CLSM_REQUIRE(S >= 0 && L >= k && k >= 1 && F >= 1 && Fpad >= F && Dpad % 16 == 0 && Dpad > 0,
                "conv_pool_fwd: bad sizes (S=%lld L=%d k=%d F=%d Fpad=%d Dpad=%d)", (long long)S, L, k, F, Fpad, Dpad);
@@ -153,7 +160,7 @@ int clsm_conv_pool_fwd(const void* X, int dtype, int64_t S, int L, int Dpad,
     return CLSM_EUNSUPPORTED;
   }
   if (impl == CLSM_IMPL_TCGEN05 || (impl == CLSM_IMPL_AUTO && tc_ok))
-    return clsm_conv_pool_fwd_tc(X, S, L, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
+    return clsm_conv_pool_fwd_tc(X, S, L, D, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
   dim3 grid(static_cast<unsigned>(ceil_div64(n_rows, BM)), static_cast<unsigned>((F + BN - 1) / BN));
   if (dtype == CLSM_BF16)
     conv_pool_simt_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(X), n_rows, L, Dpad,
@@ -165,8 +172,9 @@ int clsm_conv_pool_fwd(const void* X, int dtype, int64_t S, int L, int Dpad,
   return CLSM_OK;
 }
 
-int clsm_conv_pool_fwd_tok(const int32_t* tok, const void* table, int64_t n_rows, int ld_table, int64_t S, int L, int Dpad,
+int clsm_conv_pool_fwd_tok(const int32_t* tok, const void* table, int64_t n_rows, int ld_table, int64_t S, int L, int D, int Dpad,
                            const void* Wt, int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, void* stream) {
+  CLSM_REQUIRE(D >= 0 && D <= Dpad, "conv_pool_fwd_tok: D must be 0 (unknown) or in [1, Dpad]");
   CLSM_REQUIRE(tok != nullptr && table != nullptr && n_rows > 0, "conv_pool_fwd_tok: null tokens / table");
   CLSM_REQUIRE(S >= 0 && L >= k && k >= 1 && F >= 1 && Fpad >= F, "conv_pool_fwd_tok: bad sizes");
   CLSM_REQUIRE(Dpad % 64 == 0 && ld_table == Dpad && Fpad % 16 == 0 && Fpad <= 512,
@@ -177,7 +185,7 @@ int clsm_conv_pool_fwd_tok(const int32_t* tok, const void* table, int64_t n_rows
   clear_keys_kernel<<<static_cast<unsigned>(ceil_div64(S * F, 256)), 256, 0, st>>>(
       reinterpret_cast<unsigned long long*>(keys), S, F, ldk, col0);
   CLSM_LAUNCH_CHECK();
-  return clsm_conv_pool_fwd_tok_tc(tok, table, n_rows, S, L, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
+  return clsm_conv_pool_fwd_tok_tc(tok, table, n_rows, S, L, D, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
 }
 
 int clsm_pool_finalize(const uint64_t* keys, int64_t S, int P, int ldk, const float* bias,

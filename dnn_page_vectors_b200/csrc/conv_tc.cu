@@ -57,6 +57,8 @@ struct TcParams {
   int xstages, wstages;  // mode 1: xstages = cpj token slots, wstages weight slots of one M tile chunk (16 KB)
   int nreg;              // mode 1: TMEM accumulator regions of NT columns used round-robin by the (tile, M tile) units
   long long* prof;       // optional cycle counters (CLSM_CONV_TC_PROF=1), else nullptr
+  int last_ks;           // K = 16 steps of the LAST 64-column chunk that hold real columns (D = 300: 304 = 19 x 16, so 3 of
+                         // 4): the zero pad columns beyond them are skipped -- exact, and 5 % fewer MMAs
   const int32_t* tok;    // GATHER kernels: token ids (n_rows); tmX then maps the embedding TABLE and the token tile is
                          // fetched row by row with TMA gather4 (ids as row coordinates) -- X is never materialised
 };
@@ -239,9 +241,11 @@ conv_pool_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
               w_feed += clock64() - c0;
               tc_fence_after();
               const uint32_t a_lo = sw128_desc_lo(w_ring + ws * MT_BYTES);
+              const int nks = cc == p.cpj - 1 ? p.last_ks : KCHUNK / 16;
 #pragma unroll
               for (int ks = 0; ks < KCHUNK / 16; ++ks)   // token rows j .. j+NT-1 of the resident box (128 B = 8 units per row)
-                tc_mma_bf16_u(d_tmem, a_lo + ks * 2, x_lo + static_cast<uint32_t>(j) * 8u + ks * 2, idesc, (cc | j | ks) != 0 ? 1u : 0u);
+                if (ks < nks)
+                  tc_mma_bf16_u(d_tmem, a_lo + ks * 2, x_lo + static_cast<uint32_t>(j) * 8u + ks * 2, idesc, (cc | j | ks) != 0 ? 1u : 0u);
               if (CLUSTER) { if (elect_one()) tc_commit_mc(empty_bar(ws), static_cast<uint16_t>(3)); }   // frees the slot in BOTH CTAs
               else tc_commit_u(empty_bar(ws));
               if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
@@ -444,22 +448,23 @@ bool make_map_2d(CUtensorMap* map, const void* ptr, uint64_t cols, uint64_t rows
 
 }  // namespace
 
-static int conv_fwd_tc_impl(const void* X, const int32_t* tok, int64_t table_rows, int64_t S, int L, int Dpad, const void* Wt,
+static int conv_fwd_tc_impl(const void* X, const int32_t* tok, int64_t table_rows, int64_t S, int L, int D, int Dpad, const void* Wt,
                             int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, cudaStream_t st);
 
-int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int Dpad, const void* Wt, int k, int F, int Fpad,
+// D: the number of real columns (0 = unknown: all Dpad columns are multiplied); columns D..Dpad-1 of X and Wt are zero
+int clsm_conv_pool_fwd_tc(const void* X, int64_t S, int L, int D, int Dpad, const void* Wt, int k, int F, int Fpad,
                           uint64_t* keys, int ldk, int col0, cudaStream_t st) {
-  return conv_fwd_tc_impl(X, nullptr, 0, S, L, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
+  return conv_fwd_tc_impl(X, nullptr, 0, S, L, D, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
 }
 
 // Same kernel, token tile fetched from the embedding table by TMA gather4 (tok != nullptr, X = the (table_rows, Dpad)
 // bf16 table): the inference path, no dropout, X never written.
-int clsm_conv_pool_fwd_tok_tc(const int32_t* tok, const void* table, int64_t table_rows, int64_t S, int L, int Dpad,
+int clsm_conv_pool_fwd_tok_tc(const int32_t* tok, const void* table, int64_t table_rows, int64_t S, int L, int D, int Dpad,
                               const void* Wt, int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, cudaStream_t st) {
-  return conv_fwd_tc_impl(table, tok, table_rows, S, L, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
+  return conv_fwd_tc_impl(table, tok, table_rows, S, L, D, Dpad, Wt, k, F, Fpad, keys, ldk, col0, st);
 }
 
-static int conv_fwd_tc_impl(const void* X, const int32_t* tok, int64_t table_rows, int64_t S, int L, int Dpad, const void* Wt,
+static int conv_fwd_tc_impl(const void* X, const int32_t* tok, int64_t table_rows, int64_t S, int L, int D, int Dpad, const void* Wt,
                             int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, cudaStream_t st) {
   const bool gather = tok != nullptr;
   const int64_t n_rows = S * L;
@@ -473,6 +478,8 @@ static int conv_fwd_tc_impl(const void* X, const int32_t* tok, int64_t table_row
   p.n_tiles = static_cast<int>(ceil_div64(n_rows, p.NT));
   p.ldk = ldk; p.col0 = col0; p.keys = reinterpret_cast<unsigned long long*>(keys);
   p.tok = tok;
+  p.last_ks = KCHUNK / 16;
+  if (D > 0 && D <= Dpad && D > Dpad - KCHUNK) p.last_ks = (D - (Dpad - KCHUNK) + 15) / 16;
   // variant: 0 (default) = independent CTAs, 1 = CTA pairs with multicast weights.  CLSM_CONV_TC_VARIANT overrides.
   static int variant = -1;
   if (variant < 0) {

@@ -201,7 +201,7 @@ class Tower(object):
             # the gathered matrix X is never written.  Shapes outside that kernel's plan fall back to gather + conv.
             try:
                 for i, k in enumerate(self.windows):
-                    call("clsm_conv_pool_fwd_tok", _ptr(b["tok"]), _ptr(table), self.V1, self.Dpad, S, self.L, self.Dpad,
+                    call("clsm_conv_pool_fwd_tok", _ptr(b["tok"]), _ptr(table), self.V1, self.Dpad, S, self.L, self.D, self.Dpad,
                          _ptr(self.Wt[i]), k, self.F, self.Fpad, _ptr(b["keys"]), self.P, i * self.F, st)
                 fused = True
             except _lib.ClsmError:
@@ -227,7 +227,7 @@ class Tower(object):
         call("clsm_emb_gather_mask", _ptr(b["tok"]), n_tok, _ptr(table), self.V1, self.D, ld_table,
              self.dtype_code, _ptr(b["X"]), self.Dpad, keep, seed, _ptr(b["mask"]) if (train and keep < 1.0) else C.c_void_p(0), st)
         for i, k in enumerate(self.windows):
-            call("clsm_conv_pool_fwd", _ptr(b["X"]), self.dtype_code, S, self.L, self.Dpad, _ptr(self.Wt[i]),
+            call("clsm_conv_pool_fwd_d", _ptr(b["X"]), self.dtype_code, S, self.L, self.D, self.Dpad, _ptr(self.Wt[i]),
                  k, self.F, self.Fpad, _ptr(b["keys"]), self.P, i * self.F, IMPL[net.conv_impl], st)
 
     # ---- backward: gradient of the loss wrt sem in b['dsem']; fills flat_g and the sparse table grad

@@ -106,8 +106,14 @@ int clsm_conv_pool_fwd(const void* X, int dtype, int64_t S, int L, int Dpad,
  * the row coordinates), so the gathered matrix X is never written to memory or read back.  Results are bit-identical
  * to clsm_emb_gather (keep = 1) + clsm_conv_pool_fwd.  Ids are trusted to lie in [0, n_rows).  CLSM_EUNSUPPORTED for
  * shapes outside the kernel's resident-tile plan (then gather + clsm_conv_pool_fwd). */
-int clsm_conv_pool_fwd_tok(const int32_t* tok, const void* table, int64_t n_rows, int ld_table, int64_t S, int L, int Dpad,
+int clsm_conv_pool_fwd_tok(const int32_t* tok, const void* table, int64_t n_rows, int ld_table, int64_t S, int L, int D, int Dpad,
                            const void* Wt, int k, int F, int Fpad, uint64_t* keys, int ldk, int col0, void* stream);
+/* clsm_conv_pool_fwd told the number of REAL columns D (columns D..Dpad-1 of X and Wt are zero): the tensor-core kernel
+ * then skips the K steps that would only multiply padding (D = 300 in Dpad = 320: 19 of 20).  Same results; D = 0
+ * means unknown (= clsm_conv_pool_fwd).  clsm_conv_pool_fwd_tok takes the same D. */
+int clsm_conv_pool_fwd_d(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
+                         const void* Wt, int k, int F, int Fpad,
+                         uint64_t* keys, int ldk, int col0, int impl, void* stream);
 
 /* keys -> pooled = act(max + bias) fp32 (S, ldp), argmax int32 (S, ldp) (may be NULL).
  * For relu a column with pooled == 0 reports argmax 0 (all positions tie at 0 after the

@@ -80,6 +80,8 @@ def test_token_gather_inside_the_conv_kernel_is_bit_identical(shape):
     k1 = torch.full((S, F), -1, dtype=torch.int64, device=DEV)
     k2 = torch.full((S, F), -1, dtype=torch.int64, device=DEV)
     call("clsm_conv_pool_fwd", P(X), _lib.BF16, S, L, Dpad, P(Wt), k, F, Fpad, P(k1), F, 0, _lib.IMPL["tcgen05"], ST())
-    call("clsm_conv_pool_fwd_tok", P(tok_d), P(table), V1, Dpad, S, L, Dpad, P(Wt), k, F, Fpad, P(k2), F, 0, ST())
+    call("clsm_conv_pool_fwd_tok", P(tok_d), P(table), V1, Dpad, S, L, D, Dpad, P(Wt), k, F, Fpad, P(k2), F, 0, ST())
+    k3 = torch.full((S, F), -1, dtype=torch.int64, device=DEV)       # told D: padding K steps skipped, same bits
+    call("clsm_conv_pool_fwd_d", P(X), _lib.BF16, S, L, D, Dpad, P(Wt), k, F, Fpad, P(k3), F, 0, _lib.IMPL["tcgen05"], ST())
     torch.cuda.synchronize()
-    assert torch.equal(k1, k2)
+    assert torch.equal(k1, k2) and torch.equal(k1, k3)
