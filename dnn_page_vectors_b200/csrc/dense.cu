@@ -2,6 +2,7 @@
 //   replaces Dense(hidden_dims) + Activation('relu'), dssm_cnn_v2/cnn_dssm_tf.py:124-126,
 //   and its gradient.  These GEMMs are <0.2 % of the step's FLOPs.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -200,8 +201,176 @@ __global__ void __launch_bounds__(256) gemm_tf32_kernel(GemmP p) {
       }
 }
 
+// ---- TF32 GEMM, cp.async-pipelined (the default of the bf16 mode whenever every row is 16-byte aligned) ----------
+// gemm_tf32_kernel above stages its tiles through registers with scalar loads, one tile ahead: the document tower's
+// projection (24 576 x 300 x 128) took 54 us against a 7 us memory floor.  Here 64 x 128 x 32 tiles move with 16-byte
+// cp.async into a 3-stage ring (nothing held in registers, two tiles in flight behind the one being multiplied), 8
+// warps of 32 x 32 run mma.sync m16n8k8, operands are rounded to TF32 (cvt.rna) as fragments are read -- the same
+// arithmetic as above.  Layouts: A is (m, k) with k contiguous, or (k, m) with m contiguous (AM: pooled^T for dWd);
+// B is (k, n) with n contiguous, or (n, k) with k contiguous (BK: Wd^T for the pooled gradient).  Every tile row is
+// padded so that all fragment loads are conflict-free.
+constexpr int QM = 64, QN = 128, QK = 32, QST = 3;
+template <bool AM, bool BK>
+struct AsyncTiles {
+  static constexpr int A_ROWS = AM ? QK : QM, A_PITCH = AM ? QM + 8 : QK + 4;     // [k][m] or [m][k]
+  static constexpr int B_ROWS = BK ? QN : QK, B_PITCH = BK ? QK + 4 : QN + 8;     // [n][k] or [k][n]
+  static constexpr int A_FLOATS = A_ROWS * A_PITCH, B_FLOATS = B_ROWS * B_PITCH;
+  static constexpr int STAGE_FLOATS = A_FLOATS + B_FLOATS;
+};
+
+__device__ __forceinline__ void cp16(uint32_t dst, const void* src, int src_bytes) {      // src_bytes < 16: the rest is zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+
+template <bool AM, bool BK>
+__global__ void __launch_bounds__(256) gemm_tf32_async_kernel(GemmP p) {
+  using T = AsyncTiles<AM, BK>;
+  extern __shared__ __align__(16) float smem_dyn[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int wm = (warp >> 2) * 32, wn = (warp & 3) * 32;
+  const int g = lane >> 2, t = lane & 3;
+  const int64_t m0 = static_cast<int64_t>(blockIdx.x) * QM;
+  const int n0 = blockIdx.y * QN;
+  const int64_t kbeg = static_cast<int64_t>(blockIdx.z) * p.k_per_split;
+  const int64_t kend = (kbeg + p.k_per_split < p.K) ? kbeg + p.k_per_split : p.K;
+  const int n_kt = static_cast<int>((kend - kbeg + QK - 1) / QK);
+  const uint32_t sbase = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dyn));
+  float acc[2][4][4];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[i][j][c] = 0.0f;
+
+  auto load_stage = [&](int kt, int stage) {
+    const int64_t kk = kbeg + static_cast<int64_t>(kt) * QK;
+    const uint32_t a_s = sbase + static_cast<uint32_t>(stage * T::STAGE_FLOATS) * 4u;
+    const uint32_t b_s = a_s + T::A_FLOATS * 4u;
+    // A tile: 16-byte pieces along the contiguous dimension
+    if (AM) {                                      // rows = k (32), 16 pieces of 4 m per row
+      for (int i = tid; i < QK * (QM / 4); i += 256) {
+        const int r = i / (QM / 4), c4 = (i - r * (QM / 4)) * 4;
+        const int64_t gk = kk + r, gm = m0 + c4;
+        int bytes = (gk < kend && gm < p.M) ? static_cast<int>((p.M - gm < 4 ? p.M - gm : 4) * 4) : 0;
+        cp16(a_s + static_cast<uint32_t>(r * T::A_PITCH + c4) * 4u, p.A + (bytes ? gk * p.sak + gm : 0), bytes);
+      }
+    } else {                                       // rows = m (64), 8 pieces of 4 k per row
+      for (int i = tid; i < QM * (QK / 4); i += 256) {
+        const int r = i / (QK / 4), c4 = (i - r * (QK / 4)) * 4;
+        const int64_t gm = m0 + r, gk = kk + c4;
+        int bytes = (gm < p.M && gk < kend) ? static_cast<int>((kend - gk < 4 ? kend - gk : 4) * 4) : 0;
+        cp16(a_s + static_cast<uint32_t>(r * T::A_PITCH + c4) * 4u, p.A + (bytes ? gm * p.sam + gk : 0), bytes);
+      }
+    }
+    if (BK) {                                      // rows = n (128), 8 pieces of 4 k per row
+      for (int i = tid; i < QN * (QK / 4); i += 256) {
+        const int r = i / (QK / 4), c4 = (i - r * (QK / 4)) * 4;
+        const int gn = n0 + r; const int64_t gk = kk + c4;
+        int bytes = (gn < p.N && gk < kend) ? static_cast<int>((kend - gk < 4 ? kend - gk : 4) * 4) : 0;
+        cp16(b_s + static_cast<uint32_t>(r * T::B_PITCH + c4) * 4u, p.B + (bytes ? static_cast<int64_t>(gn) * p.sbn + gk : 0), bytes);
+      }
+    } else {                                       // rows = k (32), 32 pieces of 4 n per row
+      for (int i = tid; i < QK * (QN / 4); i += 256) {
+        const int r = i / (QN / 4), c4 = (i - r * (QN / 4)) * 4;
+        const int64_t gk = kk + r; const int gn = n0 + c4;
+        int bytes = (gk < kend && gn < p.N) ? ((p.N - gn < 4 ? p.N - gn : 4) * 4) : 0;
+        cp16(b_s + static_cast<uint32_t>(r * T::B_PITCH + c4) * 4u, p.B + (bytes ? gk * p.sbk + gn : 0), bytes);
+      }
+    }
+  };
+
+#pragma unroll
+  for (int s = 0; s < QST - 1; ++s) {
+    if (s < n_kt) load_stage(s, s);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  for (int kt = 0; kt < n_kt; ++kt) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(QST - 2) : "memory");
+    __syncthreads();                               // tile kt has landed for everyone; the slot of tile kt-1 is free
+    if (kt + QST - 1 < n_kt) load_stage(kt + QST - 1, (kt + QST - 1) % QST);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    const float* As = smem_dyn + (kt % QST) * T::STAGE_FLOATS;
+    const float* Bs = As + T::A_FLOATS;
+#pragma unroll
+    for (int ks = 0; ks < QK; ks += 8) {
+      uint32_t a[2][4], b[4][2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int r = wm + i * 16 + g;
+        if (AM) {
+          a[i][0] = to_tf32(As[(ks + t) * T::A_PITCH + r]);     a[i][1] = to_tf32(As[(ks + t) * T::A_PITCH + r + 8]);
+          a[i][2] = to_tf32(As[(ks + t + 4) * T::A_PITCH + r]); a[i][3] = to_tf32(As[(ks + t + 4) * T::A_PITCH + r + 8]);
+        } else {
+          a[i][0] = to_tf32(As[r * T::A_PITCH + ks + t]);       a[i][1] = to_tf32(As[(r + 8) * T::A_PITCH + ks + t]);
+          a[i][2] = to_tf32(As[r * T::A_PITCH + ks + t + 4]);   a[i][3] = to_tf32(As[(r + 8) * T::A_PITCH + ks + t + 4]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = wn + j * 8 + g;
+        if (BK) { b[j][0] = to_tf32(Bs[c * T::B_PITCH + ks + t]); b[j][1] = to_tf32(Bs[c * T::B_PITCH + ks + t + 4]); }
+        else    { b[j][0] = to_tf32(Bs[(ks + t) * T::B_PITCH + c]); b[j][1] = to_tf32(Bs[(ks + t + 4) * T::B_PITCH + c]); }
+      }
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                       : "+f"(acc[i][j][0]), "+f"(acc[i][j][1]), "+f"(acc[i][j][2]), "+f"(acc[i][j][3])
+                       : "r"(a[i][0]), "r"(a[i][1]), "r"(a[i][2]), "r"(a[i][3]), "r"(b[j][0]), "r"(b[j][1]));
+    }
+  }
+  float* C = p.C + static_cast<int64_t>(blockIdx.z) * p.M * p.ldc;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int64_t m = m0 + wm + i * 16 + g + (c >> 1) * 8;
+        const int n = n0 + wn + j * 8 + 2 * t + (c & 1);
+        if (m >= p.M || n >= p.N) continue;
+        float v = acc[i][j][c];
+        if (p.epi == EPI_BIAS_ACT) v = act_apply(v + p.bias[n], p.act);
+        else if (p.epi == EPI_MUL_ACTGRAD) v *= act_grad_out(p.aux[m * p.ldaux + n], p.act);
+        C[m * p.ldc + n] = v;
+      }
+}
+
+// the async kernel takes a GEMM whose contiguous operand dimensions are unit-stride and whose rows are 16-byte aligned
+bool async_ok(const GemmP& p, bool* am, bool* bk) {
+  const bool a_k = p.sak == 1, a_m = p.sam == 1 && !a_k;
+  const bool b_n = p.sbn == 1, b_k = p.sbk == 1 && !b_n;
+  if (!(a_k || a_m) || !(b_n || b_k)) return false;
+  const int64_t a_pitch = a_k ? p.sam : p.sak, b_pitch = b_n ? p.sbk : p.sbn;
+  if (a_pitch % 4 != 0 || b_pitch % 4 != 0) return false;
+  if ((reinterpret_cast<uintptr_t>(p.A) | reinterpret_cast<uintptr_t>(p.B)) & 15) return false;
+  if (p.k_per_split % 4 != 0) return false;       // split starts stay 16-byte aligned along k
+  *am = a_m; *bk = b_k;
+  return true;
+}
+
+template <bool AM, bool BK>
+void launch_async(const GemmP& p, int splits, cudaStream_t st) {
+  using T = AsyncTiles<AM, BK>;
+  const int smem = QST * T::STAGE_FLOATS * 4;
+  static bool configured = false;
+  if (!configured) { cudaFuncSetAttribute(gemm_tf32_async_kernel<AM, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); configured = true; }
+  dim3 grid(static_cast<unsigned>(ceil_div64(p.M, QM)), (p.N + QN - 1) / QN, splits);
+  gemm_tf32_async_kernel<AM, BK><<<grid, 256, smem, st>>>(p);
+}
+
 void launch_gemm(const GemmP& p, int splits, bool tf32, cudaStream_t st) {
-  if (tf32) {
+  bool am = false, bk = false;
+  static int legacy = -1;                          // CLSM_DENSE_LEGACY=1: the register-staged kernel (A/B measurements)
+  if (legacy < 0) { const char* e = getenv("CLSM_DENSE_LEGACY"); legacy = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  if (tf32 && !legacy && async_ok(p, &am, &bk)) {
+    if (am && bk) launch_async<true, true>(p, splits, st);
+    else if (am) launch_async<true, false>(p, splits, st);
+    else if (bk) launch_async<false, true>(p, splits, st);
+    else launch_async<false, false>(p, splits, st);
+  } else if (tf32) {
     dim3 grid(static_cast<unsigned>(ceil_div64(p.M, GM)), (p.N + GN - 1) / GN, splits);
     gemm_tf32_kernel<<<grid, 256, 0, st>>>(p);
   } else {
