@@ -81,45 +81,56 @@ __device__ __forceinline__ void adam1(float& p, float& m, float& v, float g, con
   p = p - __fdividef(c.lr_t * m, s + c.eps);
 }
 
-// D % 4 == 0: one thread = one float4 of one owned row (same arithmetic as adam_table_kernel<true> in adam.cu)
+// D % 4 == 0.  One WARP per owned row (same arithmetic as adam_table_kernel<true> in adam.cu).  Lane s looks up
+// source s's map entry for the row -- ONE look-up per row and source, shared by a vote, where a thread per float4
+// did `world` dependent look-ups each (at 8 ranks that, not memory, was what the pass waited for: 1.35 ms against a
+// 0.3 ms bandwidth floor) -- and rows nobody touched skip the gradient gather altogether.
 __global__ void __launch_bounds__(256) adam_table_dp_kernel(AdamDpP c) {
   const int per_row = c.D / 4;
-  const int64_t item = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const int64_t r = item < 0xffffffffll ? static_cast<int64_t>(static_cast<uint32_t>(item) / static_cast<uint32_t>(per_row)) : item / per_row;
+  const int lane = threadIdx.x & 31;
+  const int64_t r = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   if (r >= c.n_rows) return;
-  const int q = static_cast<int>(item - r * per_row);
-  float4 gi = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int s = 0; s < c.world; ++s) {
-    const int32_t g = __ldg(c.maps + s * c.R + r);
-    if (g >= 0) {
-      const float4 x = __ldg(reinterpret_cast<const float4*>(c.rows + (s * c.cap + g) * c.ldg + q * 4));
-      gi.x += x.x; gi.y += x.y; gi.z += x.z; gi.w += x.w;
+  const int32_t my_g = lane < c.world ? __ldg(c.maps + static_cast<int64_t>(lane) * c.R + r) : -1;
+  const unsigned have = __ballot_sync(0xffffffffu, my_g >= 0);          // sources that hold a piece of this row's gradient
+  int32_t gs[MAX_WORLD];                                                    // every lane gets every source's entry (all 32 lanes
+#pragma unroll                                                              // are still converged here; the q loop below is not)
+  for (int s = 0; s < MAX_WORLD; ++s) gs[s] = __shfl_sync(0xffffffffu, my_g, s);
+  for (int q = lane; q < per_row; q += 32) {
+    float4 gi = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (have != 0u) {
+#pragma unroll
+      for (int s = 0; s < MAX_WORLD; ++s) {                                 // ascending source order: fixed summation order
+        if ((have >> s) & 1u) {
+          const float4 x = __ldg(reinterpret_cast<const float4*>(c.rows + (static_cast<int64_t>(s) * c.cap + gs[s]) * c.ldg + q * 4));
+          gi.x += x.x; gi.y += x.y; gi.z += x.z; gi.w += x.w;
+        }
+      }
     }
-  }
-  const int64_t off = r * c.D + q * 4;
-  float4 pi = *reinterpret_cast<float4*>(c.p + off);
-  float4 mi = *reinterpret_cast<float4*>(c.m + off);
-  float4 vi = *reinterpret_cast<float4*>(c.v + off);
-  adam1(pi.x, mi.x, vi.x, gi.x, c); adam1(pi.y, mi.y, vi.y, gi.y, c);
-  adam1(pi.z, mi.z, vi.z, gi.z, c); adam1(pi.w, mi.w, vi.w, gi.w, c);
-  *reinterpret_cast<float4*>(c.p + off) = pi;
-  *reinterpret_cast<float4*>(c.m + off) = mi;
-  *reinterpret_cast<float4*>(c.v + off) = vi;
-  __nv_bfloat162 lo = __floats2bfloat162_rn(pi.x, pi.y), hi = __floats2bfloat162_rn(pi.z, pi.w);
-  uint2 pk;
-  pk.x = *reinterpret_cast<uint32_t*>(&lo);
-  pk.y = *reinterpret_cast<uint32_t*>(&hi);
-  // Replicas hold identical compute tables, so the old local value is also what every peer holds: only rows
-  // whose bf16 image actually changed cross NVLink.  A row without a recent gradient moves by lr * m / sqrt(v)
-  // with m decaying 10 % per step -- far below bf16 resolution after a dozen steps -- so most of the table
-  // stays put and the broadcast shrinks to the rows touched recently.
-  const int64_t coff = r * c.ld_copy + q * 4;
-  uint2* mine = reinterpret_cast<uint2*>(c.copies[c.self] + coff);
-  const uint2 old = *mine;
-  if (old.x != pk.x || old.y != pk.y) {
-    *mine = pk;
-    for (int s = 0; s < c.world; ++s)
-      if (s != c.self) *reinterpret_cast<uint2*>(c.copies[s] + coff) = pk;
+    const int64_t off = r * c.D + q * 4;
+    float4 pi = *reinterpret_cast<float4*>(c.p + off);
+    float4 mi = *reinterpret_cast<float4*>(c.m + off);
+    float4 vi = *reinterpret_cast<float4*>(c.v + off);
+    adam1(pi.x, mi.x, vi.x, gi.x, c); adam1(pi.y, mi.y, vi.y, gi.y, c);
+    adam1(pi.z, mi.z, vi.z, gi.z, c); adam1(pi.w, mi.w, vi.w, gi.w, c);
+    *reinterpret_cast<float4*>(c.p + off) = pi;
+    *reinterpret_cast<float4*>(c.m + off) = mi;
+    *reinterpret_cast<float4*>(c.v + off) = vi;
+    __nv_bfloat162 lo = __floats2bfloat162_rn(pi.x, pi.y), hi = __floats2bfloat162_rn(pi.z, pi.w);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    // Replicas hold identical compute tables, so the old local value is also what every peer holds: only rows
+    // whose bf16 image actually changed cross NVLink.  A row without a recent gradient moves by lr * m / sqrt(v)
+    // with m decaying 10 % per step -- far below bf16 resolution after a dozen steps -- so most of the table
+    // stays put and the broadcast shrinks to the rows touched recently.
+    const int64_t coff = r * c.ld_copy + q * 4;
+    uint2* mine = reinterpret_cast<uint2*>(c.copies[c.self] + coff);
+    const uint2 old = *mine;
+    if (old.x != pk.x || old.y != pk.y) {
+      *mine = pk;
+      for (int s = 0; s < c.world; ++s)
+        if (s != c.self) *reinterpret_cast<uint2*>(c.copies[s] + coff) = pk;
+    }
   }
 }
 
@@ -178,8 +189,7 @@ int clsm_adam_table_dp(float* p, float* m, float* v, int64_t n_rows, int D, int 
     c.copies[s] = static_cast<__nv_bfloat16*>(bf16_copies[s]);
   }
   c.ld_copy = ld_copy; c.self = self_rank;
-  const int64_t items = n_rows * (D / 4);
-  adam_table_dp_kernel<<<static_cast<unsigned>(ceil_div64(items, 256)), 256, 0, as_stream(stream)>>>(c);
+  adam_table_dp_kernel<<<static_cast<unsigned>(ceil_div64(n_rows * 32, 256)), 256, 0, as_stream(stream)>>>(c);     // a warp per row
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
 }
