@@ -1,5 +1,7 @@
-"""Turn gpurun_out/launches.csv (ncu launch list) and gpurun_out/prof_r01.ncu-rep (ncu --set full) into the
-tracked summaries under profiles/.  Usage: python scripts/summarize_profiles.py r01"""
+"""Turn gpurun_out/launches.csv (ncu launch list) and the ncu --set full capture (gpurun_out/prof_<tag>.ncu-rep, or its
+`--page raw --csv` export gpurun_out/prof_<tag>_raw.csv made on the GPU box) into the tracked summaries under
+profiles/: <tag>_launches_summary.txt, <tag>_ncu_full_summary.csv, <tag>_ncu_traffic.json (DRAM bytes per launch of the
+largest launch of each kernel: bench.py's `traffic`).  Usage: python scripts/summarize_profiles.py r02"""
 import collections, csv, io, json, os, subprocess, sys
 tag = sys.argv[1] if len(sys.argv) > 1 else "r01"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -24,8 +26,9 @@ with open(os.path.join(out_dir, "%s_launches_summary.txt" % tag), "w") as f:
     f.write("total %.3f ms over %d launches\n" % (tot, sum(a[0] for a in agg.values())))
 # ---- full capture
 rep = os.path.join(ROOT, "gpurun_out", "prof_%s.ncu-rep" % tag)
-if os.path.exists(rep):
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rawcsv = os.path.join(ROOT, "gpurun_out", "prof_%s_raw.csv" % tag)
+if os.path.exists(rawcsv) or os.path.exists(rep):
+    raw = open(rawcsv).read() if os.path.exists(rawcsv) else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units = rows[0], rows[1]
     want = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
@@ -44,4 +47,20 @@ if os.path.exists(rep):
         wr.writerow([hdr[i] for i in idx]); wr.writerow([units[i] for i in idx])
         for r in rows[2:]:
             wr.writerow([r[i] for i in idx])
+    # DRAM traffic per launch (GB) of the largest launch of each kernel, keyed as bench.py's roofline entries
+    names = {"conv_pool_tc_kernel": "conv_pool_tc", "dw2_tc_kernel": "dw2_tc", "dx2_tc_kernel": "dx2_tc", "adam_table_kernel": "adam_table",
+             "emb_gather_bf16_drop_kernel": "emb_gather", "seg_reduce_tree_kernel": "emb_scatter", "gemm_tf32_async_kernel": "dense"}
+    ki, ri, wi, ti = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("gpu__time_duration.sum")
+    def gb(v, u):
+        v = float(v.replace(",", ""))
+        return v * {"Gbyte": 1.0, "Mbyte": 1e-3, "Kbyte": 1e-6, "byte": 1e-9}.get(u, 1.0)
+    traffic = {}
+    for r in rows[2:]:
+        for frag, key in names.items():
+            if frag in r[ki]:
+                t = gb(r[ri], units[ri]) + gb(r[wi], units[wi])
+                if t > traffic.get(key, 0.0):
+                    traffic[key] = round(t, 4)
+    with open(os.path.join(out_dir, "%s_ncu_traffic.json" % tag), "w") as f:
+        json.dump(traffic, f, indent=1, sort_keys=True)
 print("ok")
