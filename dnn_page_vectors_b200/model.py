@@ -376,6 +376,9 @@ class CLSM(object):
         self.overlap = os.environ.get("CLSM_OVERLAP", "1") != "0"      # two-stream step, see step_resident
         self._side = None
         self._plan_stream = None
+        self._copy_stream = None       # host -> device token copies (see _copy_begin)
+        self._ev_tok_free = None       # the last training step has finished reading its token buffers
+        self._loss_pin = None          # pinned landing place of (loss, accuracy): train_on_batch waits for it alone
         self._probe = None             # scripts/overlap_probe.py: events around the two towers' post-loss work
         self._head = {}
         self._pinned = {}
@@ -392,6 +395,22 @@ class CLSM(object):
         return self
 
     # ---- batch staging: [q, pos, neg_0..neg_{J-1}] (host, any int dtype) -> device int32
+    # ---- host -> device staging.  The copies run on their own stream: they wait only until the previous step has
+    # finished READING its token buffers (forward + scatter plan, event _ev_tok_free), not for its backward and
+    # optimizer -- train_on_batch returns as soon as the loss is on the host, so the next batch's transfer overlaps the
+    # rest of the current step.
+    def _copy_begin(self):
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._ev_copied = torch.cuda.Event()
+        if self._ev_tok_free is not None:
+            self._copy_stream.wait_event(self._ev_tok_free)
+        return self._copy_stream
+
+    def _copy_end(self):
+        self._ev_copied.record(self._copy_stream)
+        torch.cuda.current_stream().wait_event(self._ev_copied)
+
     def _stage(self, x, train):
         if len(x) != 2 + self.J:
             raise ValueError("expected %d input arrays [query, pos_doc, %d neg_docs], got %d" % (2 + self.J, self.J, len(x)))
@@ -411,14 +430,17 @@ class CLSM(object):
             dn[:, j, :] = x[1 + j]
         bq = self.query_model.buffers(B, train)
         bd = self.doc_model.buffers(B * (1 + self.J), train)
-        bq["tok"].copy_(pq, non_blocking=True)
-        bd["tok"].view(B, 1 + self.J, self.document_length).copy_(pdoc, non_blocking=True)
+        with torch.cuda.stream(self._copy_begin()):
+            bq["tok"].copy_(pq, non_blocking=True)
+            bd["tok"].view(B, 1 + self.J, self.document_length).copy_(pdoc, non_blocking=True)
+        self._copy_end()
         return B, bq, bd
 
     def _stage_tensors(self, x, train):
         """Batches handed over as int32 torch tensors (pinned host memory, or already on the device): no host-side
-        repacking.  Each array goes to the device with one asynchronous contiguous copy; a strided device-to-device
-        copy (clsm_copy_rows_strided) then puts each document input into its slot of the document tower's interleaved
+        repacking.  Each host array goes to the device with one asynchronous contiguous copy (a strided host copy of
+        400-byte rows was measured at 2 ms per step on one of the test hosts); a strided device-to-device copy
+        (clsm_copy_rows_strided) then puts each document input into its slot of the document tower's interleaved
         (pair, document) token matrix."""
         B = int(x[0].shape[0])
         for a in x:
@@ -426,21 +448,24 @@ class CLSM(object):
                 raise ValueError("tensor batches must be contiguous int32 (pinned host or device memory)")
         bq = self.query_model.buffers(B, train)
         bd = self.doc_model.buffers(B * (1 + self.J), train)
-        bq["tok"].copy_(x[0], non_blocking=True)
         Ld, n = self.document_length, 1 + self.J
-        st = _stream()
         stage = bd.get("tok_stage")
         if stage is None:
             stage = bd["tok_stage"] = torch.empty((n, B, Ld), dtype=torch.int32, device=self.device)
+            bq["tok_stage"] = torch.empty((B, self.query_length), dtype=torch.int32, device=self.device)
+        src = list(x)
+        if any(not a.is_cuda for a in x):
+            with torch.cuda.stream(self._copy_begin()):
+                for i, a in enumerate(x):
+                    if not a.is_cuda:
+                        dst = bq["tok_stage"] if i == 0 else stage[i - 1]
+                        dst.copy_(a, non_blocking=True)
+                        src[i] = dst
+            self._copy_end()
+        st = _stream()
+        bq["tok"].copy_(src[0], non_blocking=True)
         for j in range(n):
-            src = x[1 + j]
-            if not src.is_cuda:
-                # host -> device as ONE contiguous transfer (a strided host copy of 400-byte rows was measured at 2 ms per
-                # step on one of the test hosts), then a strided device-to-device copy into the input's slot of the
-                # (B, 1+J, Ld) token matrix
-                stage[j].copy_(src, non_blocking=True)
-                src = stage[j]
-            call("clsm_copy_rows_strided", C.c_void_p(src.data_ptr()), Ld * 4, C.c_void_p(bd["tok"].data_ptr() + j * Ld * 4),
+            call("clsm_copy_rows_strided", C.c_void_p(src[1 + j].data_ptr()), Ld * 4, C.c_void_p(bd["tok"].data_ptr() + j * Ld * 4),
                  n * Ld * 4, Ld * 4, B, st)
         return B, bq, bd
 
@@ -493,6 +518,14 @@ class CLSM(object):
         self.iterations += 1
         if self.overlap:
             main.wait_event(self._ev_plan)
+        if self._loss_pin is None:
+            self._loss_pin = torch.empty(2, dtype=torch.float32).pin_memory()
+            self._ev_loss = torch.cuda.Event()
+            self._ev_tok_free = torch.cuda.Event()
+        self._loss_pin.copy_(h["loss_acc"], non_blocking=True)      # the step's result leaves right after the loss kernel
+        self._ev_loss.record(torch.cuda.current_stream())
+        if self.overlap:                                            # forward and scatter plans are done with the token buffers
+            self._ev_tok_free.record(torch.cuda.current_stream())
         if self.dp is not None:
             self.query_model.backward(bq)
             self.doc_model.backward(bd)
@@ -530,6 +563,8 @@ class CLSM(object):
             self.doc_model.backward(bd)
             self.query_model.adam(bq, self.iterations)
             self.doc_model.adam(bd, self.iterations)
+        if not self.overlap:                                        # one-stream order: the plans read the tokens in backward()
+            self._ev_tok_free.record(torch.cuda.current_stream())
         return h
 
     # ---- Keras-like batch API (host numpy in, python floats out)
@@ -543,9 +578,9 @@ class CLSM(object):
         B, bq, bd = self._stage(x, True)
         if B == 0:
             return [0.0, 0.0]
-        h = self.step_resident(B, bq, bd)
-        la = h["loss_acc"].cpu().numpy()
-        return [float(la[0]), float(la[1])]
+        self.step_resident(B, bq, bd)
+        self._ev_loss.synchronize()             # loss and accuracy of THIS step; its backward / optimizer run on behind
+        return [float(self._loss_pin[0]), float(self._loss_pin[1])]
 
     def test_on_batch(self, x, y=None):
         if not self.shared_doc_tower:
