@@ -32,6 +32,7 @@ SIGNATURES = {
     "clsm_dropout_mask": (i32, [i64, i32, f32, u64, vp, vp]),
     "clsm_emb_gather_mask": (i32, [vp, i64, vp, i64, i32, i32, i32, vp, i32, f32, u64, vp, vp]),
     "clsm_dropout_scale": (f32, [f32]),
+    "clsm_emb_gather_master": (i32, [vp, i64, vp, i64, i32, vp, i32, f32, u64, vp, vp]),
     "clsm_copy_rows_strided": (i32, [vp, sz, vp, sz, sz, i64, vp]),
     "clsm_dropout_rows": (i32, [vp, i64, i32, f32, u64, vp, vp]),
     "clsm_check_token_ids": (i32, [vp, i64, i64, vp, vp]),

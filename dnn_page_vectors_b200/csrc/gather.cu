@@ -118,6 +118,55 @@ __global__ void dropout_rows_kernel(const float* __restrict__ x, int64_t n, int 
   }
 }
 
+// fp32 MASTER table -> bf16 X (training, single GPU): the optimizer then need not maintain a bf16 copy of the table at
+// all (0.64 GB less written per table and step).  X = bf16(E * keep_bit * 256/t): ONE rounding, where the bf16-table
+// path rounds the table first.  Same Philox stream, same stored bits.
+template <bool DROPOUT>
+__global__ void __launch_bounds__(256)
+emb_gather_master_kernel(const int32_t* __restrict__ tok, int64_t n_tok, const float4* __restrict__ table, int D4 /* float4 per row */,
+                         uint4* __restrict__ X, int out_blocks, int ldx_v,
+                         float inv_keep, uint32_t thr, uint64_t seed, uint16_t* __restrict__ mask_bits) {
+  const int64_t item = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (item >= n_tok * out_blocks) return;
+  const int64_t r = item / out_blocks;
+  const int blk = static_cast<int>(item - r * out_blocks);
+  const int64_t id = __ldg(tok + r);
+  float4 f[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c4 = blk * 4 + i;
+    f[i] = c4 < D4 ? __ldg(table + id * D4 + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  uint32_t x[8];
+  uint32_t bits = 0xFFFFu;
+  if (DROPOUT) {
+    uint32_t bytes[4];
+    dropout_bytes16(seed, static_cast<uint64_t>(r), static_cast<uint32_t>(blk), bytes);
+    const uint32_t thr4 = thr * 0x01010101u;
+    bits = 0;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const uint32_t vm = __vcmpltu4(bytes[w], thr4);
+      bits |= ((((vm & 0x01010101u) * 0x01020408u) >> 24) & 0xFu) << (4 * w);
+      const __nv_bfloat162 q0 = __floats2bfloat162_rn(f[w].x * inv_keep, f[w].y * inv_keep);
+      const __nv_bfloat162 q1 = __floats2bfloat162_rn(f[w].z * inv_keep, f[w].w * inv_keep);
+      x[2 * w] = *reinterpret_cast<const uint32_t*>(&q0) & __byte_perm(vm, 0, 0x1100);
+      x[2 * w + 1] = *reinterpret_cast<const uint32_t*>(&q1) & __byte_perm(vm, 0, 0x3322);
+    }
+    if (mask_bits != nullptr) mask_bits[item] = static_cast<uint16_t>(bits);
+  } else {
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const __nv_bfloat162 q0 = __floats2bfloat162_rn(f[w].x, f[w].y), q1 = __floats2bfloat162_rn(f[w].z, f[w].w);
+      x[2 * w] = *reinterpret_cast<const uint32_t*>(&q0);
+      x[2 * w + 1] = *reinterpret_cast<const uint32_t*>(&q1);
+    }
+  }
+  uint4* dst = X + r * ldx_v + blk * 2;
+  dst[0] = make_uint4(x[0], x[1], x[2], x[3]);
+  dst[1] = make_uint4(x[4], x[5], x[6], x[7]);
+}
+
 __global__ void check_ids_kernel(const int32_t* __restrict__ tok, int64_t n, int64_t n_rows, int32_t* __restrict__ n_bad) {
   const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const bool bad = i < n && (tok[i] < 0 || tok[i] >= n_rows);
@@ -209,6 +258,26 @@ int clsm_emb_gather_mask(const int32_t* tok, int64_t n_tok, const void* table, i
                          int D, int ld_table, int dtype, void* X, int ldx,
                          float keep, uint64_t seed, uint16_t* mask_bits, void* stream) {
   return emb_gather_impl(tok, n_tok, table, n_rows, D, ld_table, dtype, X, ldx, keep, seed, mask_bits, stream);
+}
+
+int clsm_emb_gather_master(const int32_t* tok, int64_t n_tok, const float* table, int64_t n_rows, int D,
+                           void* X, int ldx, float keep, uint64_t seed, uint16_t* mask_bits, void* stream) {
+  CLSM_REQUIRE(n_tok >= 0 && n_rows > 0 && D > 0 && D % 4 == 0 && ldx >= D && ldx % 16 == 0,
+               "emb_gather_master: D must be a multiple of 4 and ldx a multiple of 16 (D=%d ldx=%d)", D, ldx);
+  CLSM_REQUIRE(keep > 0.0f, "emb_gather_master: keep must be > 0");
+  if (n_tok == 0) return CLSM_OK;
+  const int out_blocks = ldx / 16;
+  const unsigned grid = static_cast<unsigned>(ceil_div64(n_tok * out_blocks, 256));
+  const uint32_t thr = keep_threshold(keep);
+  const bool drop = keep < 1.0f && thr < 256u;
+  CLSM_REQUIRE(!drop || thr > 0, "emb_gather_master: keep %g rounds to a keep probability of 0/256", keep);
+  cudaStream_t st = as_stream(stream);
+  if (drop) emb_gather_master_kernel<true><<<grid, 256, 0, st>>>(tok, n_tok, reinterpret_cast<const float4*>(table), D / 4,
+      static_cast<uint4*>(X), out_blocks, ldx * 2 / 16, dropout_scale(keep), thr, seed, mask_bits);
+  else emb_gather_master_kernel<false><<<grid, 256, 0, st>>>(tok, n_tok, reinterpret_cast<const float4*>(table), D / 4,
+      static_cast<uint4*>(X), out_blocks, ldx * 2 / 16, 1.0f, 256u, seed, nullptr);
+  CLSM_LAUNCH_CHECK();
+  return CLSM_OK;
 }
 
 int clsm_check_token_ids(const int32_t* tok, int64_t n_tok, int64_t n_rows, int32_t* n_bad, void* stream) {

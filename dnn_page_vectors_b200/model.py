@@ -73,6 +73,12 @@ class Tower(object):
         self.E_m = torch.zeros_like(self.E)
         self.E_v = torch.zeros_like(self.E)
         self.E_c = torch.zeros((self.V1, self.Dpad), dtype=torch.bfloat16, device=dev) if self.bf16 else None
+        # Single-GPU bf16 training gathers straight from the fp32 master (clsm_emb_gather_master), so the optimizer
+        # does not rewrite the bf16 copy every step; the copy is refreshed on demand, when inference reads it
+        # (compute_table()).  Data-parallel training keeps it current: it is what the ranks send each other.
+        import os
+        self.lazy_copy = (self.bf16 and self.D % 4 == 0 and not net.lazy_table_adam and os.environ.get("CLSM_LAZY_COPY", "1") != "0")
+        self._copy_dirty = False
 
         # --- flat buffer of the small tensors
         sizes = [k * self.D * self.F for k in self.windows] + [self.P, self.P * self.H, self.H]
@@ -113,6 +119,15 @@ class Tower(object):
             call("clsm_pack_conv_w", _ptr(w), k, self.D, self.F, self.Dpad, self.Fpad, self.dtype_code, _ptr(wt), st)
         if table_too and self.bf16:
             call("clsm_table_to_bf16", _ptr(self.E), self.V1, self.D, _ptr(self.E_c), self.Dpad, st)
+            self._copy_dirty = False
+
+    def compute_table(self):
+        """The bf16 compute copy of the embedding table, brought up to date if training steps have moved the master
+        since it was last written."""
+        if self.bf16 and self._copy_dirty:
+            call("clsm_table_to_bf16", _ptr(self.E), self.V1, self.D, _ptr(self.E_c), self.Dpad, _stream())
+            self._copy_dirty = False
+        return self.E_c
 
     # ---- numpy import/export in reference layouts
     def get_weights(self):
@@ -194,8 +209,9 @@ class Tower(object):
         st = _stream()
         S, n_tok = b["S"], b["n_tok"]
         keep = 1.0 - net.params.dropout_prob[0] if train else 1.0
-        table = self.E_c if self.bf16 else self.E
-        ld_table = self.Dpad if self.bf16 else self.D
+        master = train and self.lazy_copy                   # training reads the fp32 master, see __init__
+        table = self.E if (master or not self.bf16) else self.compute_table()
+        ld_table = self.Dpad if (self.bf16 and not master) else self.D
         if not train and self.bf16 and net.conv_impl != "simt" and b.get("fused_gather", True):
             # inference: the embedding lookup happens inside the conv kernel (TMA gather4 of table rows by token id);
             # the gathered matrix X is never written.  Shapes outside that kernel's plan fall back to gather + conv.
@@ -224,8 +240,13 @@ class Tower(object):
     def _gather_and_conv(self, b, train, keep, seed, table, ld_table, st):
         net = self.net
         S, n_tok = b["S"], b["n_tok"]
-        call("clsm_emb_gather_mask", _ptr(b["tok"]), n_tok, _ptr(table), self.V1, self.D, ld_table,
-             self.dtype_code, _ptr(b["X"]), self.Dpad, keep, seed, _ptr(b["mask"]) if (train and keep < 1.0) else C.c_void_p(0), st)
+        mask = _ptr(b["mask"]) if (train and keep < 1.0) else C.c_void_p(0)
+        if train and self.lazy_copy:
+            call("clsm_emb_gather_master", _ptr(b["tok"]), n_tok, _ptr(self.E), self.V1, self.D, _ptr(b["X"]), self.Dpad,
+                 keep, seed, mask, st)
+        else:
+            call("clsm_emb_gather_mask", _ptr(b["tok"]), n_tok, _ptr(table), self.V1, self.D, ld_table,
+                 self.dtype_code, _ptr(b["X"]), self.Dpad, keep, seed, mask, st)
         for i, k in enumerate(self.windows):
             call("clsm_conv_pool_fwd_d", _ptr(b["X"]), self.dtype_code, S, self.L, self.D, self.Dpad, _ptr(self.Wt[i]),
                  k, self.F, self.Fpad, _ptr(b["keys"]), self.P, i * self.F, IMPL[net.conv_impl], st)
@@ -288,7 +309,8 @@ class Tower(object):
                  dE_rows.shape[0], _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
                  _ptr(self.E_c), self.Dpad, st)
         elif hi > lo:
-            copy = self.E_c[lo:hi] if self.E_c is not None else None
+            copy = self.E_c[lo:hi] if (self.E_c is not None and not self.lazy_copy) else None
+            self._copy_dirty = self._copy_dirty or (self.E_c is not None and self.lazy_copy)
             call("clsm_adam_table", _ptr(self.E[lo:hi]), _ptr(self.E_m[lo:hi]), _ptr(self.E_v[lo:hi]), hi - lo, self.D,
                  _ptr(row_of_id[lo:hi]), _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
                  _ptr(copy), self.Dpad, st)

@@ -160,6 +160,7 @@ class DataParallel(object):
             # identical replicas: rank 0's weights and optimizer state everywhere
             for t in tower.state().values():
                 dist.broadcast(t, src=0, group=group)
+            tower.lazy_copy = False                      # the bf16 compute tables are what the ranks exchange: kept current
             R = owner_rows(tower.V1, self.world)
             tower.rows_per_owner = R
             tower.shard = (min(self.rank * R, tower.V1), min((self.rank + 1) * R, tower.V1))

@@ -411,6 +411,16 @@ def test_mask_bits_bf16_dx_and_split_scatter_equal_the_one_call_path():
     unpacked = ((b[:, :, None] >> np.arange(16, dtype=np.uint16)[None, None, :]) & 1).reshape(n_tok, Dpad)[:, :D]
     np.testing.assert_array_equal(unpacked, mask.cpu().numpy())
     assert abs(lib.clsm_dropout_scale(0.75) - 4.0 / 3.0) < 1e-7 and abs(lib.clsm_dropout_scale(0.9) - 256.0 / 230.0) < 1e-7
+    # the same gather straight from the fp32 master table: ONE rounding, same mask, same stored bits
+    X3 = torch.empty_like(X1)
+    bits3 = torch.zeros_like(bits)
+    call("clsm_emb_gather_master", P(tok_d), n_tok, P(E_d), V1, D, P(X3), Dpad, keep, seed, P(bits3), ST())
+    assert torch.equal(bits3, bits)
+    want3 = bf16_round(E[tok] * mask.cpu().numpy().astype(np.float32) * np.float32(4.0 / 3.0))
+    np.testing.assert_array_equal(X3.float().cpu().numpy()[:, :D], want3)
+    assert (X3.float().cpu().numpy()[:, D:] == 0).all()
+    call("clsm_emb_gather_master", P(tok_d), n_tok, P(E_d), V1, D, P(X3), Dpad, 1.0, 0, P(None), ST())
+    np.testing.assert_array_equal(X3.float().cpu().numpy()[:, :D], bf16_round(E[tok]))
     # scatter: one call (Philox regenerated) vs plan + reduce (stored bits)
     dXn = np.zeros((n_tok, Dpad), dtype=np.float32); dXn[:, :D] = rng.randn(n_tok, D)
     dX_d = dev(dXn)

@@ -463,7 +463,7 @@ def test_two_stream_step_is_bit_identical_to_one_stream():
         torch.cuda.synchronize()
         runs.append((losses, {k: v.clone() for k, v in net.query_model.state().items()},
                      {k: v.clone() for k, v in net.doc_model.state().items()},
-                     net.query_model.E_c.clone(), net.doc_model.E_c.clone()))
+                     net.query_model.compute_table().clone(), net.doc_model.compute_table().clone()))
     a, b_ = runs
     assert a[0] == b_[0]
     for i in (1, 2):
