@@ -46,6 +46,38 @@ struct ScoreParams {
   int stages;
 };
 
+// One 16-row chunk in which SOME lane (query) has a survivor.  Out of line and SMALL on purpose: ncu showed the scan of
+// a segment with survivors stalled on instruction fetch (stall_no_inst 36 % of samples) -- the slow path, unrolled over
+// the 64 rows of a batch with the key construction inlined, was ~20 KB of code that eight epilogue warps walked at
+// different places; that, not atomics, stores or votes (all measured), halved the scan rate.  Here: the lane's hits as
+// a 16-bit mask from 16 independent compares, then one iteration per hit with the score picked by a select tree.
+// Values travel in registers (by value: a reference would put them in local memory).
+__device__ __noinline__ int chunk_hits(uint32_t v0, uint32_t v1, uint32_t v2, uint32_t v3, uint32_t v4, uint32_t v5, uint32_t v6, uint32_t v7,
+                                       uint32_t v8, uint32_t v9, uint32_t v10, uint32_t v11, uint32_t v12, uint32_t v13, uint32_t v14, uint32_t v15,
+                                       float thr_f, u64 thr, int64_t row0, int64_t row_end, u64* klist, int n) {
+  const uint32_t v[16] = {v0, v1, v2, v3, v4, v5, v6, v7, v8, v9, v10, v11, v12, v13, v14, v15};
+  unsigned hm = 0;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) hm |= (__uint_as_float(v[i]) >= thr_f) ? (1u << i) : 0u;
+  while (hm != 0u) {
+    const int pos = __ffs(hm) - 1;
+    hm &= hm - 1;
+    uint32_t a[8], b[4], c[2];                                      // select tree on the bits of pos: static register indices only
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = (pos & 1) ? v[2 * i + 1] : v[2 * i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) b[i] = (pos & 2) ? a[2 * i + 1] : a[2 * i];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) c[i] = (pos & 4) ? b[2 * i + 1] : b[2 * i];
+    const float x = __uint_as_float((pos & 8) ? c[1] : c[0]);
+    const int64_t row = row0 + pos;
+    // a row that ties the threshold score but loses on the id is dropped by the exact 64-bit compare
+    const u64 key = (static_cast<u64>(f32_to_ordered(x + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row));
+    if (row < row_end && key >= thr) klist[n++] = key;
+  }
+  return n;
+}
+
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmC, const ScoreParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -154,10 +186,9 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         tc_wait_ld();
         if (cb + 64 >= cb_begin + NT / 2) { tc_fence_before(); if (lane == 0) mbar_arrive(tempty_bar(acc)); }
         if (p.cnt != nullptr) {
-          // Lanes are different queries, so a survivor in one lane must not make the other 31 pay for it: every test
-          // below is a WARP-UNIFORM branch on a vote (all 32 lanes are converged here; lanes of queries past nQ carry
-          // thr_f = +inf and never vote yes).  Behind a threshold one row in hundreds survives per query, i.e. a few
-          // per 32 x 64 batch: the batch costs ~50 compare/vote/branch triples plus the rare append.
+          // Lanes are different queries.  A tree max per 16 rows and two levels of warp-uniform votes (all 32 lanes are
+          // converged here; lanes of queries past nQ carry thr_f = +inf and never vote yes) decide whether any lane has a
+          // survivor in a chunk; only then the small out-of-line routine above runs.
           float m[4];
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
@@ -170,19 +201,9 @@ score_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           if (__any_sync(0xffffffffu, fmaxf(fmaxf(m[0], m[1]), fmaxf(m[2], m[3])) >= thr_f)) {
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-              if (__any_sync(0xffffffffu, m[c] >= thr_f)) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                  const float x = __uint_as_float(v[c][i]);
-                  const bool hit = x >= thr_f;
-                  if (__any_sync(0xffffffffu, hit)) {
-                    const int64_t row = r0 + cb + c * 16 + i;
-                    // a row that ties the threshold score but loses on the id is dropped by the exact 64-bit compare
-                    const u64 key = (static_cast<u64>(f32_to_ordered(x + 0.0f)) << 32) | static_cast<u64>(0xFFFFFFFFu - static_cast<uint32_t>(row));
-                    if (hit && row < p.row_end && key >= thr) klist[n_mine++] = key;
-                  }
-                }
-              }
+              if (__any_sync(0xffffffffu, m[c] >= thr_f))
+                n_mine = chunk_hits(v[c][0], v[c][1], v[c][2], v[c][3], v[c][4], v[c][5], v[c][6], v[c][7], v[c][8], v[c][9], v[c][10],
+                                    v[c][11], v[c][12], v[c][13], v[c][14], v[c][15], thr_f, thr, r0 + cb + c * 16, p.row_end, klist, n_mine);
             }
           }
         } else if (qok) {
