@@ -57,6 +57,11 @@ SIGNATURES = {
     "clsm_emb_scatter": (i32, [vp, i64, vp, i32, i32, f32, u64, i64, vp, vp, vp, vp, vp, sz, vp]),
     "clsm_adam_dense": (i32, [vp, vp, vp, vp, i64, i32, f32, f32, f32, f32, vp]),
     "clsm_adam_table": (i32, [vp, vp, vp, i64, i32, vp, vp, i32, i32, f32, f32, f32, f32, vp, i32, vp]),
+    "clsm_adam_lr_table": (i32, [f32, f32, f32, i32, i32, vp]),
+    "clsm_adam_defer_workspace_bytes": (C.c_size_t, [i64, i64]),
+    "clsm_adam_defer_settle_tokens": (i32, [vp, vp, vp, i64, i32, vp, vp, i64, i32, vp, f32, f32, f32, vp, i32, vp, C.c_size_t, vp]),
+    "clsm_adam_defer_rows": (i32, [vp, vp, vp, i32, vp, vp, vp, i64, vp, i32, i32, vp, f32, f32, f32, vp, i32, vp]),
+    "clsm_adam_defer_settle_all": (i32, [vp, vp, vp, i64, i32, vp, i32, vp, f32, f32, f32, vp, i32, vp]),
     "clsm_adam_rows": (i32, [vp, vp, vp, i32, vp, vp, i64, vp, i32, i32, f32, f32, f32, f32, vp, i32, vp]),
     "clsm_table_to_bf16": (i32, [vp, i64, i32, vp, i32, vp]),
     "clsm_dp_push_rows": (i32, [vp, vp, i64, vp, i32, i32, vp, i64, i64, i32, vp, vp, i64, vp, vp]),

@@ -106,6 +106,19 @@ __host__ __device__ __forceinline__ uint32_t keep_threshold(float keep) {
   int t = static_cast<int>(keep * 256.0f + 0.5f);
   return t < 0 ? 0u : (t > 256 ? 256u : static_cast<uint32_t>(t));
 }
+// One element of Keras-1 Adam.  Every operation carries its rounding (.rn intrinsics are never contracted, by nvcc or
+// by ptxas), so the dense pass, the data-parallel pass and the deferred-row replay (adam.cu) produce the same bits
+// from the same inputs whatever code surrounds them.  sqrt.approx and the rcp-based divide are <= 2 ulp each: the
+// dense pass is HBM-bound only if the ~600 M sqrt+divide pairs per step stay off the issue limit (the IEEE
+// sequences cost ~40 instructions per element), and 2 ulp on a 1e-3 step is far inside the parity tolerance.
+__device__ __forceinline__ void adam_step1(float& p, float& m, float& v, float g, float b1, float b2, float omb1, float omb2,
+                                           float lr_t, float eps) {
+  m = __fmaf_rn(b1, m, __fmul_rn(omb1, g));
+  v = __fmaf_rn(b2, v, __fmul_rn(__fmul_rn(omb2, g), g));
+  float s;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(s) : "f"(v));
+  p = __fsub_rn(p, __fdividef(__fmul_rn(lr_t, m), __fadd_rn(s, eps)));
+}
 // inverted-dropout scale = 1 / the realised keep probability (thr / 256), so E[X] is unbiased for every keep
 __host__ __device__ __forceinline__ float dropout_scale(float keep) {
   const uint32_t t = keep_threshold(keep);

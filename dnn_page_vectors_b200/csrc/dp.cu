@@ -74,11 +74,7 @@ struct AdamDpP {
 };
 
 __device__ __forceinline__ void adam1(float& p, float& m, float& v, float g, const AdamDpP& c) {
-  m = c.b1 * m + c.omb1 * g;
-  v = c.b2 * v + c.omb2 * g * g;
-  float s;
-  asm("sqrt.approx.f32 %0, %1;" : "=f"(s) : "f"(v));
-  p = p - __fdividef(c.lr_t * m, s + c.eps);
+  adam_step1(p, m, v, g, c.b1, c.b2, c.omb1, c.omb2, c.lr_t, c.eps);      // common.cuh: the arithmetic of adam.cu
 }
 
 // D % 4 == 0.  One WARP per owned row (same arithmetic as adam_table_kernel<true> in adam.cu).  Lane s looks up

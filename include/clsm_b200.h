@@ -225,6 +225,32 @@ int clsm_adam_table(float* p, float* m, float* v, int64_t n_rows, int D,
 int clsm_adam_rows(float* p, float* m, float* v, int D, const int32_t* uniq_ids,
                    const int32_t* n_uniq, int64_t max_uniq, const float* dE_rows, int ldg, int step,
                    float lr, float b1, float b2, float eps, void* bf16_copy, int ld_copy, void* stream);
+/* Deferred rows: the SAME dense Keras semantics as clsm_adam_table, without streaming the whole table every step.
+ * A row without gradient takes its step with g = 0, which reads only the row's own p, m, v and the step number --
+ * so it can be taken later, when the row is next needed, by replaying the owed steps in order in registers.
+ * last (n_rows) int32: the last step stored p, m, v include; -1 = m and v still exactly zero (such a row owes
+ * nothing).  Initialise it to -1 with zeroed m, v, or to the current step when optimizer state is loaded.
+ * lr_tab: DEVICE array, lr_tab[s] = lr_t of step s for every s up to the step in use (fill a host array with
+ * clsm_adam_lr_table and copy it; entry 0 is unused).  Once every row is settled the table, m and v equal bit for bit
+ * what clsm_adam_table would have left.
+ *   clsm_adam_defer_settle_tokens: before a batch is gathered at step t, bring the rows its tokens name up to
+ *     to_step = t - 1.  ws: clsm_adam_defer_workspace_bytes(n_tok, n_rows).
+ *   clsm_adam_defer_rows: the optimizer step `step` of the rows that have a gradient (uniq_ids / n_uniq / dE_rows of
+ *     clsm_emb_scatter); rows that still owe steps are settled to step - 1 first.
+ *   clsm_adam_defer_settle_all: every row up to to_step -- before the table is read as a whole (export, checkpoint,
+ *     inference, a change of lr).
+ * bf16_copy (n_rows, ld_copy), when not NULL, receives the bf16 image of every row written. */
+int clsm_adam_lr_table(float lr, float b1, float b2, int first_step, int n, float* lr_t_host);
+size_t clsm_adam_defer_workspace_bytes(int64_t n_tok, int64_t n_rows);
+int clsm_adam_defer_settle_tokens(float* p, float* m, float* v, int64_t n_rows, int D, int32_t* last,
+                                  const int32_t* tok, int64_t n_tok, int to_step, const float* lr_tab,
+                                  float b1, float b2, float eps, void* bf16_copy, int ld_copy,
+                                  void* ws, size_t ws_bytes, void* stream);
+int clsm_adam_defer_rows(float* p, float* m, float* v, int D, int32_t* last, const int32_t* uniq_ids,
+                         const int32_t* n_uniq, int64_t max_uniq, const float* dE_rows, int ldg, int step,
+                         const float* lr_tab, float b1, float b2, float eps, void* bf16_copy, int ld_copy, void* stream);
+int clsm_adam_defer_settle_all(float* p, float* m, float* v, int64_t n_rows, int D, int32_t* last, int to_step,
+                               const float* lr_tab, float b1, float b2, float eps, void* bf16_copy, int ld_copy, void* stream);
 /* fp32 (n_rows, D) -> bf16 (n_rows, ld_copy) with zero pad columns */
 int clsm_table_to_bf16(const float* p, int64_t n_rows, int D, void* bf16_copy, int ld_copy, void* stream);
 

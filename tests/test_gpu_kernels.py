@@ -1,4 +1,5 @@
 """Per-kernel parity on the GPU, through the C ABI, against the CPU oracle (-m gpu)."""
+import ctypes as C
 import numpy as np
 import pytest
 import torch
@@ -539,6 +540,64 @@ def test_adam_dense_and_table():
         pp, mm, vv = E0.copy(), np.zeros((V1, D)), np.zeros((V1, D))
         O.adam_step(pp, mm, vv, gfull, 1)
         np.testing.assert_allclose(E2.cpu().numpy(), pp, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("D,loaded", [(300, False), (300, True), (20, False), (401, True)])
+def test_deferred_rows_adam_is_bit_identical_to_the_dense_pass(D, loaded):
+    """clsm_adam_defer_*: rows without gradient take their zero-gradient steps later, in registers.  After every step
+    the rows the NEXT batch reads, and after settle_all the whole table with m and v, must equal clsm_adam_table's
+    bit for bit -- from zeroed state (rows marked -1) and from loaded state (rows marked with the current step)."""
+    rng = np.random.RandomState(91)
+    V1, ldg, steps, t0 = 3000, rup(D, 64), 45, (7 if loaded else 0)
+    lr, b1, b2, eps = 1e-3, 0.9, 0.999, 1e-8
+    E0 = (rng.randn(V1, D) * 0.05).astype(np.float32)
+    m0 = (rng.randn(V1, D) * 1e-3).astype(np.float32) if loaded else np.zeros((V1, D), np.float32)
+    v0 = (rng.rand(V1, D) * 1e-5).astype(np.float32) if loaded else np.zeros((V1, D), np.float32)
+    A = [dev(E0), dev(m0), dev(v0)]                    # dense
+    Bt = [dev(E0), dev(m0), dev(v0)]                   # deferred
+    last = torch.full((V1,), t0 if loaded else -1, dtype=torch.int32, device=DEV)
+    use_copy = D % 4 == 0
+    copyA = torch.zeros((V1, ldg), dtype=torch.bfloat16, device=DEV) if use_copy else None
+    copyB = torch.zeros((V1, ldg), dtype=torch.bfloat16, device=DEV) if use_copy else None
+    if use_copy:
+        for c in (copyA, copyB):
+            call("clsm_table_to_bf16", P(A[0]), V1, D, P(c), ldg, ST())
+    tab = np.zeros(t0 + steps + 2, dtype=np.float32)
+    call("clsm_adam_lr_table", lr, b1, b2, 0, tab.size, C.c_void_p(tab.ctypes.data))
+    lr_tab = dev(tab)
+    n_tok = 700
+    ws_bytes = lib.clsm_adam_defer_workspace_bytes(n_tok, V1)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV)
+    for i in range(steps):
+        step = t0 + i + 1
+        tok = (rng.zipf(1.3, size=n_tok) % V1).astype(np.int32)
+        if i % 7 == 3:
+            tok[:50] = rng.randint(0, V1, size=50)                # rare rows: long gaps
+        ids = np.unique(tok).astype(np.int32)
+        rows = np.zeros((ids.size, ldg), dtype=np.float32); rows[:, :D] = rng.randn(ids.size, D) * 0.1
+        roi = np.full(V1, -1, dtype=np.int32); roi[ids] = np.arange(ids.size)
+        tok_d, ids_d, rows_d, roi_d, cnt_d = dev(tok), dev(ids), dev(rows), dev(roi), dev(np.array([ids.size], dtype=np.int32))
+        # what the gather of this step reads: the batch's rows as the dense pass left them after step - 1
+        call("clsm_adam_defer_settle_tokens", P(Bt[0]), P(Bt[1]), P(Bt[2]), V1, D, P(last), P(tok_d), n_tok, step - 1, P(lr_tab),
+             b1, b2, eps, P(copyB), ldg, P(ws), ws_bytes, ST())
+        np.testing.assert_array_equal(Bt[0][ids_d.long()].cpu().numpy(), A[0][ids_d.long()].cpu().numpy())
+        if use_copy:
+            np.testing.assert_array_equal(copyB[ids_d.long()].float().cpu().numpy(), copyA[ids_d.long()].float().cpu().numpy())
+        call("clsm_adam_table", P(A[0]), P(A[1]), P(A[2]), V1, D, P(roi_d), P(rows_d), ldg, step, lr, b1, b2, eps, P(copyA), ldg, ST())
+        call("clsm_adam_defer_rows", P(Bt[0]), P(Bt[1]), P(Bt[2]), D, P(last), P(ids_d), P(cnt_d), n_tok, P(rows_d), ldg, step,
+             P(lr_tab), b1, b2, eps, P(copyB), ldg, ST())
+    torch.cuda.synchronize()
+    assert int((last.cpu().numpy() == t0 + steps).sum()) < V1          # some rows do owe steps: the test tests something
+    if not loaded:
+        assert (last.cpu().numpy() == -1).any()
+    call("clsm_adam_defer_settle_all", P(Bt[0]), P(Bt[1]), P(Bt[2]), V1, D, P(last), t0 + steps, P(lr_tab), b1, b2, eps, P(copyB), ldg, ST())
+    torch.cuda.synchronize()
+    for a, b in zip(A, Bt):
+        np.testing.assert_array_equal(b.cpu().numpy(), a.cpu().numpy())
+    if use_copy:
+        np.testing.assert_array_equal(copyB.float().cpu().numpy(), copyA.float().cpu().numpy())
+    lv = last.cpu().numpy()
+    assert ((lv == t0 + steps) | (lv == -1)).all()
 
 
 # ------------------------------------------------------------------ top-k
