@@ -245,8 +245,16 @@ def main():
     if world > 1:
         from dnn_page_vectors_b200.parallel import DataParallel
         DataParallel(net)
-    batches = make_batches(c, 4, 1337 + rank)
+    # a DISTINCT batch for every warm-up and timed step (up to 32): which table rows a step touches, and how many steps
+    # the others owe, is then that of a fresh token stream, not of a 4-batch cycle
+    batches = make_batches(c, min(max(warmup + steps, 4), 32), 1337 + rank)
     B = c["B"]
+    deferred = world == 1 and net.defer_table_adam and not args.lazy_adam
+    if deferred:
+        # every table row counts as carrying optimizer state (what a loaded checkpoint, or a long run, looks like):
+        # each of its zero-gradient steps is then really executed -- in a later step or in the settle that closes the
+        # timed region -- instead of being skipped as a no-op on zero m, v
+        net.assume_optimizer_state()
 
     def barrier():
         if world > 1:
@@ -257,6 +265,7 @@ def main():
     bq, bd, resident_step = stage_resident(net, c, batches, torch)
     for i in range(warmup):
         resident_step(i)
+    net.settle()                     # the warm-up's owed row steps are paid before the clock starts
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -265,23 +274,29 @@ def main():
     marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
     marks[0].record()
     for i in range(steps):
-        resident_step(i)
+        resident_step(warmup + i)
         marks[i + 1].record()
+    net.settle()                     # INSIDE the timed region: every row step the K steps deferred is taken here at the latest
+    m_end = torch.cuda.Event(enable_timing=True)
+    m_end.record()
     barrier()
     launches = int(lib.clsm_launch_count() - l0)
-    ms = marks[0].elapsed_time(marks[steps])
+    ms = marks[0].elapsed_time(m_end)
+    settle_ms = marks[steps].elapsed_time(m_end)
     per_step = [marks[i].elapsed_time(marks[i + 1]) for i in range(steps)]
     # ---- e2e: host batches in PINNED memory through the public API (train_on_batch): ids H2D and loss D2H
     # inside every step
     pinned = [[torch.as_tensor(a).pin_memory() for a in x] for x in batches]
     for i in range(2):
         net.train_on_batch(pinned[i % len(pinned)])
+    net.settle()
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     last = None
     for i in range(steps):
         last = net.train_on_batch(pinned[i % len(pinned)])
+    net.settle()
     e3.record()
     barrier()
     ms_e2e = e2.elapsed_time(e3)
@@ -300,10 +315,16 @@ def main():
         "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "global_batch": B * world, "activation": c["act"], "dropout": 0.25,
-                   "table_adam": "lazy-rows" if args.lazy_adam else "dense (Keras semantics)",
+                   "table_adam": ("lazy-rows" if args.lazy_adam else
+                                  "dense (Keras semantics); zero-gradient row steps deferred and replayed bit-exactly, every row treated as "
+                                  "carrying optimizer state, the settle of all rows INSIDE the timed region (settle_ms)" if deferred else
+                                  "dense (Keras semantics)"),
+                   "distinct_batches": len(batches),
                    "conv_impl": args.conv_impl, "parallelism": "dp%d" % world,
                    "streams": "two (query tower's backward/scatter/Adam beside the document tower's)" if (world == 1 and net.overlap) else "one",
-                   "l2": "inputs larger than L2: each step streams both 1M x 300 tables and their Adam state (14 GB)",
+                   "l2": ("inputs larger than L2: a step writes and re-reads the 1.3 GB gathered matrix and its 1.3 GB gradient and touches "
+                          "~0.2 M table rows with their Adam state; a different batch every step" if deferred else
+                          "inputs larger than L2: each step streams both 1M x 300 tables and their Adam state (14 GB)"),
                    "tokens": "Zipf(1.07) ids (frequency rank -> id by a fixed random permutation), true length U[L/4,L], right-padded with one PAD id"},
         "step_ms": {"median": pct(per_step, 0.5), "p90": pct(per_step, 0.9), "min": min(per_step), "max": max(per_step),
                     "note": "rank 0's device time per step of the timed region (events between steps)"},
@@ -312,6 +333,9 @@ def main():
         "gpu_launches": launches,
         "clocks": clocks,
     }
+    if deferred:
+        line["settle_ms"] = settle_ms
+        line["step_ms"]["note"] += "; ms_per_step = (the K steps + the closing settle of every table row, settle_ms) / K"
 
     if world > 1 and args.dp_profile:
         dp_profile(net, resident_step, torch, rank)
@@ -324,7 +348,8 @@ def main():
         if rank == 0:
             line["kernels"] = phases
             from dnn_page_vectors_b200._lib import BF16 as _BF16
-            fill_roofline(line, c, launch, clocks, pk, steps, ms, dx_bytes=2 if bd.get("dx_dtype") == _BF16 else 4)
+            fill_roofline(line, c, launch, clocks, pk, steps, ms, dx_bytes=2 if bd.get("dx_dtype") == _BF16 else 4,
+                          n_uniq_doc=int(bd["n_uniq"].item()))
         # ---- configs[4] at this N: sharded encode and retrieval
         try:
             line_sh = bench_sharded(net, c, torch, dist, pk, rank, world, args.shard_pages)
@@ -353,7 +378,7 @@ def main():
     return 0
 
 
-def fill_roofline(line, c, launch, clocks, pk, steps, ms, dx_bytes=4):
+def fill_roofline(line, c, launch, clocks, pk, steps, ms, dx_bytes=4, n_uniq_doc=0):
     """launch: {kernel: directly measured device ms of ONE launch of the document tower (or of one table)}.
     dx_bytes: element size of the dX rows the scatter reads (2 when the tensor-core backward writes them as bf16)."""
     B = c["B"]
@@ -378,6 +403,7 @@ def fill_roofline(line, c, launch, clocks, pk, steps, ms, dx_bytes=4):
         "dense_fwd": ("tensor", dense_doc_tf, "2 |K|F H per sequence"),
         "dense_bwd": ("tensor", 2 * dense_doc_tf, "dWd and G GEMMs"),
         "adam_table": ("hbm", 24.0 * n_table / 1e9, "24 B per parameter of one 1M x 300 table (p, m, v read + write)"),
+        "adam_defer_rows": ("hbm", 28.0 * n_uniq_doc * c["D"] / 1e9, "28 B per parameter of the %d document-table rows of the batch (p, m, v read + write, gradient row read)" % n_uniq_doc),
         # SURVEY 8(d) figures.  gather: ids + table rows read; "the write is not counted when fused" -- it is NOT fused
         # here (the kernel must write X, Dpad bf16 per token), so both accountings are printed (frac_with_write below).
         "emb_gather": ("hbm", n_doc * (4 + c["D"] * 2) / 1e9, "SURVEY 8(d): ids + table rows read (the X write, which this standalone kernel also does, is not counted)"),

@@ -69,9 +69,15 @@ class Tower(object):
         self.cdtype = torch.bfloat16 if self.bf16 else torch.float32
 
         # --- embedding table: master fp32 (V1, D) + Adam state, bf16 compute copy (V1, Dpad)
-        self.E = torch.as_tensor(np.ascontiguousarray(table, dtype=np.float32)).to(dev)
-        self.E_m = torch.zeros_like(self.E)
-        self.E_v = torch.zeros_like(self.E)
+        self._E = torch.as_tensor(np.ascontiguousarray(table, dtype=np.float32)).to(dev)
+        self._E_m = torch.zeros_like(self._E)
+        self._E_v = torch.zeros_like(self._E)
+        # Deferred rows (adam.cu): the step of a row WITHOUT gradient (g = 0, pure momentum) is not taken when the batch
+        # is stepped but replayed, bit-exactly, when the row is next read.  _last[row] = the last step the stored row
+        # includes, -1 while its m and v are still zero.  E / E_m / E_v (properties) settle every row before they
+        # hand the tensors out; the training step itself works on _E / _E_m / _E_v.
+        self._last = torch.full((self.V1,), -1, dtype=torch.int32, device=dev)
+        self._owes = False                 # some row may owe steps
         self.E_c = torch.zeros((self.V1, self.Dpad), dtype=torch.bfloat16, device=dev) if self.bf16 else None
         # Single-GPU bf16 training gathers straight from the fp32 master (clsm_emb_gather_master), so the optimizer
         # does not rewrite the bf16 copy every step; the copy is refreshed on demand, when inference reads it
@@ -113,6 +119,45 @@ class Tower(object):
         lim = math.sqrt(6.0 / (self.P + self.H))
         self.Wd.copy_(torch.as_tensor(rng.uniform(-lim, lim, size=(self.P, self.H)).astype(np.float32)))
 
+    @property
+    def E(self):
+        self.settle()
+        return self._E
+
+    @property
+    def E_m(self):
+        self.settle()
+        return self._E_m
+
+    @property
+    def E_v(self):
+        self.settle()
+        return self._E_v
+
+    @property
+    def defer(self):
+        return self.net.defer_table_adam and self.net.dp is None
+
+    def _defer_copy(self):
+        """the bf16 table the deferred kernels keep current row by row: none when training reads the fp32 master"""
+        return self.E_c if (self.E_c is not None and not self.lazy_copy) else None
+
+    def settle(self):
+        """Every row takes the zero-gradient steps it still owes (up to net.iterations).  Called wherever the table or
+        its optimizer state is read as a whole: export, checkpoint, inference, set_weights, the data-parallel set-up."""
+        if not self._owes:
+            return
+        p, net = self.net.params, self.net
+        call("clsm_adam_defer_settle_all", _ptr(self._E), _ptr(self._E_m), _ptr(self._E_v), self.V1, self.D, _ptr(self._last),
+             net.iterations, _ptr(net.lr_table(net.iterations)), p.beta_1, p.beta_2, p.epsilon,
+             _ptr(self._defer_copy()), self.Dpad, _stream())
+        self._owes = False
+
+    def mark_settled(self):
+        """optimizer state was loaded: every row is current and none is known to have zero m, v"""
+        self._last.fill_(self.net.iterations)
+        self._owes = False
+
     def refresh_compute_copies(self, table_too=False):
         st = _stream()
         for w, wt, k in zip(self.convW, self.Wt, self.windows):
@@ -124,8 +169,9 @@ class Tower(object):
     def compute_table(self):
         """The bf16 compute copy of the embedding table, brought up to date if training steps have moved the master
         since it was last written."""
+        self.settle()
         if self.bf16 and self._copy_dirty:
-            call("clsm_table_to_bf16", _ptr(self.E), self.V1, self.D, _ptr(self.E_c), self.Dpad, _stream())
+            call("clsm_table_to_bf16", _ptr(self._E), self.V1, self.D, _ptr(self.E_c), self.Dpad, _stream())
             self._copy_dirty = False
         return self.E_c
 
@@ -144,7 +190,8 @@ class Tower(object):
     def set_weights(self, w, theano_kernels=False):
         """theano_kernels: conv kernels trained under Keras-Theano are applied flipped along the
         window axis (filter_flip=True); flip them once on import."""
-        self.E.copy_(torch.as_tensor(np.asarray(w["E"], dtype=np.float32)))
+        self.settle()                             # owed steps belong to the OLD table
+        self._E.copy_(torch.as_tensor(np.asarray(w["E"], dtype=np.float32)))
         for i, cw in enumerate(self.convW):
             a = np.asarray(w["convW%d" % i], dtype=np.float32)
             if a.ndim == 4:                       # Keras (k, 1, D, F)
@@ -157,8 +204,10 @@ class Tower(object):
         self.bd.copy_(torch.as_tensor(np.asarray(w["bd"], dtype=np.float32)))
         self.refresh_compute_copies(table_too=True)
 
-    def state(self):
-        return {"E": self.E, "E_m": self.E_m, "E_v": self.E_v,
+    def state(self, settle=True):
+        if settle:
+            self.settle()
+        return {"E": self._E, "E_m": self._E_m, "E_v": self._E_v,
                 "flat": self.flat, "flat_m": self.flat_m, "flat_v": self.flat_v}
 
     # ---- per-shape scratch (allocated once per (S, train) and reused)
@@ -200,6 +249,8 @@ class Tower(object):
             b["ws_sc_bytes"] = lib.clsm_emb_scatter_workspace_bytes(n_tok, self.D)
             b["ws_sc"] = torch.empty(b["ws_sc_bytes"], dtype=torch.uint8, device=dev)
             b["planned"] = False
+            b["ws_df_bytes"] = lib.clsm_adam_defer_workspace_bytes(n_tok, self.V1)
+            b["ws_df"] = torch.empty(b["ws_df_bytes"], dtype=torch.uint8, device=dev)
         self._bufs[key] = b
         return b
 
@@ -210,7 +261,18 @@ class Tower(object):
         S, n_tok = b["S"], b["n_tok"]
         keep = 1.0 - net.params.dropout_prob[0] if train else 1.0
         master = train and self.lazy_copy                   # training reads the fp32 master, see __init__
-        table = self.E if (master or not self.bf16) else self.compute_table()
+        if train and self.defer and self._owes:
+            # the rows this batch reads take the steps they owe (all but the coming one) before they are gathered
+            p = net.params
+            call("clsm_adam_defer_settle_tokens", _ptr(self._E), _ptr(self._E_m), _ptr(self._E_v), self.V1, self.D, _ptr(self._last),
+                 _ptr(b["tok"]), n_tok, net.iterations, _ptr(net.lr_table(net.iterations + 1)), p.beta_1, p.beta_2, p.epsilon,
+                 _ptr(self._defer_copy()), self.Dpad, _ptr(b["ws_df"]), b["ws_df_bytes"], st)
+        elif not train:
+            self.settle()
+        if master or not self.bf16:
+            table = self._E
+        else:
+            table = self.E_c if (train and self.defer) else self.compute_table()
         ld_table = self.Dpad if (self.bf16 and not master) else self.D
         if not train and self.bf16 and net.conv_impl != "simt" and b.get("fused_gather", True):
             # inference: the embedding lookup happens inside the conv kernel (TMA gather4 of table rows by token id);
@@ -242,7 +304,7 @@ class Tower(object):
         S, n_tok = b["S"], b["n_tok"]
         mask = _ptr(b["mask"]) if (train and keep < 1.0) else C.c_void_p(0)
         if train and self.lazy_copy:
-            call("clsm_emb_gather_master", _ptr(b["tok"]), n_tok, _ptr(self.E), self.V1, self.D, _ptr(b["X"]), self.Dpad,
+            call("clsm_emb_gather_master", _ptr(b["tok"]), n_tok, _ptr(self._E), self.V1, self.D, _ptr(b["X"]), self.Dpad,
                  keep, seed, mask, st)
         else:
             call("clsm_emb_gather_mask", _ptr(b["tok"]), n_tok, _ptr(table), self.V1, self.D, ld_table,
@@ -296,7 +358,7 @@ class Tower(object):
             # receive buffers; the kernel also stores the refreshed bf16 rows into every rank's compute table
             if hi > lo:
                 dp = self.net.dp
-                call("clsm_adam_table_dp", _ptr(self.E[lo:hi]), _ptr(self.E_m[lo:hi]), _ptr(self.E_v[lo:hi]), hi - lo, self.D,
+                call("clsm_adam_table_dp", _ptr(self._E[lo:hi]), _ptr(self._E_m[lo:hi]), _ptr(self._E_v[lo:hi]), hi - lo, self.D,
                      dp.world, _ptr(sparse_grad["map_in"]), self.rows_per_owner, _ptr(sparse_grad["rows_in"]),
                      sparse_grad["cap"], self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
                      self._peer_Ec_rows, dp.rank, self.Dpad, st)
@@ -304,14 +366,22 @@ class Tower(object):
             return
         row_of_id, dE_rows, uniq, n_uniq = sparse_grad if sparse_grad is not None else (
             b["row_of_id"], b["dE_rows"], b["uniq"], b["n_uniq"])
-        if self.net.lazy_table_adam:
-            call("clsm_adam_rows", _ptr(self.E), _ptr(self.E_m), _ptr(self.E_v), self.D, _ptr(uniq), _ptr(n_uniq),
+        if self.defer and sparse_grad is None and not self.net.lazy_table_adam:
+            # rows with a gradient take step `step`; every other row owes it (replayed when next read, see settle())
+            call("clsm_adam_defer_rows", _ptr(self._E), _ptr(self._E_m), _ptr(self._E_v), self.D, _ptr(self._last), _ptr(uniq),
+                 _ptr(n_uniq), dE_rows.shape[0], _ptr(dE_rows), self.Dpad, step, _ptr(self.net.lr_table(step)),
+                 p.beta_1, p.beta_2, p.epsilon, _ptr(self._defer_copy()), self.Dpad, st)
+            self._owes = True
+            self._copy_dirty = self._copy_dirty or (self.E_c is not None and self.lazy_copy)
+        elif self.net.lazy_table_adam:
+            call("clsm_adam_rows", _ptr(self._E), _ptr(self._E_m), _ptr(self._E_v), self.D, _ptr(uniq), _ptr(n_uniq),
                  dE_rows.shape[0], _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
                  _ptr(self.E_c), self.Dpad, st)
         elif hi > lo:
             copy = self.E_c[lo:hi] if (self.E_c is not None and not self.lazy_copy) else None
             self._copy_dirty = self._copy_dirty or (self.E_c is not None and self.lazy_copy)
-            call("clsm_adam_table", _ptr(self.E[lo:hi]), _ptr(self.E_m[lo:hi]), _ptr(self.E_v[lo:hi]), hi - lo, self.D,
+            self.settle()
+            call("clsm_adam_table", _ptr(self._E[lo:hi]), _ptr(self._E_m[lo:hi]), _ptr(self._E_v[lo:hi]), hi - lo, self.D,
                  _ptr(row_of_id[lo:hi]), _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
                  _ptr(copy), self.Dpad, st)
         self.refresh_compute_copies(table_too=False)
@@ -359,7 +429,7 @@ class CLSM(object):
 
     def __init__(self, params=None, query_length=20, document_length=975, embedding_weights=None,
                  vocab_size=None, device=None, conv_impl="auto", lazy_table_adam=False,
-                 shared_doc_tower=True, post_dense_dropout=False):
+                 shared_doc_tower=True, post_dense_dropout=False, defer_table_adam=None):
         """shared_doc_tower=False, post_dense_dropout=True is the v1 model (dssm_cnn/cnn_dssm.py:105-167): the
         query, the positive document and every negative document each get their OWN tower (embedding table included,
         :160-164) and a second Dropout(dropout_prob[1]) sits between Dense and relu (:148-150).  The default is v2
@@ -371,6 +441,11 @@ class CLSM(object):
         torch.cuda.set_device(self.device)
         self.conv_impl = conv_impl
         self.lazy_table_adam = lazy_table_adam
+        import os
+        # dense Keras Adam with the zero-gradient steps of untouched rows deferred and replayed bit-exactly (Tower.settle)
+        self.defer_table_adam = (os.environ.get("CLSM_DEFER_ADAM", "1") != "0") if defer_table_adam is None else bool(defer_table_adam)
+        self.iterations = 0
+        self._lr_tab, self._lr_key, self._lr_old = None, None, []
         self.rng = np.random.RandomState(self.params.seed)
         self.query_length, self.document_length = int(query_length), int(document_length)
         self.J = int(self.params.J)
@@ -404,6 +479,40 @@ class CLSM(object):
         self._probe = None             # scripts/overlap_probe.py: events around the two towers' post-loss work
         self._head = {}
         self._pinned = {}
+
+    def lr_table(self, upto):
+        """Device array lr_tab[s] = Adam's lr_t of step s, valid for s <= upto (the deferred-row kernels replay old steps
+        with the step size each of them had).  A change of lr / beta settles every row under the old table first."""
+        p = self.params
+        key = (float(p.lr), float(p.beta_1), float(p.beta_2))
+        if self._lr_tab is not None and self._lr_key == key and upto < self._lr_tab.shape[0]:
+            return self._lr_tab
+        if self._lr_tab is not None and self._lr_key != key:
+            saved, self.params = self.params, self._lr_params          # the steps owed so far were taken with the old values
+            for t in [self.query_model] + list(self.doc_models):
+                t.settle()
+            self.params = saved
+        n = max(1 << 16, 2 * (int(upto) + 1))
+        host = np.zeros(n, dtype=np.float32)
+        call("clsm_adam_lr_table", key[0], key[1], key[2], 0, n, C.c_void_p(host.ctypes.data))
+        if self._lr_tab is not None:
+            self._lr_old.append(self._lr_tab)                          # kernels already queued may still read it
+        self._lr_tab, self._lr_key = torch.as_tensor(host).to(self.device), key
+        import copy
+        self._lr_params = copy.copy(p)
+        return self._lr_tab
+
+    def settle(self):
+        """All towers: every table row takes the zero-gradient steps it still owes (Tower.settle)."""
+        for t in [self.query_model] + list(self.doc_models):
+            t.settle()
+
+    def assume_optimizer_state(self):
+        """Treat every table row as carrying Adam state (as after load()): its zero-gradient steps are replayed even
+        while m and v are still zero.  Same results; bench.py uses it so that no row step is free."""
+        for t in [self.query_model] + list(self.doc_models):
+            t.settle()
+            t.mark_settled()
 
     # cnn_dssm_tf.py:81-127
     def model(self, sequence_length=None):
@@ -869,8 +978,9 @@ class CLSM(object):
         pairs = [(self.query_model, st["query"])]
         pairs += [(self.doc_model, st["doc"])] if self.shared_doc_tower else list(zip(self.doc_models, st["docs"]))
         for tower, saved in pairs:
-            for name, t in tower.state().items():
+            for name, t in tower.state(settle=False).items():          # whatever the old rows owed is overwritten
                 t.copy_(saved[name])
+            tower.mark_settled()
             tower.refresh_compute_copies(table_too=True)
         return self
 

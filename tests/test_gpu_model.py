@@ -472,6 +472,49 @@ def test_two_stream_step_is_bit_identical_to_one_stream():
     assert torch.equal(a[3], b_[3]) and torch.equal(a[4], b_[4])
 
 
+@pytest.mark.parametrize("precision,cfg", [("bf16", dict(CFG_ONE, B=64, V=3000)), ("fp32", dict(CFG_SMALL, V=2000)),
+                                           ("bf16", dict(CFG_SMALL, V=2000, D=50))],        # D % 4 != 0: bf16 table kept row by row
+                         ids=["bf16-cfg1", "fp32-ref-literal", "bf16-D50"])
+def test_deferred_row_steps_leave_exactly_the_dense_adam_state(precision, cfg, tmp_path):
+    """The table optimizer defers the zero-gradient steps of rows a batch does not touch and replays them when the row
+    is next read (Tower.settle, adam.cu).  A run of 14 different batches -- with an evaluation, a save/load into a
+    fresh model and a set_weights on the way -- must leave the same weights, optimizer state, losses and compute
+    tables as the same run with the dense pass (defer_table_adam = False), bit for bit."""
+    xs = [synth(40 + i, cfg["B"], cfg["J"], cfg["Lq"], cfg["Ld"], cfg["V"]) for i in range(14)]
+    runs = []
+    for defer in (True, False):
+        net, _, _ = build(precision, "relu", dropout=0.25, conv_impl="auto" if precision == "bf16" else "simt", **cfg)
+        net.defer_table_adam = defer
+        out = []
+        for i, x in enumerate(xs):
+            out.append(net.train_on_batch(x))
+            if i == 4:
+                out.append(net.test_on_batch(xs[0]))                   # inference reads the whole (settled) table
+            if i == 7:                                                  # checkpoint mid-run, resume in a fresh model
+                path = str(tmp_path / ("ck%d.pt" % defer))
+                net.save(path)
+                net, _, _ = build(precision, "relu", dropout=0.25, seed=3, conv_impl="auto" if precision == "bf16" else "simt", **cfg)
+                net.defer_table_adam = defer
+                net.load(path)
+            if i == 10:                                                 # weights replaced while rows owe steps
+                w = net.get_weights()
+                w["doc"]["E"] = w["doc"]["E"] * np.float32(0.5)
+                net.set_weights(w)
+        if defer:
+            assert net.doc_model._owes and int((net.doc_model._last < net.iterations).sum()) > 0     # rows do owe steps here
+        torch.cuda.synchronize()
+        runs.append((out, {k: v.clone() for k, v in net.query_model.state().items()},
+                     {k: v.clone() for k, v in net.doc_model.state().items()},
+                     net.query_model.compute_table(), net.doc_model.compute_table()))
+    a, b_ = runs
+    assert a[0] == b_[0]
+    for i in (1, 2):
+        for k in a[i]:
+            assert torch.equal(a[i][k], b_[i][k]), k
+    if precision == "bf16":
+        assert torch.equal(a[3], b_[3]) and torch.equal(a[4], b_[4])
+
+
 def test_keras_checkpoint_interchange_on_the_model(tmp_path):
     """save_weights / load_weights / ModelCheckpoint with the '.npz' container (Keras-1 names and kernel layouts):
     a second model that loads the file predicts exactly what the first one does."""
