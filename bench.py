@@ -565,8 +565,9 @@ def profile_phases(net, resident_step, torch):
     finally:
         M.call = orig
         net.overlap = was
-    out = {k + "_ms": float(np.median([r.get(k, 0.0) for r in totals])) for k in totals[0]}
-    launch = {k: float(np.median([r.get(k, 0.0) for r in launches])) for k in launches[0]}
+    keys = sorted(set().union(*totals), key=lambda k: min(list(r).index(k) if k in r else 99 for r in totals))
+    out = {k + "_ms": float(np.median([r.get(k, 0.0) for r in totals])) for k in keys}
+    launch = {k: float(np.median([r.get(k, 0.0) for r in launches])) for k in set().union(*launches)}
     rename = {"conv_pool_fwd": "conv_pool_tc", "conv_pool_fwd_d": "conv_pool_tc", "emb_gather_mask": "emb_gather", "emb_gather_master": "emb_gather", "conv_pool_bwd_ex": "conv_pool_bwd",
               "emb_scatter_reduce": "emb_scatter"}
     launch = {rename.get(k, k): v for k, v in launch.items()}

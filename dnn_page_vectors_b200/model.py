@@ -79,11 +79,15 @@ class Tower(object):
         self._last = torch.full((self.V1,), -1, dtype=torch.int32, device=dev)
         self._owes = False                 # some row may owe steps
         self.E_c = torch.zeros((self.V1, self.Dpad), dtype=torch.bfloat16, device=dev) if self.bf16 else None
-        # Single-GPU bf16 training gathers straight from the fp32 master (clsm_emb_gather_master), so the optimizer
-        # does not rewrite the bf16 copy every step; the copy is refreshed on demand, when inference reads it
-        # (compute_table()).  Data-parallel training keeps it current: it is what the ranks send each other.
+        # Single-GPU bf16 training with the DENSE table pass (defer_table_adam=False) gathers straight from the fp32
+        # master (clsm_emb_gather_master), so the optimizer does not rewrite the bf16 copy every step; the copy is
+        # refreshed on demand, when inference reads it (compute_table()).  Data-parallel training keeps it current: it
+        # is what the ranks send each other.
         import os
-        self.lazy_copy = (self.bf16 and self.D % 4 == 0 and not net.lazy_table_adam and os.environ.get("CLSM_LAZY_COPY", "1") != "0")
+        # With deferred row steps (the default) the optimizer writes only the batch's rows, so keeping their bf16 images
+        # current costs ~0.1 GB per step and the gather reads 640-byte instead of 1200-byte rows: the copy stays eager.
+        self.lazy_copy = (self.bf16 and self.D % 4 == 0 and not net.lazy_table_adam and not net.defer_table_adam
+                          and os.environ.get("CLSM_LAZY_COPY", "1") != "0")
         self._copy_dirty = False
 
         # --- flat buffer of the small tensors
