@@ -336,6 +336,32 @@ def main():
     if deferred:
         line["settle_ms"] = settle_ms
         line["step_ms"]["note"] += "; ms_per_step = (the K steps + the closing settle of every table row, settle_ms) / K"
+        if not args.no_extras:
+            # the same steps with the DENSE table pass (every row of both tables streamed every step, round 1's and
+            # early round 2's optimizer; fp32-master gather, no bf16 copy written): what deferring the row steps buys
+            net.settle()
+            towers = (net.query_model, net.doc_model)
+            was = [(t.lazy_copy, ) for t in towers]
+            net.defer_table_adam = False
+            for t in towers:
+                t.lazy_copy = t.bf16 and t.D % 4 == 0
+            for i in range(3):
+                resident_step(i)
+            torch.cuda.synchronize()
+            d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n_dense = min(steps, 10)
+            d0.record()
+            for i in range(n_dense):
+                resident_step(3 + i)
+            d1.record()
+            torch.cuda.synchronize()
+            dms = d0.elapsed_time(d1) / n_dense
+            line["dense_table_pass"] = {"ms_per_step": dms, "pairs_per_s": B / (dms * 1e-3), "steps": n_dense,
+                                        "note": "same model and batches, defer_table_adam=False: clsm_adam_table over all rows of both tables each step"}
+            net.defer_table_adam = True
+            for t, (lc,) in zip(towers, was):
+                t.lazy_copy = lc
+                t.refresh_compute_copies(table_too=True)
 
     if world > 1 and args.dp_profile:
         dp_profile(net, resident_step, torch, rank)

@@ -78,6 +78,7 @@ class Tower(object):
         # hand the tensors out; the training step itself works on _E / _E_m / _E_v.
         self._last = torch.full((self.V1,), -1, dtype=torch.int32, device=dev)
         self._owes = False                 # some row may owe steps
+        self._dense_to = None              # the dense pass ran last, through this step: _last is stale until re-stamped
         self.E_c = torch.zeros((self.V1, self.Dpad), dtype=torch.bfloat16, device=dev) if self.bf16 else None
         # Single-GPU bf16 training with the DENSE table pass (defer_table_adam=False) gathers straight from the fp32
         # master (clsm_emb_gather_master), so the optimizer does not rewrite the bf16 copy every step; the copy is
@@ -149,6 +150,7 @@ class Tower(object):
     def settle(self):
         """Every row takes the zero-gradient steps it still owes (up to net.iterations).  Called wherever the table or
         its optimizer state is read as a whole: export, checkpoint, inference, set_weights, the data-parallel set-up."""
+        self._restamp()
         if not self._owes:
             return
         p, net = self.net.params, self.net
@@ -157,10 +159,16 @@ class Tower(object):
              _ptr(self._defer_copy()), self.Dpad, _stream())
         self._owes = False
 
+    def _restamp(self):
+        """after steps taken by the dense pass (which moves every row and does not stamp them)"""
+        if self._dense_to is not None:
+            self._last.fill_(self._dense_to)
+            self._dense_to = None
+
     def mark_settled(self):
         """optimizer state was loaded: every row is current and none is known to have zero m, v"""
         self._last.fill_(self.net.iterations)
-        self._owes = False
+        self._owes, self._dense_to = False, None
 
     def refresh_compute_copies(self, table_too=False):
         st = _stream()
@@ -265,14 +273,16 @@ class Tower(object):
         S, n_tok = b["S"], b["n_tok"]
         keep = 1.0 - net.params.dropout_prob[0] if train else 1.0
         master = train and self.lazy_copy                   # training reads the fp32 master, see __init__
+        if train and self.defer:
+            self._restamp()
         if train and self.defer and self._owes:
             # the rows this batch reads take the steps they owe (all but the coming one) before they are gathered
             p = net.params
             call("clsm_adam_defer_settle_tokens", _ptr(self._E), _ptr(self._E_m), _ptr(self._E_v), self.V1, self.D, _ptr(self._last),
                  _ptr(b["tok"]), n_tok, net.iterations, _ptr(net.lr_table(net.iterations + 1)), p.beta_1, p.beta_2, p.epsilon,
                  _ptr(self._defer_copy()), self.Dpad, _ptr(b["ws_df"]), b["ws_df_bytes"], st)
-        elif not train:
-            self.settle()
+        elif not (train and self.defer):
+            self.settle()                                   # inference, or training with the dense pass: whole table current
         if master or not self.bf16:
             table = self._E
         else:
@@ -360,6 +370,7 @@ class Tower(object):
         if isinstance(sparse_grad, dict):
             # peer-memory data parallel path (parallel.py): gradient pieces of all ranks sit in this rank's
             # receive buffers; the kernel also stores the refreshed bf16 rows into every rank's compute table
+            self._dense_to = step
             if hi > lo:
                 dp = self.net.dp
                 call("clsm_adam_table_dp", _ptr(self._E[lo:hi]), _ptr(self._E_m[lo:hi]), _ptr(self._E_v[lo:hi]), hi - lo, self.D,
@@ -372,6 +383,7 @@ class Tower(object):
             b["row_of_id"], b["dE_rows"], b["uniq"], b["n_uniq"])
         if self.defer and sparse_grad is None and not self.net.lazy_table_adam:
             # rows with a gradient take step `step`; every other row owes it (replayed when next read, see settle())
+            self._restamp()
             call("clsm_adam_defer_rows", _ptr(self._E), _ptr(self._E_m), _ptr(self._E_v), self.D, _ptr(self._last), _ptr(uniq),
                  _ptr(n_uniq), dE_rows.shape[0], _ptr(dE_rows), self.Dpad, step, _ptr(self.net.lr_table(step)),
                  p.beta_1, p.beta_2, p.epsilon, _ptr(self._defer_copy()), self.Dpad, st)
@@ -385,6 +397,7 @@ class Tower(object):
             copy = self.E_c[lo:hi] if (self.E_c is not None and not self.lazy_copy) else None
             self._copy_dirty = self._copy_dirty or (self.E_c is not None and self.lazy_copy)
             self.settle()
+            self._dense_to = step
             call("clsm_adam_table", _ptr(self._E[lo:hi]), _ptr(self._E_m[lo:hi]), _ptr(self._E_v[lo:hi]), hi - lo, self.D,
                  _ptr(row_of_id[lo:hi]), _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
                  _ptr(copy), self.Dpad, st)
