@@ -32,16 +32,16 @@ if os.path.exists(rawcsv) or os.path.exists(rep):
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units = rows[0], rows[1]
     want = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
-            "dram__throughput.avg.pct_of_peak_sustained_elapsed", "sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed",
+            "dram__throughput.avg.pct_of_peak_sustained_elapsed", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
             "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
             "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic", "smsp__inst_executed.sum",
             "smsp__issue_active.avg.pct_of_peak_sustained_active", "lts__t_sector_hit_rate.pct", "l1tex__m_xbar2l1tex_read_bytes.sum",
             "sm__cycles_elapsed.avg.per_second", "lts__throughput.avg.pct_of_peak_sustained_elapsed"]
     idx = []
-    for w in want:
-        for i, h in enumerate(hdr):
-            if h == w or h.endswith("." + w):
-                idx.append(i); break
+    for w in want:                                  # the plain metric if the capture has it, else a section-prefixed one
+        hit = [i for i, h in enumerate(hdr) if h == w] or [i for i, h in enumerate(hdr) if h.endswith("." + w)]
+        if hit:
+            idx.append(hit[0])
     with open(os.path.join(out_dir, "%s_ncu_full_summary.csv" % tag), "w") as f:
         wr = csv.writer(f)
         wr.writerow([hdr[i] for i in idx]); wr.writerow([units[i] for i in idx])
@@ -49,7 +49,8 @@ if os.path.exists(rawcsv) or os.path.exists(rep):
             wr.writerow([r[i] for i in idx])
     # DRAM traffic per launch (GB) of the largest launch of each kernel, keyed as bench.py's roofline entries
     names = {"conv_pool_tc_kernel": "conv_pool_tc", "dw2_tc_kernel": "dw2_tc", "dx2_tc_kernel": "dx2_tc", "adam_table_kernel": "adam_table",
-             "emb_gather_bf16_drop_kernel": "emb_gather", "seg_reduce_tree_kernel": "emb_scatter", "gemm_tf32_async_kernel": "dense"}
+             "emb_gather_bf16_drop_kernel": "emb_gather", "seg_reduce_tree_kernel": "emb_scatter", "gemm_tf32_async_kernel": "dense",
+             "defer_adam_rows_kernel": "adam_defer_rows", "defer_settle_list_kernel": "adam_defer_settle_tokens"}
     ki, ri, wi, ti = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("gpu__time_duration.sum")
     def gb(v, u):
         v = float(v.replace(",", ""))
