@@ -321,7 +321,9 @@ def main():
                                   "dense (Keras semantics)"),
                    "distinct_batches": len(batches),
                    "conv_impl": args.conv_impl, "parallelism": "dp%d" % world,
-                   "streams": "two (query tower's backward/scatter/Adam beside the document tower's)" if (world == 1 and net.overlap) else "one",
+                   "streams": ("three after the loss (query tower | document dX then conv weight gradients | document scatter + table optimizer beside those)"
+                               if (world == 1 and net.overlap and net.split_bwd) else
+                               "two (query tower's backward/scatter/Adam beside the document tower's)" if (world == 1 and net.overlap) else "one"),
                    "l2": ("inputs larger than L2: a step writes and re-reads the 1.3 GB gathered matrix and its 1.3 GB gradient and touches "
                           "~0.2 M table rows with their Adam state; a different batch every step" if deferred else
                           "inputs larger than L2: each step streams both 1M x 300 tables and their Adam state (14 GB)"),
@@ -559,7 +561,7 @@ def profile_phases(net, resident_step, torch):
     def timed(name, *a):
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         mids = None
-        if name in ("clsm_conv_pool_bwd", "clsm_conv_pool_bwd_ex"):
+        if name in ("clsm_conv_pool_bwd", "clsm_conv_pool_bwd_ex", "clsm_conv_pool_bwd_parts"):
             mids = (new_event(), new_event())
             _lib.lib.clsm_debug_mark_conv_bwd(C.c_void_p(mids[0].cuda_event), C.c_void_p(mids[1].cuda_event))
         s.record()
@@ -594,7 +596,7 @@ def profile_phases(net, resident_step, torch):
     keys = sorted(set().union(*totals), key=lambda k: min(list(r).index(k) if k in r else 99 for r in totals))
     out = {k + "_ms": float(np.median([r.get(k, 0.0) for r in totals])) for k in keys}
     launch = {k: float(np.median([r.get(k, 0.0) for r in launches])) for k in set().union(*launches)}
-    rename = {"conv_pool_fwd": "conv_pool_tc", "conv_pool_fwd_d": "conv_pool_tc", "emb_gather_mask": "emb_gather", "emb_gather_master": "emb_gather", "conv_pool_bwd_ex": "conv_pool_bwd",
+    rename = {"conv_pool_fwd": "conv_pool_tc", "conv_pool_fwd_d": "conv_pool_tc", "emb_gather_mask": "emb_gather", "emb_gather_master": "emb_gather", "conv_pool_bwd_ex": "conv_pool_bwd", "conv_pool_bwd_parts": "conv_pool_bwd",
               "emb_scatter_reduce": "emb_scatter"}
     launch = {rename.get(k, k): v for k, v in launch.items()}
     out["doc_tower_launch_ms"] = {k: round(v, 4) for k, v in launch.items()}

@@ -245,6 +245,18 @@ int clsm_conv_pool_bwd_ex(const void* X, int dtype, int64_t S, int L, int D, int
                           const float* G, const int32_t* argmax, int ldp, int col0,
                           float* dW_ref, float* db, void* dX_any, int dx_dtype, int first_window,
                           void* ws, size_t ws_bytes, void* stream) {
+  return clsm_conv_pool_bwd_parts(X, dtype, S, L, D, Dpad, Wt, k, F, Fpad, G, argmax, ldp, col0, dW_ref, db, dX_any, dx_dtype,
+                                  first_window, CLSM_BWD_DW | CLSM_BWD_DX, ws, ws_bytes, stream);
+}
+
+// The two gradients read the same inputs, write different outputs and use disjoint workspace regions, so a caller may
+// issue them as two calls on two streams (parts = CLSM_BWD_DX on one, CLSM_BWD_DW on the other).
+int clsm_conv_pool_bwd_parts(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
+                             const void* Wt, int k, int F, int Fpad,
+                             const float* G, const int32_t* argmax, int ldp, int col0,
+                             float* dW_ref, float* db, void* dX_any, int dx_dtype, int first_window, int parts,
+                             void* ws, size_t ws_bytes, void* stream) {
+  CLSM_REQUIRE((parts & ~(CLSM_BWD_DW | CLSM_BWD_DX)) == 0 && parts != 0, "conv_pool_bwd: parts must be CLSM_BWD_DW, CLSM_BWD_DX or both");
   CLSM_REQUIRE(dtype == CLSM_BF16 || dtype == CLSM_F32, "conv_pool_bwd: bad dtype");
   CLSM_REQUIRE(dx_dtype == CLSM_F32 || dx_dtype == CLSM_BF16, "conv_pool_bwd: dX must be fp32 or bf16");
   const int dx_bf16 = dx_dtype == CLSM_BF16 ? 1 : 0;
@@ -272,9 +284,11 @@ int clsm_conv_pool_bwd_ex(const void* X, int dtype, int64_t S, int L, int D, int
   w += align_up(static_cast<size_t>(kColsumChunks) * F * 4, 256);
   void* sort_scratch = w;
 
+  int rc = CLSM_OK;
+  if (parts & CLSM_BWD_DW) {
   // dW: tensor cores (bf16 mode) -> shared-memory staged CUDA cores -> generic
   int n_parts = n_groups;
-  int rc = clsm_conv_bwd_dw_tc(X, dtype, L, Dpad, S, n_groups, G, argmax, ldp, col0, F, k, part, st);
+  rc = clsm_conv_bwd_dw_tc(X, dtype, L, Dpad, S, n_groups, G, argmax, ldp, col0, F, k, part, st);
   if (rc > 0) { n_parts = rc; rc = CLSM_OK; }
   else if (rc == CLSM_EUNSUPPORTED) rc = clsm_conv_bwd_dw_fast(X, dtype, L, Dpad, S, n_groups, G, argmax, ldp, col0, F, k, part, st);
   if (rc == CLSM_EUNSUPPORTED) {            // shape outside the shared-memory plan: generic kernel
@@ -292,6 +306,8 @@ int clsm_conv_pool_bwd_ex(const void* X, int dtype, int64_t S, int L, int D, int
   conv_bwd_dw_reduce_kernel<<<static_cast<unsigned>(ceil_div64(ne, 256)), 256, 0, st>>>(part, n_parts, k, D, Dpad, F, dW_ref);
   CLSM_LAUNCH_CHECK();
   if (clsm_colsum(G, S, ldp, col0, F, db, cs, kColsumChunks, st) != CLSM_OK) { clsm_set_error("conv_pool_bwd: colsum launch failed"); return CLSM_ECUDA; }
+  }
+  if (!(parts & CLSM_BWD_DX)) return CLSM_OK;
 
   // dX: tensor cores (bf16 mode) -> shared-memory staged CUDA cores -> generic
   void* wb_scratch = static_cast<char*>(sort_scratch) + clsm_conv_bwd_dx_fast_bytes(S, L, F);

@@ -329,21 +329,37 @@ class Tower(object):
 
     # ---- backward: gradient of the loss wrt sem in b['dsem']; fills flat_g and the sparse table grad
     def backward(self, b):
+        self.backward_head(b)
+        self.backward_conv(b, 3)
+        self.backward_scatter(b)
+
+    def backward_head(self, b):
         net = self.net
         st = _stream()
-        S, n_tok = b["S"], b["n_tok"]
+        S = b["S"]
         act = ACT[net.params.activation]
         if b.get("keep2", 1.0) < 1.0:                  # dropped semantic units get no gradient, kept ones 1/keep of it
             call("clsm_dropout_rows", _ptr(b["dsem"]), S, self.H, b["keep2"], b["seed2"], _ptr(b["dsem"]), st)
         call("clsm_dense_bwd", _ptr(b["pooled"]), _ptr(b["sem"]), _ptr(b["dsem"]), S, self.P, self.P, _ptr(self.Wd),
              self.H, act | (MATH_TF32 if self.bf16 else 0), _ptr(self.g_Wd), _ptr(self.g_bd), _ptr(b["G"]),
              _ptr(b["ws"]), b["ws_bytes"], st)
+
+    def backward_conv(self, b, parts):
+        """parts: 1 = conv weight / bias gradients, 2 = the gradient of the gathered rows (dX), 3 = both.  The two read the
+        same tensors and write different ones (disjoint workspace regions too), so step_resident issues them on two
+        streams: dX first, then dW beside the embedding scatter and the table optimizer that consume dX."""
+        st = _stream()
+        S = b["S"]
         for i, k in enumerate(self.windows):
             gb = self.g_convb[i * self.F:(i + 1) * self.F]
-            call("clsm_conv_pool_bwd_ex", _ptr(b["X"]), self.dtype_code, S, self.L, self.D, self.Dpad, _ptr(self.Wt[i]),
+            call("clsm_conv_pool_bwd_parts", _ptr(b["X"]), self.dtype_code, S, self.L, self.D, self.Dpad, _ptr(self.Wt[i]),
                  k, self.F, self.Fpad, _ptr(b["G"]), _ptr(b["argmax"]), self.P, i * self.F,
-                 _ptr(self.g_convW[i]), _ptr(gb), _ptr(b["dX"]), b["dx_dtype"], 1 if i == 0 else 0,
+                 _ptr(self.g_convW[i]), _ptr(gb), _ptr(b["dX"]), b["dx_dtype"], 1 if i == 0 else 0, parts,
                  _ptr(b["ws"]), b["ws_bytes"], st)
+
+    def backward_scatter(self, b):
+        st = _stream()
+        n_tok = b["n_tok"]
         if not b["planned"]:
             self.plan_scatter(b)
         b["planned"] = False
@@ -358,14 +374,19 @@ class Tower(object):
              _ptr(b["n_uniq"]), _ptr(b["row_of_id"]), _ptr(b["ws_sc"]), b["ws_sc_bytes"], _stream())
         b["planned"] = True
 
-    def adam(self, b, step, sparse_grad=None):
+    def adam(self, b, step, sparse_grad=None, parts=3):
         """sparse_grad: optional (row_of_id, dE_rows, uniq, n_uniq) replacing this rank's own
         (the data-parallel path passes the globally reduced gradient of the rows this rank owns).
-        self.shard = (lo, hi): table rows this rank's optimizer owns (all rows when not data parallel)."""
+        self.shard = (lo, hi): table rows this rank's optimizer owns (all rows when not data parallel).
+        parts: 1 = the small tensors (+ their compute copies), 2 = the embedding table, 3 = both."""
         p = self.net.params
         st = _stream()
-        call("clsm_adam_dense", _ptr(self.flat), _ptr(self.flat_m), _ptr(self.flat_v), _ptr(self.flat_g),
-             self.n_small, step, p.lr, p.beta_1, p.beta_2, p.epsilon, st)
+        if parts & 1:
+            call("clsm_adam_dense", _ptr(self.flat), _ptr(self.flat_m), _ptr(self.flat_v), _ptr(self.flat_g),
+                 self.n_small, step, p.lr, p.beta_1, p.beta_2, p.epsilon, st)
+            self.refresh_compute_copies(table_too=False)
+        if not parts & 2:
+            return
         lo, hi = self.shard
         if isinstance(sparse_grad, dict):
             # peer-memory data parallel path (parallel.py): gradient pieces of all ranks sit in this rank's
@@ -377,7 +398,6 @@ class Tower(object):
                      dp.world, _ptr(sparse_grad["map_in"]), self.rows_per_owner, _ptr(sparse_grad["rows_in"]),
                      sparse_grad["cap"], self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
                      self._peer_Ec_rows, dp.rank, self.Dpad, st)
-            self.refresh_compute_copies(table_too=False)
             return
         row_of_id, dE_rows, uniq, n_uniq = sparse_grad if sparse_grad is not None else (
             b["row_of_id"], b["dE_rows"], b["uniq"], b["n_uniq"])
@@ -401,7 +421,6 @@ class Tower(object):
             call("clsm_adam_table", _ptr(self._E[lo:hi]), _ptr(self._E_m[lo:hi]), _ptr(self._E_v[lo:hi]), hi - lo, self.D,
                  _ptr(row_of_id[lo:hi]), _ptr(dE_rows), self.Dpad, step, p.lr, p.beta_1, p.beta_2, p.epsilon,
                  _ptr(copy), self.Dpad, st)
-        self.refresh_compute_copies(table_too=False)
 
     # ---- Keras-like predict on a tower: tokens (N, L) -> semantic vectors (N, H) numpy
     def predict(self, tokens, batch_size=4096):
@@ -489,6 +508,8 @@ class CLSM(object):
         import os
         self.overlap = os.environ.get("CLSM_OVERLAP", "1") != "0"      # two-stream step, see step_resident
         self._side = None
+        self._tail = None              # third stream: scatter + table optimizer beside the conv weight gradients
+        self.split_bwd = os.environ.get("CLSM_SPLIT_BWD", "1") != "0"
         self._plan_stream = None
         self._copy_stream = None       # host -> device token copies (see _copy_begin)
         self._ev_tok_free = None       # the last training step has finished reading its token buffers
@@ -640,6 +661,11 @@ class CLSM(object):
         return base + (rank << 44), base + 1 + (rank << 44)
 
     # ---- device-resident step (bench `value`): tokens already staged in the tower buffers
+    def _mark(self, name):
+        """scripts/overlap_probe.py: an event on the current stream at a named point of the step"""
+        if self._probe is not None and name in self._probe:
+            self._probe[name].record(torch.cuda.current_stream())
+
     def step_resident(self, B, bq, bd):
         """One training step.  After the loss kernel the two towers are independent: the query tower's backward,
         scatter and table Adam (HBM-bound: a 1.2 GB table and its Adam state) and the document tower's tensor-bound
@@ -660,7 +686,9 @@ class CLSM(object):
                 self.query_model.plan_scatter(bq)
                 self._ev_plan.record(self._plan_stream)
         self.query_model.forward(bq, True, sq)
+        self._mark("fq")
         self.doc_model.forward(bd, True, sd)
+        self._mark("fd")
         bt = B * (self.dp.world if self.dp is not None else 1)
         h = self._forward_head(B, bq, bd, True, bt)
         self.iterations += 1
@@ -697,11 +725,36 @@ class CLSM(object):
             self.query_model.adam(bq, self.iterations)
             if self._probe is not None:
                 self._probe["q1"].record(main)
+            dm = self.doc_model
+            if self._tail is None:
+                self._tail = torch.cuda.Stream(device=self.device)
+                self._ev_dx, self._ev_tab = torch.cuda.Event(), torch.cuda.Event()
             with torch.cuda.stream(self._side):
                 if self._probe is not None:
                     self._probe["d0"].record(self._side)
-                self.doc_model.backward(bd)
-                self.doc_model.adam(bd, self.iterations)
+                dm.backward_head(bd)
+                if self.split_bwd:
+                    # dX first; then the conv weight gradients (tensor-bound, persistent CTAs, this high-priority stream)
+                    # run beside the scatter of dX and the table optimizer (HBM-bound, short CTAs, a third stream)
+                    self._mark("hd")
+                    dm.backward_conv(bd, 2)
+                    self._mark("dx")
+                    self._ev_dx.record(self._side)
+                    self._tail.wait_event(self._ev_dx)
+                    with torch.cuda.stream(self._tail):
+                        dm.backward_scatter(bd)
+                        self._mark("sc")
+                        dm.adam(bd, self.iterations, parts=2)
+                        self._mark("tab")
+                        self._ev_tab.record(self._tail)
+                    dm.backward_conv(bd, 1)
+                    self._mark("dw")
+                    dm.adam(bd, self.iterations, parts=1)
+                    self._side.wait_event(self._ev_tab)
+                else:
+                    dm.backward_conv(bd, 3)
+                    dm.backward_scatter(bd)
+                    dm.adam(bd, self.iterations)
                 if self._probe is not None:
                     self._probe["d1"].record(self._side)
                 self._ev_join.record(self._side)

@@ -179,6 +179,15 @@ int clsm_conv_pool_bwd_ex(const void* X, int dtype, int64_t S, int L, int D, int
                           const float* G, const int32_t* argmax, int ldp, int col0,
                           float* dW_ref, float* db, void* dX, int dx_dtype, int first_window,
                           void* ws, size_t ws_bytes, void* stream);
+/* The same, one gradient at a time: parts = CLSM_BWD_DW (dW_ref, db), CLSM_BWD_DX (dX) or both.  The two parts read the
+ * same inputs, write different outputs and use disjoint regions of ws, so they may be issued on two streams. */
+#define CLSM_BWD_DW 1
+#define CLSM_BWD_DX 2
+int clsm_conv_pool_bwd_parts(const void* X, int dtype, int64_t S, int L, int D, int Dpad,
+                             const void* Wt, int k, int F, int Fpad,
+                             const float* G, const int32_t* argmax, int ldp, int col0,
+                             float* dW_ref, float* db, void* dX, int dx_dtype, int first_window, int parts,
+                             void* ws, size_t ws_bytes, void* stream);
 
 /* ---- embedding gradient: deterministic sort + segmented reduce -------------------------------
  * replaces the gradient of Embedding (AdvancedIncSubtensor1 / UnsortedSegmentSum).
