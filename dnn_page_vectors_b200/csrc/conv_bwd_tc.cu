@@ -1140,7 +1140,17 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
   // Slice width of tiling 2: 160 columns when that divides Dpad (D = 300 -> Dpad = 320 = 2 x 160: no padded
   // columns, against 3 x 128 = 384), else 128.
   const bool force1 = env != nullptr && env[0] == '1';
-  const int nw = (!force1 && Dpad % 160 == 0 && k * 160 <= 512) ? 160 : DW_NT;
+  // Wider windows take narrower slices (k = 5: 5 x 96 = 480 accumulator columns; k = 6, 7: 64) rather than tiling 1,
+  // which was 2x slower per FLOP at k = 5 (cfg4: 6.1 ms against 1.8 ms for k = 3).
+  int nw = DW_NT;
+  if (!force1) {
+    if (Dpad % 160 == 0 && k * 160 <= 512) nw = 160;
+    else if (k * 128 <= 512) nw = 128;
+    else if (k * 96 <= 512) nw = 96;
+    else nw = 64;
+    const char* e = getenv("CLSM_CONV_BWD_DW_NW");             // experiments: 64 / 96 / 128 / 160 where k * nw fits
+    if (e != nullptr) { const int v = atoi(e); if ((v == 64 || v == 96 || v == 128 || v == 160) && k * v <= 512) nw = v; }
+  }
   const bool tiling2 = k * nw <= 512 && !force1;
   p.n_cr = tiling2 ? (Dpad + nw - 1) / nw : (Dpad + DW_NT - 1) / DW_NT;
   p.n_slices = (tiling2 ? p.n_mt : k) * p.n_cr;
@@ -1187,8 +1197,8 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
     dw2_tc_kernel<Q, W><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);                             \
   } while (0)
   if (tiling2) {
-    if (L >= DW_KT) { if (nw == 160) DW2_LAUNCH(2, 160); else DW2_LAUNCH(2, 128); }
-    else            { if (nw == 160) DW2_LAUNCH(5, 160); else DW2_LAUNCH(5, 128); }
+    if (L >= DW_KT) { if (nw == 160) DW2_LAUNCH(2, 160); else if (nw == 128) DW2_LAUNCH(2, 128); else if (nw == 96) DW2_LAUNCH(2, 96); else DW2_LAUNCH(2, 64); }
+    else            { if (nw == 160) DW2_LAUNCH(5, 160); else if (nw == 128) DW2_LAUNCH(5, 128); else if (nw == 96) DW2_LAUNCH(5, 96); else DW2_LAUNCH(5, 64); }
   } else if (L >= DW_KT) {
     CLSM_CUDA(cudaFuncSetAttribute(dw_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     dw_tc_kernel<2><<<splits * p.n_slices, DW_THREADS, smem_bytes, st>>>(tmX, p);
