@@ -567,7 +567,7 @@ def profile_phases(net, resident_step, torch):
         s.record()
         r = orig(name, *a)
         e.record()
-        rec.append((name, s, e, mids))
+        rec.append((name, s, e, mids, a))
         return r
     was = net.overlap
     net.overlap = False
@@ -579,12 +579,12 @@ def profile_phases(net, resident_step, torch):
             resident_step(i)
             torch.cuda.synchronize()
             agg, per = {}, {}
-            for name, s, e, mids in rec:
+            for name, s, e, mids, a in rec:
                 key = name.replace("clsm_", "")
                 d = s.elapsed_time(e)
                 agg[key] = agg.get(key, 0.0) + d
                 per.setdefault(key, []).append(d)
-                if mids is not None:
+                if mids is not None and (name != "clsm_conv_pool_bwd_parts" or a[-4] == 3):
                     per.setdefault("dw2_tc", []).append(s.elapsed_time(mids[0]))
                     per.setdefault("conv_bwd_reductions", []).append(mids[0].elapsed_time(mids[1]))
                     per.setdefault("dx2_tc", []).append(mids[1].elapsed_time(e))

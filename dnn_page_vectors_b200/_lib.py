@@ -41,6 +41,9 @@ SIGNATURES = {
                                     vp, vp, vp, i32, i32, vp, sz, vp]),
     "clsm_conv_pool_bwd_parts": (i32, [vp, i32, i64, i32, i32, i32, vp, i32, i32, i32, vp, vp, i32, i32,
                                        vp, vp, vp, i32, i32, i32, vp, sz, vp]),
+    "clsm_conv_bwd_dx_multi_ok": (i32, [i64, i32, i32, vp, i32, i32]),
+    "clsm_conv_bwd_dx_multi_workspace_bytes": (sz, [i32, vp, i32, i32]),
+    "clsm_conv_pool_bwd_dx_multi": (i32, [i64, i32, i32, i32, vp, vp, i32, i32, vp, vp, i32, i32, vp, i32, vp, sz, vp]),
     "clsm_emb_scatter_plan": (i32, [vp, i64, i32, i32, i64, vp, vp, vp, vp, sz, vp]),
     "clsm_emb_scatter_reduce": (i32, [i64, vp, i32, i32, i32, f32, u64, vp, vp, vp, sz, vp]),
     "clsm_pack_conv_w": (i32, [vp, i32, i32, i32, i32, i32, i32, vp, vp]),

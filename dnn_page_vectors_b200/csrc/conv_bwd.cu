@@ -21,6 +21,10 @@ int clsm_conv_bwd_dw_tc(const void* X, int dtype, int L, int Dpad, int64_t S, in
                         const int32_t* A, int ldp, int col0, int F, int k, float* part, cudaStream_t st);          // conv_bwd_tc.cu
 size_t clsm_conv_bwd_dx_tc_bytes(int k, int Dpad, int F);                                               // conv_bwd_tc.cu
 int clsm_conv_bwd_dx_tc_tiling2_ok(int k, int Dpad, int F, int64_t n_rows);
+int clsm_conv_bwd_dx_multi_tc_ok(int n_windows, const int* ks, int Dpad, int F, int64_t n_rows);
+size_t clsm_conv_bwd_dx_multi_tc_bytes(int n_windows, const int* ks, int Dpad, int F);
+int clsm_conv_bwd_dx_multi_tc(const void* const* Wt, const int* ks, int n_windows, int Dpad, int L, int64_t S, const float* G,
+                              const int32_t* A, int ldp, int col0, int F, void* dX, int dx_bf16, void* scratch, cudaStream_t st);
 int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64_t S, const float* G, const int32_t* A,
                         int ldp, int col0, int F, float* dX, int accumulate, int dx_bf16, void* scratch, cudaStream_t st);
 
@@ -307,7 +311,8 @@ int clsm_conv_pool_bwd_parts(const void* X, int dtype, int64_t S, int L, int D, 
   CLSM_LAUNCH_CHECK();
   if (clsm_colsum(G, S, ldp, col0, F, db, cs, kColsumChunks, st) != CLSM_OK) { clsm_set_error("conv_pool_bwd: colsum launch failed"); return CLSM_ECUDA; }
   }
-  if (!(parts & CLSM_BWD_DX)) return CLSM_OK;
+  if (!(parts & CLSM_BWD_DW)) g_clsm_marks[0] = nullptr;      // diagnostics marks of a part that does not run are dropped, not kept
+  if (!(parts & CLSM_BWD_DX)) { g_clsm_marks[1] = nullptr; return CLSM_OK; }
 
   // dX: tensor cores (bf16 mode) -> shared-memory staged CUDA cores -> generic
   void* wb_scratch = static_cast<char*>(sort_scratch) + clsm_conv_bwd_dx_fast_bytes(S, L, F);
@@ -327,6 +332,34 @@ int clsm_conv_pool_bwd_parts(const void* X, int dtype, int64_t S, int L, int D, 
     conv_bwd_dx_kernel<float><<<gx, 256, 0, st>>>(static_cast<const float*>(Wt), k, Dpad, L, cps, G, argmax, ldp, col0, F, dX, first_window ? 0 : 1);
   CLSM_LAUNCH_CHECK();
   return CLSM_OK;
+}
+
+/* ---- dX of several window sizes in one pass (bf16 tensor-core path; conv_bwd_tc.cu) ---- */
+int clsm_conv_bwd_dx_multi_ok(int64_t S, int L, int n_windows, const int* ks, int D, int F) {
+  if (n_windows < 2 || ks == nullptr || S <= 0 || D <= 0) return 0;
+  for (int w = 0; w < n_windows; ++w) if (ks[w] < 1 || L < ks[w]) return 0;
+  return clsm_conv_bwd_dx_multi_tc_ok(n_windows, ks, (D + 63) / 64 * 64, F, S * L);
+}
+
+size_t clsm_conv_bwd_dx_multi_workspace_bytes(int n_windows, const int* ks, int D, int F) {
+  if (n_windows < 1 || ks == nullptr) return 0;
+  return clsm_conv_bwd_dx_multi_tc_bytes(n_windows, ks, (D + 63) / 64 * 64, F);
+}
+
+int clsm_conv_pool_bwd_dx_multi(int64_t S, int L, int D, int Dpad, const void* const* Wt, const int* ks, int n_windows, int F,
+                                const float* G, const int32_t* argmax, int ldp, int col0, void* dX, int dx_dtype,
+                                void* ws, size_t ws_bytes, void* stream) {
+  CLSM_REQUIRE(Wt != nullptr && ks != nullptr && n_windows >= 2 && n_windows <= 4, "conv_pool_bwd_dx_multi: 2..4 windows");
+  CLSM_REQUIRE(dx_dtype == CLSM_F32 || dx_dtype == CLSM_BF16, "conv_pool_bwd_dx_multi: dX must be fp32 or bf16");
+  CLSM_REQUIRE(S > 0 && Dpad == (D + 63) / 64 * 64 && ldp >= col0 + n_windows * F, "conv_pool_bwd_dx_multi: bad sizes");
+  for (int w = 0; w < n_windows; ++w) CLSM_REQUIRE(ks[w] >= 1 && ks[w] <= 7 && L >= ks[w], "conv_pool_bwd_dx_multi: windows must be 1..7 and <= L");
+  if (ws_bytes < clsm_conv_bwd_dx_multi_workspace_bytes(n_windows, ks, D, F)) {
+    clsm_set_error("conv_pool_bwd_dx_multi: workspace too small");
+    return CLSM_EWORKSPACE;
+  }
+  const int rc = clsm_conv_bwd_dx_multi_tc(Wt, ks, n_windows, Dpad, L, S, G, argmax, ldp, col0, F, dX, dx_dtype == CLSM_BF16 ? 1 : 0, ws, as_stream(stream));
+  if (rc == CLSM_EUNSUPPORTED) clsm_set_error("conv_pool_bwd_dx_multi: shape outside the kernel's plan (ask clsm_conv_bwd_dx_multi_ok first)");
+  return rc;
 }
 
 }  // extern "C"

@@ -49,15 +49,16 @@ struct DxParams {
 __device__ long long g_conv_bwd_prof[8];
 
 // Wb[c, j*Fk + f] = Wt[f, j*Dpad + c]   (Fk = fblocks*64, zero padded)
+// (ldw = row length of Wb in elements, col_off = first column written: several windows side by side in one matrix)
 __global__ void pack_wb_kernel(const __nv_bfloat16* __restrict__ Wt, int k, int Dpad, int F, int Fk,
-                               __nv_bfloat16* __restrict__ Wb) {
+                               __nv_bfloat16* __restrict__ Wb, int64_t ldw, int64_t col_off) {
   const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const int64_t K = static_cast<int64_t>(k) * Fk;
   if (i >= K * Dpad) return;
   const int c = static_cast<int>(i / K);
   const int kk = static_cast<int>(i - c * K);
   const int j = kk / Fk, f = kk - j * Fk;
-  Wb[i] = f < F ? Wt[static_cast<int64_t>(f) * k * Dpad + static_cast<int64_t>(j) * Dpad + c] : __float2bfloat16_rn(0.0f);
+  Wb[c * ldw + col_off + kk] = f < F ? Wt[static_cast<int64_t>(f) * k * Dpad + static_cast<int64_t>(j) * Dpad + c] : __float2bfloat16_rn(0.0f);
 }
 
 template <int NCH, int MAXC>      // MAXC = candidate slots per builder thread per chunk: ceil(sequences per tile * 64 / 128)
@@ -515,6 +516,217 @@ dx2_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const Dx2Params p) {
       }
       xphase ^= 1u;
       has_prev = true; pr_lo = r_lo; ps_first = s_first; pnseq = nseq;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512));
+  }
+}
+
+// =====================================================================================================
+// dX of SEVERAL window sizes in one pass (the reference's default model has windows 3 and 4; BASELINE cfg4 has 1, 2, 3, 5):
+//   dX[r, c] = sum_w sum_{j < k_w} sum_f dY_w[r - j, f] * W_w[j, c, f]
+// One launch per window makes every window after the first add into fp32 dX rows in HBM (a 5.2 GB read-modify-write per
+// window on cfg4).  Here the accumulator of a (token tile, M tile) stays in TMEM across the windows: the n_mt regions
+// of a tile are all live until the last window has added its part, the one-hot dY slots are rebuilt per (tile, window),
+// and dX is written once -- as bf16 when asked.  Same roles, barriers and descriptors as dx2_tc_kernel above; the dY
+// tile carries a halo of kmax - 1 rows, so window offset j reads it advanced by (kmax - 1 - j) rows for every window.
+// The weights of all windows sit side by side in ONE matrix Wb (Dpad x sum_w k_w * Fk), window w at column wcol[w].
+struct DxmParams {
+  int64_t n_rows;
+  int L, F, Dpad;
+  int n_mt, NT, n_tiles, fblocks;
+  int nwin, kmax;
+  int k[4], wcol[4], gcol[4];
+  const float* G; const int32_t* A; int ldp;
+  void* dX; int dx_bf16;
+  int last_ks, wstages, xrows;
+};
+
+template <int NCH>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+dxm_tc_kernel(const __grid_constant__ CUtensorMap tmWb, const DxmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t x_slot_bytes = ((static_cast<uint32_t>(p.xrows) * 128u) + 1023u) & ~1023u;
+  const uint32_t w_ring = base;
+  const uint32_t x_ring = base + static_cast<uint32_t>(p.wstages) * MT_BYTES;
+  const int stages = p.wstages + p.fblocks;                   // barrier pairs: weight slots, then dY slots
+  const uint32_t bars = x_ring + static_cast<uint32_t>(p.fblocks) * x_slot_bytes;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (stages + s); };
+  auto tfull_bar = [&](int r) { return bars + 8u * (2 * stages + r); };
+  auto tempty_bar = [&](int r) { return bars + 8u * (2 * stages + 4 + r); };
+  const uint32_t tmem_slot = bars + 8u * (2 * stages + 8);
+
+  const int warp = warp_id_uniform(), lane = threadIdx.x % 32;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) { mbar_init(full_bar(s), s < p.wstages ? 1 : NUM_BLD_WARPS); mbar_init(empty_bar(s), 1); }
+    for (int r = 0; r < 4; ++r) { mbar_init(tfull_bar(r), 1); mbar_init(tempty_bar(r), NUM_EPI_WARPS); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmWb) : "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    // ---- weights: one (window, M tile, filter block, window offset) chunk per slot, warp-uniform loop
+    int ws = 0; uint32_t wphase = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x)
+      for (int w = 0; w < p.nwin; ++w)
+        for (int m = 0; m < p.n_mt; ++m)
+          for (int fb = 0; fb < p.fblocks; ++fb)
+            for (int j = 0; j < p.k[w]; ++j) {
+              mbar_wait(empty_bar(ws), wphase ^ 1u);
+              if (elect_one()) {
+                mbar_expect_tx(full_bar(ws), MT_BYTES);
+                tma_load_2d(w_ring + ws * MT_BYTES, &tmWb, p.wcol[w] + (j * p.fblocks + fb) * KCHUNK, m * MT, full_bar(ws));
+              }
+              if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
+            }
+  } else if (warp == 1) {
+    // ---- MMA issue, warp-uniform loop.  Region m of TMEM = M tile m of the current token tile, for all windows.
+    const uint32_t idesc = make_idesc(p.NT);
+    int ws = 0; uint32_t wphase = 0, xphase = 0, tphase = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      for (int w = 0; w < p.nwin; ++w) {
+        for (int m = 0; m < p.n_mt; ++m) {
+          if (w == 0) { mbar_wait(tempty_bar(m), tphase ^ 1u); tc_fence_after(); }      // the previous tile's rows of this region are stored
+          const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(m * p.NT);
+          for (int fb = 0; fb < p.fblocks; ++fb) {
+            if (m == 0) mbar_wait(full_bar(p.wstages + fb), xphase);
+            const uint32_t x_lo = sw128_desc_lo(x_ring + fb * x_slot_bytes);
+            for (int j = 0; j < p.k[w]; ++j) {
+              mbar_wait(full_bar(ws), wphase);
+              tc_fence_after();
+              const uint32_t a_lo = sw128_desc_lo(w_ring + ws * MT_BYTES);
+              const int nks = fb == p.fblocks - 1 ? p.last_ks : KCHUNK / 16;
+#pragma unroll
+              for (int ks = 0; ks < KCHUNK / 16; ++ks)
+                if (ks < nks)
+                  tc_mma_bf16_u(d_tmem, a_lo + ks * 2, x_lo + static_cast<uint32_t>(p.kmax - 1 - j) * 8u + ks * 2, idesc, (w | fb | j | ks) != 0 ? 1u : 0u);
+              tc_commit_u(empty_bar(ws));
+              if (++ws == p.wstages) { ws = 0; wphase ^= 1u; }
+            }
+            if (m == p.n_mt - 1) tc_commit_u(empty_bar(p.wstages + fb));     // the builders may rebuild this slot
+          }
+          if (w == p.nwin - 1) tc_commit_u(tfull_bar(m));
+        }
+        xphase ^= 1u;
+      }
+      tphase ^= 1u;
+    }
+  } else if (warp < 2 + NUM_EPI_WARPS) {
+    // ---- epilogue: D[c, token] -> dX[token, c], once per (tile, M tile), after the last window
+    const int lq = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int ncol = p.NT / 2;
+    uint32_t tphase = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      const int64_t rbeg = static_cast<int64_t>(tile) * p.NT + half * ncol;
+      for (int m = 0; m < p.n_mt; ++m) {
+        mbar_wait(tfull_bar(m), tphase);
+        tc_fence_after();
+        const int c = m * MT + lq * 32 + lane;
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + static_cast<uint32_t>(m * p.NT + half * ncol);
+        uint32_t v[NCH][16];
+#pragma unroll
+        for (int q = 0; q < NCH; ++q) tc_ld16_async(taddr + q * 16, v[q]);
+        tc_wait_ld();
+        tc_fence_before();
+        if (lane == 0) mbar_arrive(tempty_bar(m));
+        if (c < p.Dpad) {
+          if (p.dx_bf16) {
+            __nv_bfloat16* dst16 = static_cast<__nv_bfloat16*>(p.dX) + rbeg * p.Dpad + c;
+#pragma unroll
+            for (int q = 0; q < NCH; ++q) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const int n = q * 16 + i;
+                if (rbeg + n < p.n_rows) dst16[static_cast<int64_t>(n) * p.Dpad] = __float2bfloat16_rn(__uint_as_float(v[q][i]));
+              }
+            }
+          } else {
+            float* dst = static_cast<float*>(p.dX) + rbeg * p.Dpad + c;
+#pragma unroll
+            for (int q = 0; q < NCH; ++q) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const int n = q * 16 + i;
+                if (rbeg + n < p.n_rows) dst[static_cast<int64_t>(n) * p.Dpad] = __uint_as_float(v[q][i]);
+              }
+            }
+          }
+        }
+      }
+      tphase ^= 1u;
+    }
+  } else {
+    // ---- dY builders (see dx2_tc_kernel): the slots are rebuilt for every (tile, window); what a slot held before is
+    // cleared by recomputing the previous (tile, window)'s hit positions
+    const int bt = threadIdx.x - (2 + NUM_EPI_WARPS) * 32;        // 0..127
+    constexpr int NB = NUM_BLD_WARPS * 32;
+    const int fl = bt & 63, par = bt >> 6;
+    const uint32_t zero_chunks = static_cast<uint32_t>(p.fblocks) * x_slot_bytes / 16;
+    uint8_t* xbase = base_ptr + (x_ring - base);
+    for (uint32_t i = bt; i < zero_chunks; i += NB) reinterpret_cast<uint4*>(xbase)[i] = make_uint4(0u, 0u, 0u, 0u);
+    asm volatile("bar.sync 1, %0;" ::"n"(NB) : "memory");
+    const int rows_used = p.NT + p.kmax - 1;
+    auto tile_geom = [&](int tile, int64_t& r_lo, int64_t& s_first, int& nseq) {
+      r_lo = static_cast<int64_t>(tile) * p.NT - (p.kmax - 1);               // token row of slot row 0 (may be < 0)
+      const int64_t r_first = r_lo < 0 ? 0 : r_lo;
+      int64_t r_last = static_cast<int64_t>(tile) * p.NT + p.NT - 1;
+      if (r_last > p.n_rows - 1) r_last = p.n_rows - 1;
+      s_first = r_first / p.L;
+      nseq = static_cast<int>(r_last / p.L - s_first) + 1;
+    };
+    auto scatter = [&](uint8_t* slot, int col, int64_t r_lo, int64_t s_first, int nseq, bool clear) {
+      for (int sq = par; sq < nseq; sq += 2) {
+        const int64_t sidx = s_first + sq;
+        const float g = __ldg(p.G + sidx * p.ldp + col);
+        const int a = __ldg(p.A + sidx * p.ldp + col);
+        const int64_t row = sidx * p.L + a - r_lo;
+        if (g != 0.0f && row >= 0 && row < rows_used) {
+          const uint32_t r = static_cast<uint32_t>(row);
+          const uint32_t off = r * 128u + ((static_cast<uint32_t>(fl >> 3) ^ (r & 7u)) << 4) + static_cast<uint32_t>(fl & 7) * 2u;
+          *reinterpret_cast<__nv_bfloat16*>(slot + off) = clear ? __float2bfloat16_rn(0.0f) : __float2bfloat16_rn(g);
+        }
+      }
+    };
+    uint32_t xphase = 0;
+    bool has_prev = false;
+    int64_t pr_lo = 0, ps_first = 0; int pnseq = 0, pgcol = 0;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+      int64_t r_lo, s_first; int nseq;
+      tile_geom(tile, r_lo, s_first, nseq);
+      for (int w = 0; w < p.nwin; ++w) {
+        for (int fb = 0; fb < p.fblocks; ++fb) {
+          const int f = fb * 64 + fl;
+          uint8_t* slot = xbase + static_cast<size_t>(fb) * x_slot_bytes;
+          mbar_wait(empty_bar(p.wstages + fb), xphase ^ 1u);
+          if (has_prev && f < p.F) scatter(slot, pgcol + f, pr_lo, ps_first, pnseq, true);
+          asm volatile("bar.sync 2, %0;" ::"n"(NB) : "memory");
+          if (f < p.F) scatter(slot, p.gcol[w] + f, r_lo, s_first, nseq, false);
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(full_bar(p.wstages + fb));
+        }
+        xphase ^= 1u;
+        has_prev = true; pr_lo = r_lo; ps_first = s_first; pnseq = nseq; pgcol = p.gcol[w];
+      }
     }
   }
 
@@ -1052,7 +1264,7 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
 
   __nv_bfloat16* Wb = static_cast<__nv_bfloat16*>(scratch);
   const int64_t n_wb = static_cast<int64_t>(Dpad) * k * Fk;
-  pack_wb_kernel<<<static_cast<unsigned>(ceil_div64(n_wb, 256)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(Wt), k, Dpad, F, Fk, Wb);
+  pack_wb_kernel<<<static_cast<unsigned>(ceil_div64(n_wb, 256)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(Wt), k, Dpad, F, Fk, Wb, static_cast<int64_t>(k) * Fk, 0);
   CLSM_LAUNCH_CHECK();
 
   EncodeTiledFn enc = get_encode();
@@ -1123,6 +1335,94 @@ int clsm_conv_bwd_dx_tc(const void* Wt, int dtype, int k, int Dpad, int L, int64
     fprintf(stderr, "[dx_tc prof] NT %d tiles %d grid %d maxc %d | MMA thread: total %.0f, wait TMEM %.0f, wait operands %.0f (cycles per CTA)\n",
             p.NT, p.n_tiles, grid, maxc, h[4] / static_cast<double>(grid), h[5] / static_cast<double>(grid), h[6] / static_cast<double>(grid));
   }
+  return CLSM_OK;
+}
+
+// ---- dX of several windows in one pass (dxm_tc_kernel) -------------------------------------------------------
+static bool dxm_plan(int n_windows, const int* ks, int Dpad, int F, int64_t n_rows, DxmParams* out) {
+  const char* env = getenv("CLSM_CONV_BWD_DX");
+  if (env != nullptr && (env[0] == 's' || env[0] == '1')) return false;
+  if (n_windows < 2 || n_windows > 4 || Dpad % 64 != 0 || F < 1 || F > 512) return false;
+  DxmParams q{};
+  q.n_mt = (Dpad + MT - 1) / MT;
+  if (q.n_mt > 4 || n_rows + 512 >= (1ll << 31)) return false;
+  q.kmax = 0;
+  int ktot = 0;
+  for (int w = 0; w < n_windows; ++w) { if (ks[w] < 1 || ks[w] > 7) return false; if (ks[w] > q.kmax) q.kmax = ks[w]; ktot += ks[w]; }
+  q.fblocks = (F + 63) / 64;
+  int nt = (512 / q.n_mt) / 32 * 32;                 // all n_mt regions of a tile are live at once
+  if (nt > 224) nt = 224;
+  q.NT = nt; q.nwin = n_windows; q.F = F; q.Dpad = Dpad; q.n_rows = n_rows;
+  q.n_tiles = static_cast<int>(ceil_div64(n_rows, nt));
+  q.last_ks = (F - (q.fblocks - 1) * 64 + 15) / 16;
+  q.xrows = (nt + q.kmax - 1 + 7) / 8 * 8;
+  const int x_slot = (q.xrows * 128 + 1023) / 1024 * 1024;
+  q.wstages = (SMEM_LIMIT - 2048 - q.fblocks * x_slot) / MT_BYTES;
+  if (q.wstages > 8) q.wstages = 8;
+  if (q.wstages < 3) return false;
+  int col = 0;
+  for (int w = 0; w < n_windows; ++w) { q.k[w] = ks[w]; q.wcol[w] = col; q.gcol[w] = w * F; col += ks[w] * q.fblocks * 64; }
+  (void)ktot;
+  *out = q;
+  return true;
+}
+
+int clsm_conv_bwd_dx_multi_tc_ok(int n_windows, const int* ks, int Dpad, int F, int64_t n_rows) {
+  DxmParams q;
+  return dxm_plan(n_windows, ks, Dpad, F, n_rows, &q) ? 1 : 0;
+}
+
+size_t clsm_conv_bwd_dx_multi_tc_bytes(int n_windows, const int* ks, int Dpad, int F) {
+  size_t ktot = 0;
+  for (int w = 0; w < n_windows; ++w) ktot += static_cast<size_t>(ks[w]);
+  return align_up(static_cast<size_t>(Dpad) * ktot * (static_cast<size_t>((F + 63) / 64) * 64) * 2, 256);
+}
+
+// Wt[w]: window w's compute weights (Fpad, k_w * Dpad) bf16; G / A: (S, ldp) with window w at columns col0 + w * F.
+int clsm_conv_bwd_dx_multi_tc(const void* const* Wt, const int* ks, int n_windows, int Dpad, int L, int64_t S, const float* G,
+                              const int32_t* A, int ldp, int col0, int F, void* dX, int dx_bf16, void* scratch, cudaStream_t st) {
+  DxmParams q;
+  if (!dxm_plan(n_windows, ks, Dpad, F, S * L, &q)) return CLSM_EUNSUPPORTED;
+  q.L = L; q.G = G; q.A = A; q.ldp = ldp; q.dX = dX; q.dx_bf16 = dx_bf16;
+  for (int w = 0; w < n_windows; ++w) q.gcol[w] += col0;
+  const int Fk = q.fblocks * 64;
+  int64_t ldw = 0;
+  for (int w = 0; w < n_windows; ++w) ldw += static_cast<int64_t>(ks[w]) * Fk;
+  __nv_bfloat16* Wb = static_cast<__nv_bfloat16*>(scratch);
+  for (int w = 0; w < n_windows; ++w) {
+    const int64_t n_wb = static_cast<int64_t>(Dpad) * ks[w] * Fk;
+    pack_wb_kernel<<<static_cast<unsigned>(ceil_div64(n_wb, 256)), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(Wt[w]), ks[w], Dpad, F, Fk, Wb, ldw, q.wcol[w]);
+    CLSM_LAUNCH_CHECK();
+  }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) { clsm_set_error("conv_pool_bwd(tcgen05): cuTensorMapEncodeTiled unavailable"); return CLSM_ECUDA; }
+  CUtensorMap tmWb;
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(ldw), static_cast<cuuint64_t>(Dpad)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ldw) * 2};
+  cuuint32_t box[2] = {KCHUNK, MT};
+  cuuint32_t estr[2] = {1, 1};
+  if (enc(&tmWb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Wb, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+    clsm_set_error("conv_pool_bwd(tcgen05): cuTensorMapEncodeTiled failed");
+    return CLSM_ECUDA;
+  }
+  int grid = clsm_sm_count();
+  if (grid > q.n_tiles) grid = q.n_tiles;
+  const int x_slot = (q.xrows * 128 + 1023) / 1024 * 1024;
+  const int stages = q.wstages + q.fblocks;
+  const int smem = q.wstages * MT_BYTES + q.fblocks * x_slot + 1024 + 8 * (2 * stages + 9);
+#define DXM_LAUNCH(N)                                                                                            \
+  do {                                                                                                           \
+    CLSM_CUDA(cudaFuncSetAttribute(dxm_tc_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));  \
+    dxm_tc_kernel<N><<<grid, NUM_THREADS, smem, st>>>(tmWb, q);                                                  \
+  } while (0)
+  switch (q.NT / 32) {
+    case 4: DXM_LAUNCH(4); break;
+    case 5: DXM_LAUNCH(5); break;
+    default: DXM_LAUNCH(7); break;
+  }
+#undef DXM_LAUNCH
+  CLSM_LAUNCH_CHECK();
   return CLSM_OK;
 }
 

@@ -244,6 +244,17 @@ class Tower(object):
             # halved); fp32 when several windows accumulate into them or the CUDA-core kernels run
             dx16 = (self.bf16 and len(self.windows) == 1 and self.net.conv_impl != "simt" and
                     lib.clsm_conv_bwd_dx_bf16_ok(S, self.L, self.windows[0], self.D, self.F) == 1)
+            # several window sizes: ONE fused dX pass keeps the accumulators on chip across the windows and writes the
+            # rows once, bf16 too (clsm_conv_pool_bwd_dx_multi), instead of adding into fp32 rows in HBM per window
+            b["dx_multi"] = False
+            if self.bf16 and len(self.windows) > 1 and self.net.conv_impl != "simt":
+                ks_c = (C.c_int * len(self.windows))(*self.windows)
+                if lib.clsm_conv_bwd_dx_multi_ok(S, self.L, len(self.windows), ks_c, self.D, self.F) == 1:
+                    b["dx_multi"], dx16 = True, True
+                    b["ks_c"] = ks_c
+                    b["wt_c"] = (C.c_void_p * len(self.windows))(*[w.data_ptr() for w in self.Wt])
+                    b["ws_dxm_bytes"] = lib.clsm_conv_bwd_dx_multi_workspace_bytes(len(self.windows), ks_c, self.D, self.F)
+                    b["ws_dxm"] = torch.empty(b["ws_dxm_bytes"], dtype=torch.uint8, device=dev)
             b["dx_dtype"] = BF16 if dx16 else F32
             b["dX"] = torch.empty((n_tok, self.Dpad), dtype=torch.bfloat16 if dx16 else torch.float32, device=dev)
             b["mask"] = torch.empty((n_tok, self.Dpad // 16), dtype=torch.int16, device=dev)       # 1 keep bit per element
@@ -350,11 +361,18 @@ class Tower(object):
         streams: dX first, then dW beside the embedding scatter and the table optimizer that consume dX."""
         st = _stream()
         S = b["S"]
+        multi = b.get("dx_multi", False)
+        if multi and parts & 2:
+            call("clsm_conv_pool_bwd_dx_multi", S, self.L, self.D, self.Dpad, b["wt_c"], b["ks_c"], len(self.windows), self.F,
+                 _ptr(b["G"]), _ptr(b["argmax"]), self.P, 0, _ptr(b["dX"]), b["dx_dtype"], _ptr(b["ws_dxm"]), b["ws_dxm_bytes"], st)
+            parts &= 1
+            if not parts:
+                return
         for i, k in enumerate(self.windows):
             gb = self.g_convb[i * self.F:(i + 1) * self.F]
             call("clsm_conv_pool_bwd_parts", _ptr(b["X"]), self.dtype_code, S, self.L, self.D, self.Dpad, _ptr(self.Wt[i]),
                  k, self.F, self.Fpad, _ptr(b["G"]), _ptr(b["argmax"]), self.P, i * self.F,
-                 _ptr(self.g_convW[i]), _ptr(gb), _ptr(b["dX"]), b["dx_dtype"], 1 if i == 0 else 0, parts,
+                 _ptr(self.g_convW[i]), _ptr(gb), _ptr(b["dX"]), F32 if multi else b["dx_dtype"], 1 if (i == 0 or multi) else 0, parts,
                  _ptr(b["ws"]), b["ws_bytes"], st)
 
     def backward_scatter(self, b):

@@ -188,6 +188,18 @@ int clsm_conv_pool_bwd_parts(const void* X, int dtype, int64_t S, int L, int D, 
                              const float* G, const int32_t* argmax, int ldp, int col0,
                              float* dW_ref, float* db, void* dX, int dx_dtype, int first_window, int parts,
                              void* ws, size_t ws_bytes, void* stream);
+/* dX of SEVERAL window sizes in one pass (bf16 tensor-core path): the accumulators stay on chip across the windows and
+ * dX (S*L, Dpad), fp32 or bf16, is written once -- one launch per window makes every window after the first add into
+ * fp32 rows in HBM.  Wt / ks: HOST arrays of n_windows (2..4) device pointers to the windows' compute weights
+ * (Fpad, k_w * Dpad) bf16 and of their widths; window w's columns of G / argmax are col0 + w*F .. col0 + (w+1)*F.
+ * clsm_conv_bwd_dx_multi_ok() = 1 when the kernel takes the shape (else use clsm_conv_pool_bwd_parts per window);
+ * ws: clsm_conv_bwd_dx_multi_workspace_bytes().  The conv weight gradients still come from
+ * clsm_conv_pool_bwd_parts(..., CLSM_BWD_DW, ...) per window. */
+int clsm_conv_bwd_dx_multi_ok(int64_t S, int L, int n_windows, const int* ks, int D, int F);
+size_t clsm_conv_bwd_dx_multi_workspace_bytes(int n_windows, const int* ks, int D, int F);
+int clsm_conv_pool_bwd_dx_multi(int64_t S, int L, int D, int Dpad, const void* const* Wt, const int* ks, int n_windows, int F,
+                                const float* G, const int32_t* argmax, int ldp, int col0, void* dX, int dx_dtype,
+                                void* ws, size_t ws_bytes, void* stream);
 
 /* ---- embedding gradient: deterministic sort + segmented reduce -------------------------------
  * replaces the gradient of Embedding (AdvancedIncSubtensor1 / UnsortedSegmentSum).

@@ -32,7 +32,11 @@ step(0)
 torch.cuda.synchronize()
 M.call = orig
 for name, s, e, mids, a in rec:
-    if name == "clsm_conv_pool_bwd_parts":
+    if name == "clsm_conv_pool_bwd_parts" and a[-4] == 3:
         print("bwd  S=%d k=%d: dW %.3f | reductions %.3f | dX %.3f ms" % (a[2], a[7], s.elapsed_time(mids[0]), mids[0].elapsed_time(mids[1]), mids[1].elapsed_time(e)))
+    elif name == "clsm_conv_pool_bwd_parts":
+        print("bwd  S=%d k=%d: dW + reductions %.3f ms" % (a[2], a[7], s.elapsed_time(e)))
+    elif name == "clsm_conv_pool_bwd_dx_multi":
+        print("bwd  S=%d all windows, fused dX %.3f ms" % (a[0], s.elapsed_time(e)))
     elif name in ("clsm_conv_pool_fwd_d", "clsm_emb_scatter_reduce", "clsm_emb_gather_mask", "clsm_adam_defer_rows", "clsm_adam_defer_settle_tokens", "clsm_dense_bwd"):
         print("%-28s %.3f ms" % (name[5:] + (" k=%d" % a[7] if name == "clsm_conv_pool_fwd_d" else ""), s.elapsed_time(e)))

@@ -131,6 +131,52 @@ def test_tcgen05_backward_bit_exact(shape):
     assert (got[:, D:] == 0).all()
 
 
+@pytest.mark.parametrize("shape", [(40, 100, 300, (1, 2, 3, 5), 300),        # BASELINE cfg4's windows
+                                   (64, 30, 100, (3, 4), 150),               # the reference's literal model (config.py)
+                                   (5, 1000, 64, (2, 7, 3), 256),            # long rows, widest window, two M tiles
+                                   (300, 7, 64, (1, 7), 16),                 # rows as short as the widest window
+                                   (2048, 100, 300, (1, 2, 3, 5), 300)],     # ~915 tiles: every CTA walks several
+                         ids=lambda s: "S%d-L%d-D%d-k%s-F%d" % (s[0], s[1], s[2], "_".join(map(str, s[3])), s[4]))
+@pytest.mark.parametrize("dx16", [False, True], ids=["fp32rows", "bf16rows"])
+def test_fused_multi_window_dx_bit_exact(shape, dx16):
+    """clsm_conv_pool_bwd_dx_multi: the dX of all window sizes accumulated on chip and written once.  Exact-arithmetic
+    inputs: the sum over windows equals the oracle's in any order; bf16 rows are that sum rounded once."""
+    S, L, D, ks, F = shape
+    rng = np.random.RandomState(35)
+    Dpad, Fpad = rup(D, 64), rup(F, 16)
+    nw = len(ks)
+    X = np.zeros((S, L, D), dtype=np.float32)                    # dX does not depend on X
+    G = (rng.randint(-4, 5, size=(S, nw * F)) / 8.0 * (rng.rand(S, nw * F) > 0.4)).astype(np.float32)
+    A = np.zeros((S, nw * F), dtype=np.int32)
+    want = np.zeros((S, L, D), dtype=np.float64)
+    Wts = []
+    for w, k in enumerate(ks):
+        _, W = exact_case(36 + w, 1, L, D, k, F)
+        Wts.append(pack_w(W, Dpad, Fpad, True))
+        Aw = rng.randint(0, L - k + 1, size=(S, F)).astype(np.int32)
+        Aw[0] = 0
+        Aw[S - 1] = L - k
+        A[:, w * F:(w + 1) * F] = Aw
+        want += oracle_conv_bwd_chunked(X, W, G[:, w * F:(w + 1) * F], Aw.astype(np.int64))[2]
+    import ctypes as C
+    ks_c = (C.c_int * nw)(*ks)
+    wt_c = (C.c_void_p * nw)(*[t.data_ptr() for t in Wts])
+    assert lib.clsm_conv_bwd_dx_multi_ok(S, L, nw, ks_c, D, F) == 1
+    ws_bytes = lib.clsm_conv_bwd_dx_multi_workspace_bytes(nw, ks_c, D, F)
+    ws = torch.full((ws_bytes,), 0xA5, dtype=torch.uint8, device=DEV)
+    dX = torch.full((S * L, Dpad), 3.0, dtype=torch.bfloat16 if dx16 else torch.float32, device=DEV)
+    G_d, A_d = dev(G), dev(A)
+    call("clsm_conv_pool_bwd_dx_multi", S, L, D, Dpad, wt_c, ks_c, nw, F, P(G_d), P(A_d), nw * F, 0, P(dX),
+         BF16 if dx16 else _lib.F32, P(ws), ws_bytes, ST())
+    torch.cuda.synchronize()
+    got = dX.float().cpu().numpy()
+    ref = want.reshape(S * L, D).astype(np.float32)
+    if dx16:
+        ref = torch.as_tensor(ref).to(torch.bfloat16).float().numpy()
+    np.testing.assert_array_equal(got[:, :D], ref)
+    assert (got[:, D:] == 0).all()
+
+
 # ------------------------------------------------------------------ retrieval: exact ids
 def exact_topk_oracle(q, c, k, id_base=0, qchunk=8):
     """Top-k by (score desc, id asc) of exact float64 scores, without a full sort per row."""
