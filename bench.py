@@ -518,6 +518,7 @@ def dp_profile(net, resident_step, torch, rank):
         setattr(obj, name, f)
         return orig
     import dnn_page_vectors_b200.parallel as PAR
+    was_pipe, net.dp_pipeline = net.dp_pipeline, False          # phases are timed on the one-stream order
     o0 = wrap(PAR, "allreduce_flat", "allreduce_small (inside exchange)")
     o1 = wrap(net.dp, "exchange", "exchange")
     o2 = wrap(net.dp, "after_adam", "allgather")
@@ -538,6 +539,7 @@ def dp_profile(net, resident_step, torch, rank):
         runs.append(agg)
     net.dp.exchange, net.dp.after_adam, net.query_model.adam, net.doc_model.adam = o1, o2, o3, o4
     PAR.allreduce_flat = o0
+    net.dp_pipeline = was_pipe
     med = {k: round(float(np.median([r[k] for r in runs])), 3) for k in runs[0]}
     sys.stderr.write("[dp profile, rank %d, ms] %s\n" % (rank, json.dumps(med)))
 

@@ -526,6 +526,7 @@ class CLSM(object):
         import os
         self.overlap = os.environ.get("CLSM_OVERLAP", "1") != "0"      # two-stream step, see step_resident
         self._side = None
+        self.dp_pipeline = os.environ.get("CLSM_DP_PIPELINE", "1") != "0"
         self._tail = None              # third stream: scatter + table optimizer beside the conv weight gradients
         self.split_bwd = os.environ.get("CLSM_SPLIT_BWD", "1") != "0"
         self._plan_stream = None
@@ -720,7 +721,47 @@ class CLSM(object):
         self._ev_loss.record(torch.cuda.current_stream())
         if self.overlap:                                            # forward and scatter plans are done with the token buffers
             self._ev_tok_free.record(torch.cuda.current_stream())
-        if self.dp is not None:
+        if self.dp is not None and self.dp.p2p and self.overlap and self.dp_pipeline:
+            # Data parallel, peer-memory path.  The towers are independent after the loss, so the query tower's whole
+            # tail -- backward, row push, small-gradient allreduce, sharded table optimizer with its NVLink broadcast --
+            # runs on this stream while the document tower's tensor-bound backward runs on the high-priority one.
+            # Collectives are issued in the same order on every rank (query tower's first).
+            main = torch.cuda.current_stream()
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=self.device, priority=-1)
+                self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
+            self._ev_fork.record(main)
+            self._side.wait_event(self._ev_fork)
+            self.query_model.backward(bq)
+            gq = self.dp.exchange_tower(self.query_model, bq, "q")
+            self.query_model.adam(bq, self.iterations, gq)
+            dm = self.doc_model
+            if self._tail is None:
+                self._tail = torch.cuda.Stream(device=self.device)
+                self._ev_dx, self._ev_tab = torch.cuda.Event(), torch.cuda.Event()
+            with torch.cuda.stream(self._side):
+                if self.split_bwd:
+                    # dX first: its scatter and the row push to the owners (HBM / NVLink) then run beside the conv
+                    # weight gradients (tensor cores), and the allreduce that orders the pushes follows both
+                    dm.backward_head(bd)
+                    dm.backward_conv(bd, 2)
+                    self._ev_dx.record(self._side)
+                    self._tail.wait_event(self._ev_dx)
+                    with torch.cuda.stream(self._tail):
+                        dm.backward_scatter(bd)
+                        gd = self.dp.push_tower(dm, bd, "d")
+                        self._ev_tab.record(self._tail)
+                    dm.backward_conv(bd, 1)
+                    self._side.wait_event(self._ev_tab)
+                    self.dp.allreduce_small(dm)
+                else:
+                    dm.backward(bd)
+                    gd = self.dp.exchange_tower(dm, bd, "d")
+                dm.adam(bd, self.iterations, gd)
+                self._ev_join.record(self._side)
+            main.wait_event(self._ev_join)
+            self.dp.after_adam(self)
+        elif self.dp is not None:
             self.query_model.backward(bq)
             self.doc_model.backward(bd)
             gq, gd = self.dp.exchange(self, bq, bd)

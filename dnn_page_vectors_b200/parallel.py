@@ -240,38 +240,55 @@ class DataParallel(object):
         """Peer-memory exchange: push each owner's piece of both towers' row-sparse gradients into the owner's
         receive buffers, then allreduce the small gradients -- the collective also orders the pushes before the
         owners' Adam kernels.  Returns per tower the dict Tower.adam() hands to clsm_adam_table_dp."""
+        out = [self._push_tower(tower, b, tag) for tower, b, tag in ((net.query_model, bq, "q"), (net.doc_model, bd, "d"))]
+        allreduce_flat([net.query_model.flat_g, net.doc_model.flat_g], self.group)
+        return out[0], out[1]
+
+    def exchange_tower(self, tower, b, tag):
+        """One tower's half of _exchange_p2p, on the CURRENT stream: push its row-sparse table gradient to the owners,
+        then allreduce its small gradients (which orders the pushes before the owners' Adam).  CLSM.step_resident runs
+        the query tower's exchange and optimizer on one stream while the document tower's backward runs on another;
+        every rank issues the two towers' collectives in the same order."""
+        g = self._push_tower(tower, b, tag)
+        dist.all_reduce(tower.flat_g, group=self.group)
+        return g
+
+    def push_tower(self, tower, b, tag):
+        """the push alone (the caller follows it, on a stream that waits for this one, with allreduce_small)"""
+        return self._push_tower(tower, b, tag)
+
+    def allreduce_small(self, tower):
+        dist.all_reduce(tower.flat_g, group=self.group)
+
+    def _push_tower(self, tower, b, tag):
         from .model import _ptr, _stream
         from ._lib import call
         W = self.world
-        out = []
-        for tower, b, tag in ((net.query_model, bq, "q"), (net.doc_model, bd, "d")):
-            g = self._bufs.get(tag)
-            if g is None:
-                # first step: size and map the receive buffers (collective)
-                nmax = torch.tensor([int(b["n_tok"])], dtype=torch.int64, device=b["dE_rows"].device)
-                dist.all_reduce(nmax, op=dist.ReduceOp.MAX, group=self.group)
-                R = tower.rows_per_owner
-                cap = int(min(R, int(nmax.item())))
-                dev = b["dE_rows"].device
-                rows_in = torch.empty((W, cap, tower.Dpad), dtype=torch.float32, device=dev)
-                map_in = torch.full((W, R), -1, dtype=torch.int32, device=dev)
-                peers_rows = share_across_ranks(rows_in, self.group)
-                peers_map = share_across_ranks(map_in, self.group)
-                g = {"p2p": True, "cap": cap, "tok_basis": int(nmax.item()), "rows_in": rows_in, "map_in": map_in,
-                     "_keep": (peers_rows, peers_map),
-                     "peer_rows": _ptr_array([t.data_ptr() + self.rank * cap * tower.Dpad * 4 for t in peers_rows]),
-                     "peer_map": _ptr_array([t.data_ptr() + self.rank * R * 4 for t in peers_map]),
-                     "seg": torch.zeros(W + 1, dtype=torch.int32, device=dev)}
-                self._bufs[tag] = g
-            if int(b["n_tok"]) > g["tok_basis"]:
-                raise RuntimeError("data-parallel batch grew after the first step (%d > %d tokens per rank): the peer "
-                                   "receive buffers were sized from the first step" % (int(b["n_tok"]), g["tok_basis"]))
-            call("clsm_dp_push_rows", _ptr(b["uniq"]), _ptr(b["n_uniq"]), b["dE_rows"].shape[0], _ptr(b["dE_rows"]), tower.Dpad,
-                 tower.D, _ptr(b["row_of_id"]), tower.V1, tower.rows_per_owner, W, g["peer_rows"], g["peer_map"], g["cap"],
-                 _ptr(g["seg"]), _stream())
-            out.append(g)
-        allreduce_flat([net.query_model.flat_g, net.doc_model.flat_g], self.group)
-        return out[0], out[1]
+        g = self._bufs.get(tag)
+        if g is None:
+            # first step: size and map the receive buffers (collective)
+            nmax = torch.tensor([int(b["n_tok"])], dtype=torch.int64, device=b["dE_rows"].device)
+            dist.all_reduce(nmax, op=dist.ReduceOp.MAX, group=self.group)
+            R = tower.rows_per_owner
+            cap = int(min(R, int(nmax.item())))
+            dev = b["dE_rows"].device
+            rows_in = torch.empty((W, cap, tower.Dpad), dtype=torch.float32, device=dev)
+            map_in = torch.full((W, R), -1, dtype=torch.int32, device=dev)
+            peers_rows = share_across_ranks(rows_in, self.group)
+            peers_map = share_across_ranks(map_in, self.group)
+            g = {"p2p": True, "cap": cap, "tok_basis": int(nmax.item()), "rows_in": rows_in, "map_in": map_in,
+                 "_keep": (peers_rows, peers_map),
+                 "peer_rows": _ptr_array([t.data_ptr() + self.rank * cap * tower.Dpad * 4 for t in peers_rows]),
+                 "peer_map": _ptr_array([t.data_ptr() + self.rank * R * 4 for t in peers_map]),
+                 "seg": torch.zeros(W + 1, dtype=torch.int32, device=dev)}
+            self._bufs[tag] = g
+        if int(b["n_tok"]) > g["tok_basis"]:
+            raise RuntimeError("data-parallel batch grew after the first step (%d > %d tokens per rank): the peer "
+                               "receive buffers were sized from the first step" % (int(b["n_tok"]), g["tok_basis"]))
+        call("clsm_dp_push_rows", _ptr(b["uniq"]), _ptr(b["n_uniq"]), b["dE_rows"].shape[0], _ptr(b["dE_rows"]), tower.Dpad,
+             tower.D, _ptr(b["row_of_id"]), tower.V1, tower.rows_per_owner, W, g["peer_rows"], g["peer_map"], g["cap"],
+             _ptr(g["seg"]), _stream())
+        return g
 
     def after_adam(self, net):
         """Every owner has refreshed the bf16 compute rows of its slice: allgather them in place.  (Peer-memory
