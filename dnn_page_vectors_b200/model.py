@@ -541,7 +541,7 @@ class CLSM(object):
         """Device array lr_tab[s] = Adam's lr_t of step s, valid for s <= upto (the deferred-row kernels replay old steps
         with the step size each of them had).  A change of lr / beta settles every row under the old table first."""
         p = self.params
-        key = (float(p.lr), float(p.beta_1), float(p.beta_2))
+        key = (float(p.lr), float(p.beta_1), float(p.beta_2), float(p.epsilon))
         if self._lr_tab is not None and self._lr_key == key and upto < self._lr_tab.shape[0]:
             return self._lr_tab
         if self._lr_tab is not None and self._lr_key != key:
