@@ -653,20 +653,19 @@ def bench_sharded(net, c, torch, dist, pk, rank, world, shard_pages):
     NB = 16384
     rng = np.random.RandomState(7 + rank)
     pool = [torch.as_tensor(zipf_tokens(rng, c["V"], NB, Ld)).to(dev) for _ in range(8)]
-    b = net.doc_model.buffers(NB, False)
-    out = torch.empty((NB, H), dtype=torch.bfloat16, device=dev)
+    outs = [torch.empty((NB, H), dtype=torch.bfloat16, device=dev) for _ in range(2)]
     n_calls = max(shard_pages // NB, 1)
-    for i in range(3):
+
+    def fill(i, b):
         b["tok"].copy_(pool[i % len(pool)])
-        net.encode_resident(net.doc_model, b, out)
+    # two batches in flight (CLSM.encode_batches): batch i's convolution beside batch i-1's finalize / dense / normalise
+    net.encode_batches(net.doc_model, [NB] * 3, fill, lambda i: outs[i & 1])
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(n_calls):
-        b["tok"].copy_(pool[i % len(pool)])
-        net.encode_resident(net.doc_model, b, out)
+    net.encode_batches(net.doc_model, [NB] * n_calls, fill, lambda i: outs[i & 1])
     e1.record()
     torch.cuda.synchronize()
     enc_ms = maxr(e0.elapsed_time(e1))

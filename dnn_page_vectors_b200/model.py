@@ -223,8 +223,9 @@ class Tower(object):
                 "flat": self.flat, "flat_m": self.flat_m, "flat_v": self.flat_v}
 
     # ---- per-shape scratch (allocated once per (S, train) and reused)
-    def buffers(self, S, train):
-        key = (int(S), bool(train))
+    def buffers(self, S, train, slot=0):
+        """slot: a second (third, ...) independent set of the same shape, for callers that keep two batches in flight"""
+        key = (int(S), bool(train)) if slot == 0 else (int(S), bool(train), int(slot))
         b = self._bufs.get(key)
         if b is not None:
             return b
@@ -279,6 +280,11 @@ class Tower(object):
 
     # ---- forward: tok already in b['tok']
     def forward(self, b, train, seed=0):
+        self.forward_conv(b, train, seed)
+        return self.forward_tail(b, train)
+
+    def forward_conv(self, b, train, seed=0):
+        """embedding lookup (+ dropout) and convolution + max-pool of every window: token ids -> pool keys"""
         net = self.net
         st = _stream()
         S, n_tok = b["S"], b["n_tok"]
@@ -313,11 +319,17 @@ class Tower(object):
             fused = False
         if not fused:
             self._gather_and_conv(b, train, keep, seed, table, ld_table, st)
+        b["keep"], b["seed"] = keep, seed
+
+    def forward_tail(self, b, train):
+        """pool keys -> pooled activations -> semantic vectors"""
+        net = self.net
+        st = _stream()
+        S, seed = b["S"], b["seed"]
         call("clsm_pool_finalize", _ptr(b["keys"]), S, self.P, self.P, _ptr(self.convb), ACT[net.params.activation],
              _ptr(b["pooled"]), _ptr(b["argmax"]), self.P, st)
         call("clsm_dense_fwd", _ptr(b["pooled"]), S, self.P, self.P, _ptr(self.Wd), _ptr(self.bd), self.H,
              ACT[net.params.activation] | (MATH_TF32 if self.bf16 else 0), _ptr(b["sem"]), st)
-        b["keep"], b["seed"] = keep, seed
         b["keep2"] = 1.0
         if train and net.post_dense_dropout:           # v1's second Dropout, dssm_cnn/cnn_dssm.py:149
             b["keep2"], b["seed2"] = 1.0 - net.params.dropout_prob[1], seed ^ 0x5DEECE66D
@@ -527,6 +539,7 @@ class CLSM(object):
         self.overlap = os.environ.get("CLSM_OVERLAP", "1") != "0"      # two-stream step, see step_resident
         self._side = None
         self.dp_pipeline = os.environ.get("CLSM_DP_PIPELINE", "1") != "0"
+        self._enc = None               # encode_batches: two streams and their events
         self._tail = None              # third stream: scatter + table optimizer beside the conv weight gradients
         self.split_bwd = os.environ.get("CLSM_SPLIT_BWD", "1") != "0"
         self._plan_stream = None
@@ -960,21 +973,63 @@ class CLSM(object):
         N = tokens.shape[0]
         if out is None:
             out = torch.empty((N, tower.H), dtype=dtype, device=self.device)
-        for s in range(0, N, batch_size):
-            chunk = tokens[s:s + batch_size]
-            b = tower.buffers(chunk.shape[0], False)
-            b["tok"].copy_(torch.as_tensor(chunk), non_blocking=False)
-            self.encode_resident(tower, b, out[s:s + chunk.shape[0]], normalise)
+        starts = list(range(0, N, batch_size))
+
+        def fill(i, b):
+            b["tok"].copy_(torch.as_tensor(tokens[starts[i]:starts[i] + batch_size]), non_blocking=False)
+        self.encode_batches(tower, [min(batch_size, N - s0) for s0 in starts], fill,
+                            lambda i: out[starts[i]:starts[i] + batch_size], normalise)
         return out
 
-    def encode_resident(self, tower, b, out, normalise=True):
-        sem = tower.forward(b, False)
+    def encode_batches(self, tower, sizes, fill, out_of, normalise=True):
+        """Encode a run of batches with two of them in flight: batch i's convolution (tensor cores, every SM) on one
+        stream, batch i-1's tail -- pool finalize, dense projection, normalisation, ~0.2 of a batch's time as short
+        launches -- on another, two buffer sets alternating.  sizes[i] = rows of batch i; fill(i, b) writes its token ids
+        into b["tok"] (called under the convolution stream); out_of(i) = its (rows, H) destination."""
+        if not sizes:
+            return
+        tower.settle()
+        main = torch.cuda.current_stream()
+        if self._enc is None:
+            self._enc = {"conv": torch.cuda.Stream(device=self.device, priority=-1), "tail": torch.cuda.Stream(device=self.device),
+                         "start": torch.cuda.Event(), "conv_done": [torch.cuda.Event(), torch.cuda.Event()],
+                         "tail_done": [torch.cuda.Event(), torch.cuda.Event()], "end": torch.cuda.Event()}
+        e = self._enc
+        e["start"].record(main)
+        e["conv"].wait_event(e["start"])
+        e["tail"].wait_event(e["start"])
+        used = [False, False]
+        for i, S in enumerate(sizes):
+            slot = i & 1
+            b = tower.buffers(S, False, slot=slot)
+            with torch.cuda.stream(e["conv"]):
+                if used[slot]:
+                    e["conv"].wait_event(e["tail_done"][slot])       # the tail of batch i-2 has read these buffers
+                fill(i, b)
+                tower.forward_conv(b, False)
+                e["conv_done"][slot].record(e["conv"])
+            with torch.cuda.stream(e["tail"]):
+                e["tail"].wait_event(e["conv_done"][slot])
+                self._encode_tail(tower, b, out_of(i), normalise)
+                e["tail_done"][slot].record(e["tail"])
+            used[slot] = True
+        e["end"].record(e["tail"])
+        main.wait_event(e["end"])
+        main.wait_event(e["conv_done"][(len(sizes) - 1) & 1])
+
+    def _encode_tail(self, tower, b, out, normalise):
+        sem = tower.forward_tail(b, False)
         if not normalise:
             out.copy_(sem)
         elif out.dtype == torch.bfloat16:
             call("clsm_normalize_rows_bf16", _ptr(sem), b["S"], tower.H, _ptr(out), _stream())
         else:
             call("clsm_normalize_rows", _ptr(sem), b["S"], tower.H, _ptr(out), _stream())
+
+    def encode_resident(self, tower, b, out, normalise=True):
+        """one batch whose token ids are already in b["tok"], on the current stream"""
+        tower.forward_conv(b, False)
+        self._encode_tail(tower, b, out, normalise)
         return out
 
     def topk(self, query_vecs, corpus_vecs, k=100, id_base=0):

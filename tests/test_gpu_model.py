@@ -304,6 +304,12 @@ def test_bf16_encode_pages_and_topk_against_oracle(H):
     vec = net.encode_pages(pages, batch_size=256, dtype=torch.bfloat16)
     qv = net.encode_queries(queries, dtype=torch.bfloat16)
     assert vec.dtype == torch.bfloat16 and vec.shape == (700, H)
+    # encode_pages keeps two batches in flight on two streams (256 + 256 + 188 rows here): same bits as one batch on one
+    b = net.doc_model.buffers(700, False)
+    b["tok"].copy_(torch.as_tensor(pages))
+    one = torch.empty((700, H), dtype=torch.bfloat16, device=DEV)
+    net.encode_resident(net.doc_model, b, one)
+    assert torch.equal(one, vec)
     ovec = O.normalise_rows(O.tower_fwd(pages.astype(np.int64), round_compute_copies(pd_), "relu")["sem"])
     oq = O.normalise_rows(O.tower_fwd(queries.astype(np.int64), round_compute_copies(pq), "relu")["sem"])
     v, q = vec.float().cpu().numpy().astype(np.float64), qv.float().cpu().numpy().astype(np.float64)
